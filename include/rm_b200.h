@@ -1,0 +1,161 @@
+/*
+ * rm_b200.h — C ABI of the B200-native sphere-tracing render pass.
+ *
+ * This is the drop-in boundary for the reference's `src/ray_marching` render pass
+ * (Mesoptier/ray-marching).  The reference has no FFI; its plugin surface is the pair
+ *   RayMarchingResources::new(&RenderState)                  renderer.rs:51-175   (init)
+ *   impl egui_wgpu::CallbackTrait for RayMarchingCallback    renderer.rs:195-256  (prepare, paint)
+ * and every entry point below names the piece of that surface it replaces.  The byte layouts
+ * taken by rm_prepare / rm_set_limits are exactly the reference's GPU buffer contents, so a Rust
+ * host can pass `Uniforms{..}.as_shader_bytes()` (renderer.rs:213-222), `builder.cmd_count` and
+ * `builder.buffer` (renderer.rs:230-239) unchanged.  See INTEGRATION.md for the Rust binding.
+ *
+ * There is exactly one implementation behind this ABI: hand-written CUDA kernels for sm_100a.
+ * There is no CPU path and no fallback; if CUDA or a device is unavailable every call returns
+ * RM_E_CUDA.  No call throws or aborts across the boundary.
+ *
+ * Threading: one rm_ctx per device; a ctx is not thread-safe but may move between threads.
+ * rm_paint is asynchronous on the stream it is given; rm_download / rm_sync synchronise.
+ */
+#ifndef RM_B200_H
+#define RM_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+#define RM_API
+#else
+#define RM_API __attribute__((visibility("default")))
+#endif
+
+typedef struct rm_ctx rm_ctx;
+
+/* ---- error codes (reference behaviour: unwrap() panics, renderer.rs:24,203,250) ---------- */
+enum {
+    RM_OK = 0,
+    RM_E_INVALID_ARG = -1,
+    RM_E_PROGRAM_TOO_LARGE = -2, /* > capacity words; reference: 1024-B buffer TODO renderer.rs:229 */
+    RM_E_BAD_OPCODE = -3,        /* reference: silently returns 0.0 and desyncs, wgsl:223-225 */
+    RM_E_STACK_OVERFLOW = -4,    /* value stack > 32, wgsl:173 */
+    RM_E_STACK_UNBALANCED = -5,  /* pop from empty stack / truncated params / empty result */
+    RM_E_CUDA = -6,
+    RM_E_NOT_PREPARED = -7,
+    RM_E_BAD_PARAM = -8          /* SmoothUnion k <= 0 or non-finite */
+};
+
+/* ---- byte sizes of the reference's GPU buffers --------------------------------------------- */
+#define RM_UNIFORMS_BYTES 144u /* Uniforms: extent@0, inv_proj@16, inv_view@80   renderer.rs:29-34 */
+#define RM_LIMITS_BYTES 12u    /* RayMarchLimits {f32 min_dist, f32 max_dist, u32 max_iter} :36-41 */
+#define RM_DEFAULT_MAX_WORDS 255u /* 1024-B command buffer minus cmd_count       renderer.rs:144 */
+#define RM_STACK_MAX 32u          /* value_stack_max_size                         wgsl:173 */
+#define RM_SAMPLES_PER_PIXEL 16u  /* aa_samples^2                                 wgsl:34 */
+
+/* ---- command opcodes: CSGCommandType, csg/builder.rs:1-24 ---------------------------------- */
+enum {
+    RM_OP_SPHERE = 0,         /* [0, cx,cy,cz, r]          sphere.rs:15-21, wgsl:229-233 */
+    RM_OP_BOX = 1,            /* [1, cx,cy,cz, rx,ry,rz]   box.rs:14-20,   wgsl:235-240 */
+    RM_OP_UNION = 100,        /* [100]   min(a,b)          wgsl:242-246 */
+    RM_OP_SUBTRACTION = 101,  /* [101]   max(a,-b)         wgsl:248-252 */
+    RM_OP_INTERSECTION = 102, /* [102]   max(a,b)   extension: slot reserved at builder.rs:14 */
+    RM_OP_SMOOTH_UNION = 103  /* [103,k] polynomial smooth-min, extension */
+};
+
+/* ---- arithmetic mode ------------------------------------------------------------------------ */
+enum {
+    RM_MODE_EXACT = 0, /* IEEE add/mul/div/sqrt, no FMA contraction: bit-identical to the oracle */
+    RM_MODE_FAST = 1   /* FMA contraction + MUFU sqrt/rcp: within the north-star parity gates */
+};
+
+/* ---- kernel selection -------------------------------------------------------------------------- */
+enum {
+    RM_KERNEL_WAVEFRONT = 0, /* persistent warps over 8x4 tiles with ballot refill of ray slots (default) */
+    RM_KERNEL_SIMPLE = 1     /* one thread per sample ray + resolve pass (verification path) */
+};
+
+/* sample classes of the debug AOV */
+enum { RM_CLS_SKY = 0, RM_CLS_FLOOR = 1, RM_CLS_OBJECT = 2 };
+
+/* ---- lifetime: replaces RayMarchingResources::new, renderer.rs:51-175 ---------------------- */
+/* Creates the per-device resources: limits (defaults 0.01 / 100.0 / 100, renderer.rs:133-137),
+ * command buffer (RM_DEFAULT_MAX_WORDS words) and uniforms. */
+RM_API int rm_create(int cuda_device, rm_ctx **out);
+/* Same with a larger command buffer (resolves the TODO at renderer.rs:229). */
+RM_API int rm_create_ex(int cuda_device, uint32_t max_words, rm_ctx **out);
+/* Replaces Drop of the callback_resources type-map (main.rs:30-34). */
+RM_API void rm_destroy(rm_ctx *ctx);
+
+/* Replaces the constant RayMarchLimits upload, renderer.rs:130-140 (12 bytes). */
+RM_API int rm_set_limits(rm_ctx *ctx, const void *limits12);
+RM_API int rm_set_mode(rm_ctx *ctx, int mode);
+RM_API int rm_get_mode(rm_ctx *ctx);
+RM_API int rm_set_kernel(rm_ctx *ctx, int kernel);
+
+/* ---- per frame: replaces RayMarchingCallback::prepare, renderer.rs:196-242 ------------------ */
+/* Validates the program (opcodes, word count, stack discipline), then uploads the 144-byte
+ * uniform block and the command words.  Inputs are borrowed for the call only. */
+RM_API int rm_prepare(rm_ctx *ctx, const void *uniforms144, uint32_t cmd_count, const uint32_t *words,
+                      uint32_t n_words);
+/* Uniform-only update (new camera pose, program unchanged) — SURVEY.md §8(f) N2/N3. */
+RM_API int rm_prepare_uniforms(rm_ctx *ctx, const void *uniforms144);
+/* Static validation only (no device work): same codes as rm_prepare. */
+RM_API int rm_validate_program(uint32_t cmd_count, const uint32_t *words, uint32_t n_words,
+                               uint32_t max_words);
+
+/* ---- per frame: replaces RayMarchingCallback::paint, renderer.rs:244-255 -------------------- */
+/* Shades rows [row0,row0+nrows) of a W×H frame (row 0 = top) as RGBA8 (R,G,B,A bytes; A=255).
+ * dst_rgba8_dev: device pointer receiving the band, row `row0` at offset 0, `pitch_bytes`
+ * between rows (>= 4*W, multiple of 16); NULL = ctx-owned buffer (read back with rm_download).
+ * cuda_stream: a cudaStream_t, or NULL for the ctx's own stream.  Asynchronous. */
+RM_API int rm_paint(rm_ctx *ctx, uint32_t W, uint32_t H, uint32_t row0, uint32_t nrows,
+                    void *dst_rgba8_dev, size_t pitch_bytes, void *cuda_stream);
+/* Pose batch (config 5): paints n_poses frames from an array of 144-byte uniform blocks held in
+ * HOST memory; frame p goes to dst + p*frame_stride_bytes (device memory), or, when dst is NULL,
+ * every frame overwrites the ctx-owned buffer (throughput mode). */
+RM_API int rm_paint_poses(rm_ctx *ctx, const void *uniforms144_array, uint32_t n_poses, uint32_t W,
+                          uint32_t H, void *dst_rgba8_dev, size_t pitch_bytes,
+                          size_t frame_stride_bytes, void *cuda_stream);
+/* Copies the ctx-owned framebuffer of the last rm_paint(dst=NULL) to host memory; synchronises. */
+RM_API int rm_download(rm_ctx *ctx, void *host_rgba8, size_t bytes);
+RM_API int rm_sync(rm_ctx *ctx);
+
+/* ---- debug / verification surface (untimed) -------------------------------------------------- */
+/* Straightforward one-thread-per-sample kernels that also emit the AOVs the parity gates need.
+ * All pointers are HOST memory and may be NULL.  cls: nrows*W*16 bytes (sample i*4+j);
+ * t: nrows*W*16 floats (marched distance for object hits, floor_dist otherwise);
+ * counters: {N_step, N_hit, N_floor, N_sample}; rgba: nrows*W*4 bytes. */
+RM_API int rm_paint_debug(rm_ctx *ctx, uint32_t W, uint32_t H, uint32_t row0, uint32_t nrows,
+                          uint8_t *cls_host, float *t_host, uint64_t *counters4, uint8_t *rgba_host);
+/* Evaluates the prepared program's map_scene at n host points (xyz interleaved). */
+RM_API int rm_map(rm_ctx *ctx, const float *pts_host, uint64_t n, float *out_host);
+/* Work counters {N_step, N_hit, N_floor, N_sample} accumulated by rm_paint when enabled with
+ * rm_set_counters(ctx, 1) (adds atomics; keep off when timing). */
+RM_API int rm_set_counters(rm_ctx *ctx, int enable);
+RM_API int rm_get_counters(rm_ctx *ctx, uint64_t *counters4, int reset);
+
+/* ---- measurement helpers --------------------------------------------------------------------- */
+/* Records CUDA event `slot` (0..15) on the ctx stream / returns elapsed ms between two slots. */
+RM_API int rm_mark(rm_ctx *ctx, int slot);
+RM_API int rm_elapsed_ms(rm_ctx *ctx, int slot_a, int slot_b, float *ms);
+/* Writes a 256-MiB scratch buffer (> 126 MB L2) on the ctx stream. */
+RM_API int rm_flush_l2(rm_ctx *ctx);
+/* FFMA micro-benchmark: measured FP32 peak in TFLOP/s (2 flop per FFMA) and the SM count. */
+RM_API int rm_fp32_peak(rm_ctx *ctx, double *tflops, int *sm_count, int *sm_clock_khz);
+/* Number of kernels launched by this ctx since creation (for bench.py's gpu_launches). */
+RM_API uint64_t rm_launch_count(rm_ctx *ctx);
+/* Pinned host memory for rm_download / e2e runs. */
+RM_API void *rm_host_alloc(size_t bytes);
+RM_API void rm_host_free(void *p);
+
+RM_API const char *rm_last_error(rm_ctx *ctx);
+RM_API const char *rm_strerror(int code);
+RM_API const char *rm_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RM_B200_H */

@@ -321,11 +321,17 @@ int rmo_render(const void *uniforms144, const void *limits12, uint32_t cmd_count
 #else
     (void)nthreads;
 #endif
+    /* work items = 64-pixel chunks of a row, so that single rows also use every core */
+    const int64_t chunks_per_row = ((int64_t)W + 63) / 64;
+    const int64_t n_chunks = chunks_per_row * (int64_t)nrows;
 #pragma omp parallel for schedule(dynamic, 1) reduction(+ : n_step, n_hit, n_floor, n_sample)
-    for (int64_t r = 0; r < (int64_t)nrows; ++r) {
+    for (int64_t ch = 0; ch < n_chunks; ++ch) {
         rmo_counters cnt = {0, 0, 0, 0};
-        uint32_t py = row0 + (uint32_t)r;
-        for (uint32_t px = 0; px < W; ++px) {
+        const int64_t r = ch / chunks_per_row;
+        const uint32_t x0 = (uint32_t)(ch % chunks_per_row) * 64u;
+        const uint32_t x1 = x0 + 64u < W ? x0 + 64u : W;
+        const uint32_t py = row0 + (uint32_t)r;
+        for (uint32_t px = x0; px < x1; ++px) {
             size_t pix = (size_t)r * W + px;
             shade_pixel(&U, &sc, W, H, px, py, rgba + pix * 4, cls ? cls + pix * 16 : NULL,
                         t ? t + pix * 16 : NULL, &cnt);

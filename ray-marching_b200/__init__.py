@@ -1,0 +1,264 @@
+"""ray_marching_b200 — ctypes binding of the C-ABI render-pass library (include/rm_b200.h).
+
+The directory is named ``ray-marching_b200``; import it with ``rm_import.load()`` (repo root) which
+registers it as the module ``ray_marching_b200``.
+
+There is exactly one implementation behind this binding: the sm_100a CUDA kernels in
+``librm_b200.so``.  If the library is missing, or there is no CUDA device, calls raise — there is no
+CPU path (the CPU oracle lives in ``oracle/`` and is test infrastructure only).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import subprocess
+from pathlib import Path
+
+import numpy as np
+
+PKG_DIR = Path(__file__).resolve().parent
+LIB_PATH = PKG_DIR / "librm_b200.so"
+HOST_LIB_PATH = PKG_DIR / "librm_host.so"
+
+RM_OK = 0
+MODE_EXACT, MODE_FAST = 0, 1
+KERNEL_WAVEFRONT, KERNEL_SIMPLE = 0, 1
+UNIFORMS_BYTES, LIMITS_BYTES = 144, 12
+
+# every symbol include/rm_b200.h declares (checked by tests/test_abi_symbols.py)
+ABI_SYMBOLS = [
+    "rm_create", "rm_create_ex", "rm_destroy", "rm_set_limits", "rm_set_mode", "rm_get_mode", "rm_set_kernel",
+    "rm_prepare", "rm_prepare_uniforms", "rm_validate_program", "rm_paint", "rm_paint_poses", "rm_download",
+    "rm_sync", "rm_paint_debug", "rm_map", "rm_set_counters", "rm_get_counters", "rm_mark", "rm_elapsed_ms",
+    "rm_flush_l2", "rm_fp32_peak", "rm_launch_count", "rm_host_alloc", "rm_host_free", "rm_last_error",
+    "rm_strerror", "rm_version",
+]
+
+
+class RmError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"rm_b200 error {code}: {msg}")
+        self.code = code
+
+
+def build(verbose: bool = False) -> None:
+    """Compile librm_b200.so and librm_host.so in-tree for sm_100a (nvcc cross-compiles without a GPU)."""
+    for d in ("csrc", "host"):
+        if not (PKG_DIR / d / "Makefile").exists():
+            continue
+        r = subprocess.run(["make", "-C", str(PKG_DIR / d)], capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError(f"build of {d} failed:\n{r.stdout}\n{r.stderr}")
+        if verbose:
+            print(r.stdout)
+
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    """Loads librm_b200.so; raises if it has not been built (no fallback)."""
+    global _lib
+    if _lib is None:
+        if not LIB_PATH.exists():
+            raise RuntimeError(f"{LIB_PATH} is missing: run __graft_entry__.build() (nvcc, sm_100a) first")
+        L = C.CDLL(str(LIB_PATH))
+        vp, u32, u64, sz, i = C.c_void_p, C.c_uint32, C.c_uint64, C.c_size_t, C.c_int
+        sig = {
+            "rm_create": (i, [i, C.POINTER(vp)]),
+            "rm_create_ex": (i, [i, u32, C.POINTER(vp)]),
+            "rm_destroy": (None, [vp]),
+            "rm_set_limits": (i, [vp, vp]),
+            "rm_set_mode": (i, [vp, i]),
+            "rm_get_mode": (i, [vp]),
+            "rm_set_kernel": (i, [vp, i]),
+            "rm_prepare": (i, [vp, vp, u32, vp, u32]),
+            "rm_prepare_uniforms": (i, [vp, vp]),
+            "rm_validate_program": (i, [u32, vp, u32, u32]),
+            "rm_paint": (i, [vp, u32, u32, u32, u32, vp, sz, vp]),
+            "rm_paint_poses": (i, [vp, vp, u32, u32, u32, vp, sz, sz, vp]),
+            "rm_download": (i, [vp, vp, sz]),
+            "rm_sync": (i, [vp]),
+            "rm_paint_debug": (i, [vp, u32, u32, u32, u32, vp, vp, vp, vp]),
+            "rm_map": (i, [vp, vp, u64, vp]),
+            "rm_set_counters": (i, [vp, i]),
+            "rm_get_counters": (i, [vp, vp, i]),
+            "rm_mark": (i, [vp, i]),
+            "rm_elapsed_ms": (i, [vp, i, i, C.POINTER(C.c_float)]),
+            "rm_flush_l2": (i, [vp]),
+            "rm_fp32_peak": (i, [vp, C.POINTER(C.c_double), C.POINTER(i), C.POINTER(i)]),
+            "rm_launch_count": (u64, [vp]),
+            "rm_host_alloc": (vp, [sz]),
+            "rm_host_free": (None, [vp]),
+            "rm_last_error": (C.c_char_p, [vp]),
+            "rm_strerror": (C.c_char_p, [i]),
+            "rm_version": (C.c_char_p, []),
+        }
+        for name, (res, args) in sig.items():
+            f = getattr(L, name)
+            f.restype, f.argtypes = res, args
+        _lib = L
+    return _lib
+
+
+def _words_arr(words) -> np.ndarray:
+    return np.ascontiguousarray(np.asarray(words, dtype=np.uint32))
+
+
+def validate_program(cmd_count: int, words, max_words: int = 255) -> int:
+    """Static validation only — no device needed.  Returns an RM_* code."""
+    w = _words_arr(words)
+    return lib().rm_validate_program(cmd_count, w.ctypes.data if w.size else None, w.size, max_words)
+
+
+class PinnedBuffer:
+    """Page-locked host buffer exposed as a numpy uint8 array."""
+
+    def __init__(self, nbytes: int):
+        self.ptr = lib().rm_host_alloc(nbytes)
+        if not self.ptr:
+            raise RmError(-6, "rm_host_alloc failed")
+        self.nbytes = nbytes
+        self.array = np.ctypeslib.as_array((C.c_uint8 * nbytes).from_address(self.ptr))
+
+    def free(self):
+        if self.ptr:
+            lib().rm_host_free(self.ptr)
+            self.ptr = None
+
+    def __del__(self):
+        self.free()
+
+
+class Context:
+    """One device's render-pass resources (the reference's RayMarchingResources, renderer.rs:43-175)."""
+
+    def __init__(self, device: int = 0, max_words: int = 255):
+        self._L = lib()
+        h = C.c_void_p()
+        rc = self._L.rm_create_ex(device, max_words, C.byref(h))
+        if rc != RM_OK:
+            raise RmError(rc, f"rm_create_ex(device={device}): {self._L.rm_strerror(rc).decode()} "
+                              "(a CUDA device of compute capability 10.x is required; there is no CPU path)")
+        self._h = h
+        self.device = device
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.rm_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        self.close()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _chk(self, rc: int):
+        if rc != RM_OK:
+            raise RmError(rc, self._L.rm_last_error(self._h).decode() or self._L.rm_strerror(rc).decode())
+
+    # ---- configuration
+    def set_limits(self, min_dist=0.01, max_dist=100.0, max_iter=100):
+        b = np.array([min_dist, max_dist], np.float32).tobytes() + np.array([max_iter], np.uint32).tobytes()
+        self._chk(self._L.rm_set_limits(self._h, b))
+
+    def set_mode(self, mode: int):
+        self._chk(self._L.rm_set_mode(self._h, mode))
+
+    def set_kernel(self, kernel: int):
+        self._chk(self._L.rm_set_kernel(self._h, kernel))
+
+    # ---- prepare (renderer.rs:196-242)
+    def prepare(self, uniforms: bytes, cmd_count: int, words):
+        assert len(uniforms) == UNIFORMS_BYTES
+        w = _words_arr(words)
+        self._chk(self._L.rm_prepare(self._h, uniforms, cmd_count, w.ctypes.data if w.size else None, w.size))
+
+    def prepare_uniforms(self, uniforms: bytes):
+        assert len(uniforms) == UNIFORMS_BYTES
+        self._chk(self._L.rm_prepare_uniforms(self._h, uniforms))
+
+    # ---- paint (renderer.rs:244-255)
+    def paint(self, W: int, H: int, row0: int = 0, nrows: int | None = None, dst_ptr: int | None = None,
+              pitch: int = 0, stream: int | None = None):
+        nrows = H - row0 if nrows is None else nrows
+        self._chk(self._L.rm_paint(self._h, W, H, row0, nrows, dst_ptr, pitch, stream))
+
+    def paint_poses(self, uniforms_array: bytes, n_poses: int, W: int, H: int, dst_ptr: int | None = None,
+                    pitch: int = 0, frame_stride: int = 0, stream: int | None = None):
+        assert len(uniforms_array) >= n_poses * UNIFORMS_BYTES
+        self._chk(self._L.rm_paint_poses(self._h, uniforms_array, n_poses, W, H, dst_ptr, pitch, frame_stride, stream))
+
+    def download(self, out: np.ndarray | PinnedBuffer | None = None, nbytes: int | None = None) -> np.ndarray:
+        if isinstance(out, PinnedBuffer):
+            self._chk(self._L.rm_download(self._h, out.ptr, nbytes or out.nbytes))
+            return out.array
+        assert out is not None and out.flags["C_CONTIGUOUS"]
+        self._chk(self._L.rm_download(self._h, out.ctypes.data, nbytes or out.nbytes))
+        return out
+
+    def render(self, uniforms: bytes, cmd_count: int, words, W: int, H: int, row0: int = 0,
+               nrows: int | None = None) -> np.ndarray:
+        """prepare + paint + download -> uint8 [nrows, W, 4] (host)."""
+        nrows = H - row0 if nrows is None else nrows
+        self.prepare(uniforms, cmd_count, words)
+        self.paint(W, H, row0, nrows)
+        out = np.empty((nrows, W, 4), np.uint8)
+        if nrows:
+            self.download(out)
+        return out
+
+    def sync(self):
+        self._chk(self._L.rm_sync(self._h))
+
+    # ---- verification surface
+    def paint_debug(self, W: int, H: int, row0: int = 0, nrows: int | None = None, aov: bool = True):
+        nrows = H - row0 if nrows is None else nrows
+        cls = np.zeros((nrows, W, 16), np.uint8) if aov else None
+        t = np.zeros((nrows, W, 16), np.float32) if aov else None
+        cnt = np.zeros(4, np.uint64)
+        rgba = np.zeros((nrows, W, 4), np.uint8)
+        self._chk(self._L.rm_paint_debug(self._h, W, H, row0, nrows, cls.ctypes.data if aov else None,
+                                         t.ctypes.data if aov else None, cnt.ctypes.data, rgba.ctypes.data))
+        out = {"rgba": rgba, "counters": cnt}
+        if aov:
+            out["cls"], out["t"] = cls, t
+        return out
+
+    def map(self, pts: np.ndarray) -> np.ndarray:
+        pts = np.ascontiguousarray(pts, np.float32).reshape(-1, 3)
+        out = np.zeros(pts.shape[0], np.float32)
+        self._chk(self._L.rm_map(self._h, pts.ctypes.data, pts.shape[0], out.ctypes.data))
+        return out
+
+    def set_counters(self, on: bool):
+        self._chk(self._L.rm_set_counters(self._h, int(on)))
+
+    def get_counters(self, reset: bool = True) -> np.ndarray:
+        cnt = np.zeros(4, np.uint64)
+        self._chk(self._L.rm_get_counters(self._h, cnt.ctypes.data, int(reset)))
+        return cnt
+
+    # ---- measurement
+    def mark(self, slot: int):
+        self._chk(self._L.rm_mark(self._h, slot))
+
+    def elapsed_ms(self, a: int, b: int) -> float:
+        ms = C.c_float()
+        self._chk(self._L.rm_elapsed_ms(self._h, a, b, C.byref(ms)))
+        return ms.value
+
+    def flush_l2(self):
+        self._chk(self._L.rm_flush_l2(self._h))
+
+    def fp32_peak(self):
+        tf, sm, khz = C.c_double(), C.c_int(), C.c_int()
+        self._chk(self._L.rm_fp32_peak(self._h, C.byref(tf), C.byref(sm), C.byref(khz)))
+        return {"tflops": tf.value, "sm_count": sm.value, "sm_clock_khz": khz.value}
+
+    @property
+    def launch_count(self) -> int:
+        return int(self._L.rm_launch_count(self._h))

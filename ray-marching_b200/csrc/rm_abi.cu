@@ -1,0 +1,226 @@
+// rm_abi.cu — the extern "C" entry points of include/rm_b200.h.
+// Host-side state of one device: the reference's RayMarchingResources (renderer.rs:43-49) minus
+// all wgpu plumbing — limits, command buffer (decoded), uniforms — plus a framebuffer.
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+
+#include "../../include/rm_b200.h"
+#include "rm_kernels.h"
+#include "rm_program.h"
+#include "rm_wavefront.h"
+
+using namespace rm;
+
+namespace {
+constexpr uint32_t kMaxWordsCap = 3072;  // decoded program must fit in shared memory (48 B/insn)
+constexpr int kEventSlots = 16;
+constexpr size_t kFlushBytes = 256ull << 20;
+}  // namespace
+
+struct rm_ctx {
+    int device = 0;
+    int sm_count = 0;
+    uint32_t max_words = RM_DEFAULT_MAX_WORDS;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t events[kEventSlots] = {};
+    cudaEvent_t upload_done = nullptr;
+    int mode = RM_MODE_EXACT;
+    int kernel = RM_KERNEL_WAVEFRONT;
+    bool prepared = false;
+    bool counters_on = false;
+    float limits_f[2] = {0.01f, 100.0f};  // renderer.rs:133-137
+    uint32_t max_iter = 100;
+    float uniforms[36] = {};
+    Program prog;
+    RmInsn *d_prog = nullptr;
+    RmInsn *h_prog = nullptr;  // pinned staging
+    size_t prog_cap = 0;       // instructions
+    uint8_t *d_fb = nullptr;
+    size_t fb_cap = 0, fb_bytes = 0;
+    float *d_codes = nullptr;
+    size_t codes_cap = 0;
+    void *d_flush = nullptr;
+    unsigned long long *d_counters = nullptr;
+    WavefrontState wf;
+    cudaStream_t last_paint_stream = nullptr;
+    uint64_t launches = 0;
+    std::string err;
+};
+
+namespace {
+
+int fail(rm_ctx *c, int code, const char *what, cudaError_t e = cudaSuccess) {
+    if (c) {
+        c->err = what;
+        if (e != cudaSuccess) {
+            c->err += ": ";
+            c->err += cudaGetErrorString(e);
+        }
+    }
+    return code;
+}
+#define RM_CUDA(ctx, call)                                             \
+    do {                                                               \
+        cudaError_t e__ = (call);                                      \
+        if (e__ != cudaSuccess) return fail((ctx), RM_E_CUDA, #call, e__); \
+    } while (0)
+
+int ensure(rm_ctx *c, void **p, size_t *cap, size_t need) {
+    if (need <= *cap) return RM_OK;
+    if (*p) cudaFree(*p);
+    *p = nullptr;
+    *cap = 0;
+    RM_CUDA(c, cudaMalloc(p, need));
+    *cap = need;
+    return RM_OK;
+}
+
+FrameParams make_params(const rm_ctx *c, const float *u, uint32_t W, uint32_t H, uint32_t row0, uint32_t nrows) {
+    FrameParams fp;
+    std::memcpy(fp.extent, u, 8);
+    std::memcpy(fp.inv_proj, u + 4, 64);
+    std::memcpy(fp.inv_view, u + 20, 64);
+    fp.min_dist = c->limits_f[0];
+    fp.max_dist = c->limits_f[1];
+    fp.max_iter = c->max_iter;
+    fp.W = W; fp.H = H; fp.row0 = row0; fp.nrows = nrows;
+    fp.n_insn = (uint32_t)c->prog.insns.size();
+    return fp;
+}
+
+int check_band(rm_ctx *c, uint32_t W, uint32_t H, uint32_t row0, uint32_t nrows) {
+    if (!c) return RM_E_INVALID_ARG;
+    if (W == 0 || H == 0 || W > 65536 || H > 65536) return fail(c, RM_E_INVALID_ARG, "bad frame size");
+    if ((uint64_t)row0 + nrows > H) return fail(c, RM_E_INVALID_ARG, "band outside frame");
+    if (!c->prepared) return fail(c, RM_E_NOT_PREPARED, "rm_prepare has not been called");
+    return RM_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char *rm_version(void) { return "rm_b200 0.1 (sm_100a)"; }
+
+const char *rm_strerror(int code) {
+    switch (code) {
+        case RM_OK: return "ok";
+        case RM_E_INVALID_ARG: return "invalid argument";
+        case RM_E_PROGRAM_TOO_LARGE: return "command buffer larger than capacity";
+        case RM_E_BAD_OPCODE: return "unknown command opcode";
+        case RM_E_STACK_OVERFLOW: return "value stack deeper than 32";
+        case RM_E_STACK_UNBALANCED: return "value stack underflow or truncated command stream";
+        case RM_E_CUDA: return "CUDA error";
+        case RM_E_NOT_PREPARED: return "no program/uniforms prepared";
+        case RM_E_BAD_PARAM: return "bad command parameter";
+        default: return "unknown error";
+    }
+}
+
+const char *rm_last_error(rm_ctx *ctx) { return ctx ? ctx->err.c_str() : "null ctx"; }
+
+int rm_create_ex(int cuda_device, uint32_t max_words, rm_ctx **out) {
+    if (!out || max_words == 0 || max_words > kMaxWordsCap) return RM_E_INVALID_ARG;
+    *out = nullptr;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || cuda_device < 0 || cuda_device >= n) return RM_E_CUDA;
+    if (cudaSetDevice(cuda_device) != cudaSuccess) return RM_E_CUDA;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, cuda_device) != cudaSuccess) return RM_E_CUDA;
+    if (prop.major != 10) return RM_E_CUDA;  // kernels are built for sm_100a only; no fallback
+    rm_ctx *c = new (std::nothrow) rm_ctx();
+    if (!c) return RM_E_INVALID_ARG;
+    c->device = cuda_device;
+    c->sm_count = prop.multiProcessorCount;
+    c->max_words = max_words;
+    bool ok = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) == cudaSuccess;
+    for (int i = 0; ok && i < kEventSlots; ++i) ok = cudaEventCreate(&c->events[i]) == cudaSuccess;
+    ok = ok && cudaEventCreateWithFlags(&c->upload_done, cudaEventDisableTiming) == cudaSuccess;
+    c->prog_cap = max_words;
+    ok = ok && cudaMalloc(&c->d_prog, c->prog_cap * sizeof(RmInsn)) == cudaSuccess;
+    ok = ok && cudaMallocHost(&c->h_prog, c->prog_cap * sizeof(RmInsn)) == cudaSuccess;
+    ok = ok && cudaMalloc(&c->d_counters, 4 * sizeof(unsigned long long)) == cudaSuccess;
+    ok = ok && cudaMemset(c->d_counters, 0, 4 * sizeof(unsigned long long)) == cudaSuccess;
+    ok = ok && wavefront_init(&c->wf, cuda_device) == cudaSuccess;
+    if (!ok) {
+        rm_destroy(c);
+        return RM_E_CUDA;
+    }
+    *out = c;
+    return RM_OK;
+}
+
+int rm_create(int cuda_device, rm_ctx **out) { return rm_create_ex(cuda_device, RM_DEFAULT_MAX_WORDS, out); }
+
+void rm_destroy(rm_ctx *c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    wavefront_destroy(&c->wf);
+    for (auto &e : c->events) if (e) cudaEventDestroy(e);
+    if (c->upload_done) cudaEventDestroy(c->upload_done);
+    if (c->d_prog) cudaFree(c->d_prog);
+    if (c->h_prog) cudaFreeHost(c->h_prog);
+    if (c->d_fb) cudaFree(c->d_fb);
+    if (c->d_codes) cudaFree(c->d_codes);
+    if (c->d_flush) cudaFree(c->d_flush);
+    if (c->d_counters) cudaFree(c->d_counters);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+int rm_set_limits(rm_ctx *c, const void *limits12) {
+    if (!c || !limits12) return RM_E_INVALID_ARG;
+    float f[2];
+    uint32_t it;
+    std::memcpy(f, limits12, 8);
+    std::memcpy(&it, (const char *)limits12 + 8, 4);
+    c->limits_f[0] = f[0]; c->limits_f[1] = f[1]; c->max_iter = it;
+    return RM_OK;
+}
+
+int rm_set_mode(rm_ctx *c, int mode) {
+    if (!c || (mode != RM_MODE_EXACT && mode != RM_MODE_FAST)) return RM_E_INVALID_ARG;
+    c->mode = mode;
+    return RM_OK;
+}
+int rm_get_mode(rm_ctx *c) { return c ? c->mode : RM_E_INVALID_ARG; }
+
+int rm_validate_program(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, uint32_t max_words) {
+    return decode_program(cmd_count, words, n_words, max_words, nullptr);
+}
+
+int rm_prepare_uniforms(rm_ctx *c, const void *uniforms144) {
+    if (!c || !uniforms144) return RM_E_INVALID_ARG;
+    std::memcpy(c->uniforms, uniforms144, RM_UNIFORMS_BYTES);
+    return RM_OK;
+}
+
+int rm_prepare(rm_ctx *c, const void *uniforms144, uint32_t cmd_count, const uint32_t *words, uint32_t n_words) {
+    if (!c || !uniforms144) return RM_E_INVALID_ARG;
+    Program p;
+    int rc = decode_program(cmd_count, words, n_words, c->max_words, &p);
+    if (rc != RM_OK) return fail(c, rc, rm_strerror(rc));
+    RM_CUDA(c, cudaSetDevice(c->device));
+    // the staging buffer may still be in flight from the previous prepare
+    RM_CUDA(c, cudaEventSynchronize(c->upload_done));
+    c->prog = std::move(p);
+    const size_t n = c->prog.insns.size();
+    if (n) {
+        std::memcpy(c->h_prog, c->prog.insns.data(), n * sizeof(RmInsn));
+        RM_CUDA(c, cudaMemcpyAsync(c->d_prog, c->h_prog, n * sizeof(RmInsn), cudaMemcpyHostToDevice, c->stream));
+    }
+    RM_CUDA(c, cudaEventRecord(c->upload_done, c->stream));
+    std::memcpy(c->uniforms, uniforms144, RM_UNIFORMS_BYTES);
+    c->prepared = true;
+    return RM_OK;
+}
+
+}  // extern "C"
+
+// paint / debug / measurement entry points live in rm_abi_paint.inc to keep files short
+#include "rm_abi_paint.inc"

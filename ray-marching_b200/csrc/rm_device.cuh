@@ -1,0 +1,264 @@
+// rm_device.cuh — device-side building blocks shared by all kernels of the render pass.
+// Arithmetic restates /root/reference/src/ray_marching/ray_marching.wgsl; each function cites
+// the shader lines it follows.  Two arithmetic policies:
+//   Arith<true>  (RM_MODE_EXACT): every add/mul/div/sqrt rounds once (no FMA contraction, IEEE
+//                sqrt.rn/div.rn) in the shader's evaluation order -> bit-identical to the oracle.
+//   Arith<false> (RM_MODE_FAST):  FMA contraction, MUFU sqrt/rsqrt/rcp.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "rm_program.h"
+
+namespace rm {
+
+// constants of the shader (SURVEY.md §5 "Config / flags")
+#define RM_NORMAL_EPS 0.0001f                   /* wgsl:136 */
+#define RM_LIGHT_X 2.0f                         /* wgsl:100 */
+#define RM_LIGHT_Y (-5.0f)
+#define RM_LIGHT_Z 3.0f
+#define RM_AMBIENT 0.02f                        /* wgsl:103 */
+#define RM_ALBEDO_R 0.4f                        /* wgsl:105 */
+#define RM_ALBEDO_G 0.7f
+#define RM_ALBEDO_B 0.1f
+#define RM_FLOOR_Y (-1.5f)                      /* wgsl:119 */
+
+// Per-launch frame block: the reference's two uniform buffers + the band being shaded.
+struct FrameParams {
+    float inv_proj[16];  // column-major, Uniforms @16   wgsl:26
+    float inv_view[16];  // column-major, Uniforms @80   wgsl:28
+    float extent[2];     // Uniforms @0                  wgsl:24
+    float min_dist, max_dist;  // RayMarchLimits         wgsl:78-82
+    uint32_t max_iter;
+    uint32_t W, H, row0, nrows;
+    uint32_t n_insn;     // decoded instruction count (0 = empty scene)
+};
+
+template <bool EX>
+struct Arith;
+
+template <>
+struct Arith<true> {
+    static __device__ __forceinline__ float add(float a, float b) { return __fadd_rn(a, b); }
+    static __device__ __forceinline__ float sub(float a, float b) { return __fsub_rn(a, b); }
+    static __device__ __forceinline__ float mul(float a, float b) { return __fmul_rn(a, b); }
+    static __device__ __forceinline__ float div(float a, float b) { return __fdiv_rn(a, b); }
+    static __device__ __forceinline__ float sqrt(float a) { return __fsqrt_rn(a); }
+    // a*b + c with two roundings
+    static __device__ __forceinline__ float mad(float a, float b, float c) { return __fadd_rn(__fmul_rn(a, b), c); }
+    // (x*x + y*y) + z*z
+    static __device__ __forceinline__ float dot3s(float x, float y, float z) {
+        return __fadd_rn(__fadd_rn(__fmul_rn(x, x), __fmul_rn(y, y)), __fmul_rn(z, z));
+    }
+    static __device__ __forceinline__ float length3(float x, float y, float z) { return __fsqrt_rn(dot3s(x, y, z)); }
+    static __device__ __forceinline__ void normalize3(float &x, float &y, float &z) {
+        float l = length3(x, y, z);
+        x = __fdiv_rn(x, l); y = __fdiv_rn(y, l); z = __fdiv_rn(z, l);
+    }
+};
+
+template <>
+struct Arith<false> {
+    static __device__ __forceinline__ float add(float a, float b) { return a + b; }
+    static __device__ __forceinline__ float sub(float a, float b) { return a - b; }
+    static __device__ __forceinline__ float mul(float a, float b) { return a * b; }
+    static __device__ __forceinline__ float div(float a, float b) { return __fdividef(a, b); }
+    static __device__ __forceinline__ float sqrt(float a) {
+        float r;
+        asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a));
+        return r;
+    }
+    static __device__ __forceinline__ float mad(float a, float b, float c) { return fmaf(a, b, c); }
+    static __device__ __forceinline__ float dot3s(float x, float y, float z) { return fmaf(z, z, fmaf(y, y, x * x)); }
+    static __device__ __forceinline__ float length3(float x, float y, float z) { return sqrt(dot3s(x, y, z)); }
+    static __device__ __forceinline__ void normalize3(float &x, float &y, float &z) {
+        float r = rsqrtf(dot3s(x, y, z));
+        x *= r; y *= r; z *= r;
+    }
+};
+
+// ---- primitives -----------------------------------------------------------------------------
+// wgsl:229-233  length(pos - center) - radius
+template <bool EX>
+__device__ __forceinline__ float sd_sphere(float px, float py, float pz, float cx, float cy, float cz, float r) {
+    using A = Arith<EX>;
+    float dx = A::sub(px, cx), dy = A::sub(py, cy), dz = A::sub(pz, cz);
+    return A::sub(A::length3(dx, dy, dz), r);
+}
+// wgsl:235-240  q = abs(pos-c) - r;  length(max(q,0)) + min(max(q.x,max(q.y,q.z)),0)
+template <bool EX>
+__device__ __forceinline__ float sd_box(float px, float py, float pz, float cx, float cy, float cz, float rx,
+                                        float ry, float rz) {
+    using A = Arith<EX>;
+    float qx = A::sub(fabsf(A::sub(px, cx)), rx);
+    float qy = A::sub(fabsf(A::sub(py, cy)), ry);
+    float qz = A::sub(fabsf(A::sub(pz, cz)), rz);
+    float len = A::length3(fmaxf(qx, 0.0f), fmaxf(qy, 0.0f), fmaxf(qz, 0.0f));
+    return A::add(len, fminf(fmaxf(qx, fmaxf(qy, qz)), 0.0f));
+}
+
+// ---- binary operators: a = left operand (deeper stack entry), b = right (top) ----------------
+// X2: h = max(k-|a-b|,0)/k ; min(a,b) - h*h*k*0.25
+template <bool EX>
+__device__ __forceinline__ float op_smooth(float a, float b, float k, float inv_k, float kq, bool k_pow2) {
+    using A = Arith<EX>;
+    float e = fmaxf(A::sub(k, fabsf(A::sub(a, b))), 0.0f);
+    float m = fminf(a, b);
+    if (EX) {
+        float h = k_pow2 ? __fmul_rn(e, inv_k) : __fdiv_rn(e, k);
+        return __fsub_rn(m, __fmul_rn(__fmul_rn(__fmul_rn(h, h), k), 0.25f));
+    } else {
+        float h = e * inv_k;
+        return fmaf(-(h * h), kq, m);
+    }
+}
+template <bool EX>
+__device__ __forceinline__ float combine(uint32_t cb, float a, float b, const float4 &q1, float kq, bool k_pow2) {
+    switch (cb) {
+        case CB_UNION: return fminf(a, b);   // wgsl:242-246
+        case CB_SUB: return fmaxf(a, -b);    // wgsl:248-252
+        case CB_INTER: return fmaxf(a, b);   // X1
+        default: return op_smooth<EX>(a, b, q1.z, q1.w, kq, k_pow2);
+    }
+}
+
+// ---- map_scene for one point: the decoded-program interpreter (wgsl:187-203) -----------------
+// prog: decoded instructions (shared or global memory), viewed as float4[3*n].
+template <bool EX>
+__device__ __forceinline__ float map_eval1(const float4 *__restrict__ prog, uint32_t n_insn, float max_dist,
+                                           float px, float py, float pz) {
+    if (n_insn == 0) return max_dist;  // wgsl:189-191
+    float acc = 0.0f;
+    float spill[RM_STACK_MAX - 1];
+    for (uint32_t i = 0; i < n_insn; ++i) {
+        const float4 q0 = prog[3 * i], q1 = prog[3 * i + 1], q2 = prog[3 * i + 2];
+        const uint32_t op = __float_as_uint(q2.y), slot = __float_as_uint(q2.z);
+        const bool k_pow2 = (__float_as_uint(q2.w) & FLAG_K_POW2) != 0;
+        const uint32_t src = op >> 3, cb = op & 7u;
+        float a, b;
+        if (src == SRC_SPHERE) {
+            b = sd_sphere<EX>(px, py, pz, q0.x, q0.y, q0.z, q0.w);
+            a = acc;
+        } else if (src == SRC_BOX) {
+            b = sd_box<EX>(px, py, pz, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y);
+            a = acc;
+        } else {
+            b = acc;
+            a = spill[slot];
+        }
+        if (cb == CB_FIRST) acc = b;
+        else if (cb == CB_PUSH) { spill[slot] = acc; acc = b; }
+        else acc = combine<EX>(cb, a, b, q1, q2.x, k_pow2);
+    }
+    return acc;
+}
+
+// ---- ray generation: fs_main wgsl:39-62 with the pixel->pt_screen closed form --
+__device__ __forceinline__ void mat4_mul(const float *m, float x, float y, float z, float w, float out[4]) {
+    // column sum accumulated left to right, one rounding per op (SURVEY.md §8(c).1 rule 3)
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+        float acc = __fmul_rn(m[r], x);
+        acc = __fadd_rn(acc, __fmul_rn(m[4 + r], y));
+        acc = __fadd_rn(acc, __fmul_rn(m[8 + r], z));
+        acc = __fadd_rn(acc, __fmul_rn(m[12 + r], w));
+        out[r] = acc;
+    }
+}
+// Ray generation is ~80 flops per sample (<0.5 % of the work) and feeds every threshold
+// decision downstream, so it is evaluated with exact roundings in both modes.
+__device__ __forceinline__ void gen_ray(const FrameParams &fp, uint32_t px, uint32_t py, uint32_t sample,
+                                        float ro[3], float rd[3]) {
+    const float sx = __fsub_rn(__fmul_rn(__fdiv_rn(__fadd_rn((float)px, 0.5f), (float)fp.W), 2.0f), 1.0f);
+    const float sy = __fsub_rn(1.0f, __fmul_rn(__fdiv_rn(__fadd_rn((float)py, 0.5f), (float)fp.H), 2.0f));
+    float ro4[4];
+    mat4_mul(fp.inv_view, 0.0f, 0.0f, 0.0f, 1.0f, ro4);  // wgsl:39-40
+    const uint32_t i = sample >> 2, j = sample & 3u;     // wgsl:44-45: i outer (x), j inner (y)
+    const float offx = __fsub_rn(__fdiv_rn(__fadd_rn((float)i, 0.5f), 4.0f), 0.5f);  // wgsl:52
+    const float offy = __fsub_rn(__fdiv_rn(__fadd_rn((float)j, 0.5f), 4.0f), 0.5f);
+    const float ax = __fmul_rn(__fdiv_rn(offx, fp.extent[0]), 2.0f);  // wgsl:53
+    const float ay = __fmul_rn(__fdiv_rn(offy, fp.extent[1]), 2.0f);
+    float pv[4], pw[4];
+    mat4_mul(fp.inv_proj, __fadd_rn(sx, ax), __fadd_rn(sy, ay), -1.0f, 1.0f, pv);  // wgsl:56-58
+    mat4_mul(fp.inv_view, pv[0], pv[1], pv[2], pv[3], pw);                          // wgsl:59
+    const float dx = __fsub_rn(pw[0], ro4[0]), dy = __fsub_rn(pw[1], ro4[1]);
+    const float dz = __fsub_rn(pw[2], ro4[2]), dw = __fsub_rn(pw[3], ro4[3]);
+    const float len = __fsqrt_rn(__fadd_rn(
+        __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz)), __fmul_rn(dw, dw)));
+    rd[0] = __fdiv_rn(dx, len); rd[1] = __fdiv_rn(dy, len); rd[2] = __fdiv_rn(dz, len);  // wgsl:62
+    ro[0] = ro4[0]; ro[1] = ro4[1]; ro[2] = ro4[2];
+}
+
+// ---- hit shading wgsl:100-105 given the un-normalised tetrahedron sum n (wgsl:138-143) --------
+template <bool EX>
+__device__ __forceinline__ float shade_diffuse(float nx, float ny, float nz, float px, float py, float pz) {
+    using A = Arith<EX>;
+    A::normalize3(nx, ny, nz);
+    float lx = A::sub(px, RM_LIGHT_X), ly = A::sub(py, RM_LIGHT_Y), lz = A::sub(pz, RM_LIGHT_Z);
+    A::normalize3(lx, ly, lz);
+    float d = A::add(A::add(A::mul(nx, lx), A::mul(ny, ly)), A::mul(nz, lz));
+    return fmaxf(RM_AMBIENT, d);
+}
+
+// ---- floor / sky wgsl:117-130.  Returns class; colour via c[3]; t = floor_dist. ---------------
+__device__ __forceinline__ int shade_miss(const float ro[3], const float rd[3], float c[3], float &t) {
+    const float fd = __fdiv_rn(__fsub_rn(RM_FLOOR_Y, ro[1]), rd[1]);  // wgsl:120
+    t = fd;
+    if (fd > 0.0f) {
+        const float fx = __fadd_rn(ro[0], __fmul_rn(rd[0], fd)), fz = __fadd_rn(ro[2], __fmul_rn(rd[2], fd));
+        // round = RNE (rintf); f32->i32 saturating, NaN -> 0: cvt.rni.s32.f32 does both (Q6/Q7)
+        const int ix = __float2int_rn(__fadd_rn(fx, 0.5f)), iz = __float2int_rn(__fadd_rn(fz, 0.5f));
+        const float col = (float)((ix ^ iz) & 1);
+        c[0] = __fadd_rn(0.1f, __fmul_rn(0.2f, col));
+        c[1] = c[0];
+        c[2] = __fadd_rn(0.2f, __fmul_rn(0.2f, col));
+        return 1;
+    }
+    c[0] = c[1] = c[2] = 0.0f;
+    return 0;
+}
+
+// unorm8 = floor(clamp(v,0,1)*255 + 0.5)
+__device__ __forceinline__ uint32_t unorm8(float v) {
+    float c = fminf(fmaxf(v, 0.0f), 1.0f);  // NaN -> 0 via fmaxf
+    return (uint32_t)floorf(__fadd_rn(__fmul_rn(c, 255.0f), 0.5f));
+}
+
+// Per-sample result code written by the marching kernels and consumed by the resolve:
+//   v >= 0   object hit, v = diffuse intensity (>= 0.02)      wgsl:103-105
+//   v == -1  floor, dark cell;  v == -2  floor, light cell   wgsl:124-127
+//   v == -3  sky                                              wgsl:130
+#define RM_CODE_FLOOR_DARK (-1.0f)
+#define RM_CODE_FLOOR_LIGHT (-2.0f)
+#define RM_CODE_SKY (-3.0f)
+
+// Colour of a sample code, gamma'd (wgsl:68) — always with exact roundings (negligible cost).
+__device__ __forceinline__ void code_to_gamma(float code, float g[3]) {
+    if (code >= 0.0f) {
+        g[0] = __fsqrt_rn(__fmul_rn(RM_ALBEDO_R, code));
+        g[1] = __fsqrt_rn(__fmul_rn(RM_ALBEDO_G, code));
+        g[2] = __fsqrt_rn(__fmul_rn(RM_ALBEDO_B, code));
+    } else if (code == RM_CODE_SKY) {
+        g[0] = g[1] = g[2] = 0.0f;
+    } else {
+        const float col = (code == RM_CODE_FLOOR_LIGHT) ? 1.0f : 0.0f;
+        const float rg = __fadd_rn(0.1f, __fmul_rn(0.2f, col)), b = __fadd_rn(0.2f, __fmul_rn(0.2f, col));
+        g[0] = g[1] = __fsqrt_rn(rg);
+        g[2] = __fsqrt_rn(b);
+    }
+}
+
+// In-order 16-sample mean (wgsl:44-45,68-75) and RGBA8 pack.
+__device__ __forceinline__ uint32_t resolve_pixel(const float *codes16) {
+    float sr = 0.0f, sg = 0.0f, sb = 0.0f;
+#pragma unroll
+    for (int s = 0; s < 16; ++s) {
+        float g[3];
+        code_to_gamma(codes16[s], g);
+        sr = __fadd_rn(sr, g[0]); sg = __fadd_rn(sg, g[1]); sb = __fadd_rn(sb, g[2]);
+    }
+    return unorm8(__fdiv_rn(sr, 16.0f)) | (unorm8(__fdiv_rn(sg, 16.0f)) << 8) |
+           (unorm8(__fdiv_rn(sb, 16.0f)) << 16) | 0xff000000u;
+}
+
+}  // namespace rm

@@ -1,0 +1,186 @@
+// rm_kernels.cu — the straightforward kernels: one thread per sample ray + in-order resolve.
+// They are the verification path behind rm_paint_debug / rm_map (AOVs, counters) and the
+// bit-exactness anchor for the persistent wavefront kernel in rm_wavefront.cu.
+#include "rm_kernels.h"
+
+namespace rm {
+
+namespace {
+
+constexpr int kSimpleThreads = 128;
+
+// March one ray exactly as ray_march (wgsl:87-131).  Returns the sample code (see rm_kernels.h).
+template <bool EX>
+__device__ __forceinline__ float march_one(const FrameParams &fp, const float4 *prog, const float ro[3],
+                                           const float rd[3], int &cls, float &t_out, uint32_t &n_step) {
+    using A = Arith<EX>;
+    float dist = 0.0f;  // wgsl:88
+    n_step = 0;
+    for (uint32_t it = 0; it < fp.max_iter; ++it) {  // wgsl:90
+        const float px = A::mad(rd[0], dist, ro[0]), py = A::mad(rd[1], dist, ro[1]),
+                    pz = A::mad(rd[2], dist, ro[2]);  // wgsl:91
+        const float s = map_eval1<EX>(prog, fp.n_insn, fp.max_dist, px, py, pz);  // wgsl:94
+        ++n_step;
+        if (s < fp.min_dist) {  // wgsl:97
+            // calculate_normal wgsl:135-144: taps (+,-,-) (-,-,+) (-,+,-) (+,+,+)
+            const float e = RM_NORMAL_EPS;
+            const float m0 = map_eval1<EX>(prog, fp.n_insn, fp.max_dist, __fadd_rn(px, e), __fadd_rn(py, -e), __fadd_rn(pz, -e));
+            const float m1 = map_eval1<EX>(prog, fp.n_insn, fp.max_dist, __fadd_rn(px, -e), __fadd_rn(py, -e), __fadd_rn(pz, e));
+            const float m2 = map_eval1<EX>(prog, fp.n_insn, fp.max_dist, __fadd_rn(px, -e), __fadd_rn(py, e), __fadd_rn(pz, -e));
+            const float m3 = map_eval1<EX>(prog, fp.n_insn, fp.max_dist, __fadd_rn(px, e), __fadd_rn(py, e), __fadd_rn(pz, e));
+            const float nx = A::add(A::add(A::add(m0, -m1), -m2), m3);
+            const float ny = A::add(A::add(A::add(-m0, -m1), m2), m3);
+            const float nz = A::add(A::add(A::add(-m0, m1), -m2), m3);
+            cls = 2;
+            t_out = dist;
+            return shade_diffuse<EX>(nx, ny, nz, px, py, pz);
+        }
+        if (s > fp.max_dist) break;  // wgsl:109-111
+        dist = A::add(dist, s);      // wgsl:114
+    }
+    float c[3];
+    cls = shade_miss(ro, rd, c, t_out);
+    if (cls == 0) return RM_CODE_SKY;
+    return c[0] > 0.2f ? RM_CODE_FLOOR_LIGHT : RM_CODE_FLOOR_DARK;
+}
+
+template <bool EX>
+__global__ void __launch_bounds__(kSimpleThreads)
+k_samples_simple(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ prog_g, float *__restrict__ codes,
+                 DebugOut dbg) {
+    extern __shared__ float4 s_prog[];
+    const uint32_t nq = fp.n_insn * 3;
+    for (uint32_t i = threadIdx.x; i < nq; i += blockDim.x) s_prog[i] = reinterpret_cast<const float4 *>(prog_g)[i];
+    __syncthreads();
+    const unsigned long long total = (unsigned long long)fp.nrows * fp.W * 16ull;
+    const unsigned long long idx = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t n_step = 0;
+    int cls = -1;
+    if (idx < total) {
+        const unsigned long long pix = idx >> 4;
+        const uint32_t sample = (uint32_t)(idx & 15u);
+        const uint32_t px = (uint32_t)(pix % fp.W), py = fp.row0 + (uint32_t)(pix / fp.W);
+        float ro[3], rd[3], t;
+        gen_ray(fp, px, py, sample, ro, rd);
+        const float code = march_one<EX>(fp, s_prog, ro, rd, cls, t, n_step);
+        codes[idx] = code;
+        if (dbg.cls) dbg.cls[idx] = (uint8_t)cls;
+        if (dbg.t) dbg.t[idx] = t;
+    }
+    if (dbg.counters) {
+        const unsigned m = 0xffffffffu;
+        uint32_t s = __reduce_add_sync(m, n_step);
+        uint32_t h = __popc(__ballot_sync(m, cls == 2));
+        uint32_t f = __popc(__ballot_sync(m, cls == 1));
+        uint32_t n = __popc(__ballot_sync(m, cls >= 0));
+        if ((threadIdx.x & 31) == 0) {
+            atomicAdd(&dbg.counters[0], (unsigned long long)s);
+            atomicAdd(&dbg.counters[1], (unsigned long long)h);
+            atomicAdd(&dbg.counters[2], (unsigned long long)f);
+            atomicAdd(&dbg.counters[3], (unsigned long long)n);
+        }
+    }
+}
+
+}  // namespace
+
+namespace {
+
+__global__ void __launch_bounds__(256)
+k_resolve(const __grid_constant__ FrameParams fp, const float *__restrict__ codes, uint8_t *__restrict__ dst, size_t pitch) {
+    const unsigned long long npix = (unsigned long long)fp.nrows * fp.W;
+    const unsigned long long pix = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (pix >= npix) return;
+    float c[16];
+    const float4 *p = reinterpret_cast<const float4 *>(codes + pix * 16);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const float4 v = p[q];
+        c[4 * q] = v.x; c[4 * q + 1] = v.y; c[4 * q + 2] = v.z; c[4 * q + 3] = v.w;
+    }
+    const uint32_t x = (uint32_t)(pix % fp.W), y = (uint32_t)(pix / fp.W);
+    *reinterpret_cast<uint32_t *>(dst + (size_t)y * pitch + (size_t)x * 4) = resolve_pixel(c);
+}
+
+template <bool EX>
+__global__ void __launch_bounds__(kSimpleThreads)
+k_map(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ prog_g, const float *__restrict__ pts,
+      unsigned long long n, float *__restrict__ out) {
+    extern __shared__ float4 s_prog[];
+    const uint32_t nq = fp.n_insn * 3;
+    for (uint32_t i = threadIdx.x; i < nq; i += blockDim.x) s_prog[i] = reinterpret_cast<const float4 *>(prog_g)[i];
+    __syncthreads();
+    const unsigned long long idx = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx < n) out[idx] = map_eval1<EX>(s_prog, fp.n_insn, fp.max_dist, pts[3 * idx], pts[3 * idx + 1], pts[3 * idx + 2]);
+}
+
+__global__ void __launch_bounds__(256) k_ffma_probe(int iters, float *sink) {
+    float a0 = threadIdx.x * 1e-3f, a1 = a0 + 1.f, a2 = a0 + 2.f, a3 = a0 + 3.f, a4 = a0 + 4.f, a5 = a0 + 5.f,
+          a6 = a0 + 6.f, a7 = a0 + 7.f;
+    const float m = 0.999f, c = 1e-3f;
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int u = 0; u < 16; ++u) {
+            a0 = fmaf(a0, m, c); a1 = fmaf(a1, m, c); a2 = fmaf(a2, m, c); a3 = fmaf(a3, m, c);
+            a4 = fmaf(a4, m, c); a5 = fmaf(a5, m, c); a6 = fmaf(a6, m, c); a7 = fmaf(a7, m, c);
+        }
+    }
+    const float s = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
+    if (s == 123.456f) sink[0] = s;  // keep the chains alive without a store in practice
+}
+
+template <typename K>
+cudaError_t set_smem(K kernel, size_t bytes) {
+    if (bytes > 48 * 1024) return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    return cudaSuccess;
+}
+
+}  // namespace
+
+cudaError_t launch_samples_simple(bool exact, const FrameParams &fp, const RmInsn *prog_dev, float *codes_dev,
+                                  DebugOut dbg, cudaStream_t st) {
+    const unsigned long long total = (unsigned long long)fp.nrows * fp.W * 16ull;
+    if (total == 0) return cudaSuccess;
+    const unsigned long long blocks = (total + kSimpleThreads - 1) / kSimpleThreads;
+    if (blocks > 0x7fffffffull) return cudaErrorInvalidValue;
+    const size_t smem = (size_t)fp.n_insn * sizeof(RmInsn);
+    cudaError_t e;
+    if (exact) {
+        if ((e = set_smem(k_samples_simple<true>, smem)) != cudaSuccess) return e;
+        k_samples_simple<true><<<(unsigned)blocks, kSimpleThreads, smem, st>>>(fp, prog_dev, codes_dev, dbg);
+    } else {
+        if ((e = set_smem(k_samples_simple<false>, smem)) != cudaSuccess) return e;
+        k_samples_simple<false><<<(unsigned)blocks, kSimpleThreads, smem, st>>>(fp, prog_dev, codes_dev, dbg);
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_resolve(const FrameParams &fp, const float *codes_dev, uint8_t *dst, size_t pitch, cudaStream_t st) {
+    const unsigned long long npix = (unsigned long long)fp.nrows * fp.W;
+    if (npix == 0) return cudaSuccess;
+    k_resolve<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(fp, codes_dev, dst, pitch);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_map(bool exact, const FrameParams &fp, const RmInsn *prog_dev, const float *pts_dev,
+                       unsigned long long n, float *out_dev, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    const size_t smem = (size_t)fp.n_insn * sizeof(RmInsn);
+    const unsigned blocks = (unsigned)((n + kSimpleThreads - 1) / kSimpleThreads);
+    cudaError_t e;
+    if (exact) {
+        if ((e = set_smem(k_map<true>, smem)) != cudaSuccess) return e;
+        k_map<true><<<blocks, kSimpleThreads, smem, st>>>(fp, prog_dev, pts_dev, n, out_dev);
+    } else {
+        if ((e = set_smem(k_map<false>, smem)) != cudaSuccess) return e;
+        k_map<false><<<blocks, kSimpleThreads, smem, st>>>(fp, prog_dev, pts_dev, n, out_dev);
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_ffma_probe(int blocks, int threads, int iters, float *sink_dev, cudaStream_t st) {
+    k_ffma_probe<<<blocks, threads, 0, st>>>(iters, sink_dev);
+    return cudaGetLastError();
+}
+
+}  // namespace rm

@@ -1,0 +1,69 @@
+// rm_program.h — host-side validation and pre-decoding of the reference's postfix CSG command
+// stream (wire format: /root/reference/src/ray_marching/csg/builder.rs:26-62; interpreter it
+// replaces: ray_marching.wgsl:146-252) into the fixed-width instruction stream the kernels run.
+//
+// The program is identical for every ray, so everything that the WGSL interpreter resolves at
+// run time per thread — cursor arithmetic, opcode decode, value-stack indices — is resolved here
+// once per rm_prepare:
+//   * the top of the value stack lives in a register (the accumulator); deeper entries live in
+//     statically numbered spill slots;
+//   * "primitive immediately followed by a binary operator" is fused into one instruction
+//     acc = op(acc, prim(p)), which is the whole program for left-deep chains;
+//   * per-instruction constants that are exact (k*0.25, 1/k when k is a power of two) are
+//     precomputed.  Nothing here changes evaluation order or rounding.
+#pragma once
+#include <stdint.h>
+
+#include <vector>
+
+#ifndef RM_STACK_MAX
+#define RM_STACK_MAX 32u  // value_stack_max_size, ray_marching.wgsl:173 (same value as rm_b200.h)
+#endif
+
+namespace rm {
+
+// combine modes (low 3 bits of RmInsn::op)
+enum : uint32_t {
+    CB_FIRST = 0,   // acc = v                       (stack was empty)
+    CB_PUSH = 1,    // spill[slot] = acc; acc = v
+    CB_UNION = 2,   // acc = min(a, b)               wgsl:242-246
+    CB_SUB = 3,     // acc = max(a, -b)              wgsl:248-252
+    CB_INTER = 4,   // acc = max(a, b)               X1
+    CB_SMOOTH = 5,  // acc = smooth-min(a, b; k)     X2
+};
+// operand source (bits 3..4 of RmInsn::op)
+enum : uint32_t {
+    SRC_POP = 0,     // b = acc, a = spill[slot]     (binary op whose right operand is a subtree)
+    SRC_SPHERE = 1,  // b = sphere(p), a = acc       wgsl:229-233
+    SRC_BOX = 2,     // b = box(p),    a = acc       wgsl:235-240
+};
+enum : uint32_t { FLAG_K_POW2 = 1u };  // 1/k is exact: multiply instead of divide in exact mode
+
+// One decoded instruction = 3 x 16 bytes (three broadcast LDS.128).
+struct alignas(16) RmInsn {
+    float cx, cy, cz, r0;      // centre, sphere radius / box radius x
+    float r1, r2, k, inv_k;    // box radius y,z; smooth-union k and 1/k
+    float kq;                  // k * 0.25 (exact scaling)
+    uint32_t op;               // src << 3 | combine
+    uint32_t slot;             // spill slot read (SRC_POP) or written (CB_PUSH)
+    uint32_t flags;
+};
+static_assert(sizeof(RmInsn) == 48, "RmInsn must be 48 bytes");
+
+struct Program {
+    std::vector<RmInsn> insns;
+    uint32_t cmd_count = 0;
+    uint32_t max_depth = 0;   // value-stack depth of the original program (<= 32)
+    uint32_t n_spill = 0;     // spill slots used (= max_depth - 1, or 0)
+    uint32_t n_sphere = 0, n_box = 0, n_union = 0, n_sub = 0, n_inter = 0, n_smooth = 0;
+    // algorithmic flops of one map_scene evaluation (SURVEY.md §8(a) FLOP table)
+    uint32_t flops_per_eval() const {
+        return 10 * n_sphere + 22 * n_box + n_union + 2 * n_sub + n_inter + 10 * n_smooth;
+    }
+};
+
+// Returns an RM_* code (rm_b200.h).  `out` may be null for validation only.
+int decode_program(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, uint32_t max_words,
+                   Program *out);
+
+}  // namespace rm

@@ -1,0 +1,396 @@
+// rm_wavefront.cu — the production kernel of the render pass: persistent warps over 8x4 pixel
+// tiles, each lane owning R ray slots that run a per-ray state machine
+//     MARCH -> (hit) TAP0 -> TAP1 -> TAP2 -> TAP3 -> shade -> done        (wgsl:87-144)
+// so that the only expensive thing — one map_scene evaluation of the decoded program per slot —
+// is executed by all 32*R slots in lock-step, with warp-uniform control flow through the
+// interpreter.  Finished slots are refilled from the warp's tile pool by ballot/popc ranking
+// (compaction of live rays); a tile's 512 sample results are parked in shared memory and resolved
+// in the shader's sample order, so the image is bit-identical to the one-thread-per-sample path.
+// The framebuffer tile is written with 128-bit stores.
+#include "rm_wavefront.h"
+
+#include <cstdlib>
+
+namespace rm {
+
+namespace {
+
+constexpr int WF_WARPS = 4;      // warps per CTA
+constexpr int WF_K = 4;          // tiles in flight per warp
+constexpr int TILE_W = 8, TILE_H = 4;
+constexpr int TILE_RAYS = TILE_W * TILE_H * 16;  // 512
+constexpr unsigned FULL = 0xffffffffu;
+constexpr int RING = 1024;
+
+constexpr uint32_t M_Q = 0x1ffu;          // sample slot in tile: sample*32 + pixel
+constexpr uint32_t M_BUF_SHIFT = 9;       // 2 bits
+constexpr uint32_t M_STATE_SHIFT = 11;    // 3 bits: 0 MARCH, 1..4 TAP0..TAP3
+constexpr uint32_t M_LIVE = 1u << 14;
+
+struct WarpShared {
+    float codes[WF_K][TILE_RAYS];
+    int remaining[WF_K];
+    int tile[WF_K];  // tile id, or -1 when the buffer is free
+};
+
+// map_scene for R points at once: one instruction fetch/decode feeds R evaluations.
+template <bool EX, int R>
+__device__ __forceinline__ void map_evalR(const float4 *__restrict__ prog, uint32_t n_insn, float max_dist,
+                                          const float (&px)[R], const float (&py)[R], const float (&pz)[R],
+                                          float (&acc)[R], float (*spill)[R]) {
+    if (n_insn == 0) {  // wgsl:189-191
+#pragma unroll
+        for (int r = 0; r < R; ++r) acc[r] = max_dist;
+        return;
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) acc[r] = 0.0f;
+#pragma unroll 1
+    for (uint32_t i = 0; i < n_insn; ++i) {
+        const float4 q0 = prog[3 * i], q1 = prog[3 * i + 1], q2 = prog[3 * i + 2];
+        const uint32_t op = __float_as_uint(q2.y);
+        const uint32_t src = op >> 3, cb = op & 7u;
+        float a[R], b[R];
+        if (src == SRC_SPHERE) {
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                b[r] = sd_sphere<EX>(px[r], py[r], pz[r], q0.x, q0.y, q0.z, q0.w);
+                a[r] = acc[r];
+            }
+        } else if (src == SRC_BOX) {
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                b[r] = sd_box<EX>(px[r], py[r], pz[r], q0.x, q0.y, q0.z, q0.w, q1.x, q1.y);
+                a[r] = acc[r];
+            }
+        } else {
+            const uint32_t slot = __float_as_uint(q2.z);
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                b[r] = acc[r];
+                a[r] = spill[slot][r];
+            }
+        }
+        switch (cb) {
+            case CB_FIRST:
+#pragma unroll
+                for (int r = 0; r < R; ++r) acc[r] = b[r];
+                break;
+            case CB_PUSH: {
+                const uint32_t slot = __float_as_uint(q2.z);
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    spill[slot][r] = acc[r];
+                    acc[r] = b[r];
+                }
+                break;
+            }
+            case CB_UNION:
+#pragma unroll
+                for (int r = 0; r < R; ++r) acc[r] = fminf(a[r], b[r]);
+                break;
+            case CB_SUB:
+#pragma unroll
+                for (int r = 0; r < R; ++r) acc[r] = fmaxf(a[r], -b[r]);
+                break;
+            case CB_INTER:
+#pragma unroll
+                for (int r = 0; r < R; ++r) acc[r] = fmaxf(a[r], b[r]);
+                break;
+            default: {
+                const bool k_pow2 = (__float_as_uint(q2.w) & FLAG_K_POW2) != 0;
+#pragma unroll
+                for (int r = 0; r < R; ++r) acc[r] = op_smooth<EX>(a[r], b[r], q1.z, q1.w, q2.x, k_pow2);
+                break;
+            }
+        }
+    }
+}
+
+template <bool EX, int R, bool COUNT>
+__global__ void __launch_bounds__(WF_WARPS * 32)
+k_wavefront(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ prog_g, uint8_t *__restrict__ dst,
+            size_t pitch, unsigned int *__restrict__ tile_counter, unsigned long long *__restrict__ counters) {
+    using A = Arith<EX>;
+    extern __shared__ float4 smem_f4[];
+    float4 *s_prog = smem_f4;
+    const uint32_t nq = fp.n_insn * 3;
+    WarpShared *s_warps = reinterpret_cast<WarpShared *>(smem_f4 + nq);
+    for (uint32_t i = threadIdx.x; i < nq; i += blockDim.x) s_prog[i] = reinterpret_cast<const float4 *>(prog_g)[i];
+    const int lane = threadIdx.x & 31;
+    WarpShared &ws = s_warps[threadIdx.x >> 5];
+    if (lane < WF_K) {
+        ws.remaining[lane] = 0;
+        ws.tile[lane] = -1;
+    }
+    __syncthreads();
+
+    const uint32_t tiles_x = (fp.W + TILE_W - 1) / TILE_W;
+    const uint32_t tiles_y = (fp.nrows + TILE_H - 1) / TILE_H;
+    const uint32_t n_tiles = tiles_x * tiles_y;
+    const unsigned lt_mask = (1u << lane) - 1u;
+
+    // ray origin = inv_view * (0,0,0,1)  (wgsl:39-40) — identical for every ray of the frame
+    float ro[3];
+    {
+        float ro4[4];
+        mat4_mul(fp.inv_view, 0.0f, 0.0f, 0.0f, 1.0f, ro4);
+        ro[0] = ro4[0]; ro[1] = ro4[1]; ro[2] = ro4[2];
+    }
+
+    float rdx[R], rdy[R], rdz[R], dist[R], m0[R], m1[R], m2[R];
+    uint32_t meta[R], iter[R];
+    float spill[RM_STACK_MAX - 1][R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) { meta[r] = 0; iter[r] = 0; dist[r] = 0.f; rdx[r] = rdy[r] = rdz[r] = 0.f; m0[r] = m1[r] = m2[r] = 0.f; }
+
+    int cur_buf = 0, pool_next = TILE_RAYS;
+    uint32_t cur_tile = 0;
+    bool exhausted = false;
+    uint32_t c_step = 0, c_hit = 0, c_floor = 0, c_sample = 0;
+
+    // finishes a ray as a miss (floor / sky, wgsl:117-130)
+    auto miss_code = [&](float dx, float dy, float dz) -> float {
+        const float rd[3] = {dx, dy, dz};
+        float c[3], t;
+        const int cls = shade_miss(ro, rd, c, t);
+        if (COUNT && cls == 1) ++c_floor;
+        if (cls == 0) return RM_CODE_SKY;
+        return c[0] > 0.2f ? RM_CODE_FLOOR_LIGHT : RM_CODE_FLOOR_DARK;
+    };
+
+    for (;;) {
+        // ---------------- refill empty slots from the tile pool (ballot compaction) ----------------
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            bool empty = !(meta[r] & M_LIVE);
+            unsigned em = __ballot_sync(FULL, empty);
+            while (em) {
+                if (pool_next >= TILE_RAYS) {
+                    if (exhausted) break;
+                    int b = -1;
+#pragma unroll
+                    for (int k = WF_K - 1; k >= 0; --k) if (ws.tile[k] < 0) b = k;
+                    if (b < 0) break;  // every tile buffer still has rays in flight
+                    unsigned t = 0;
+                    if (lane == 0) t = atomicAdd(tile_counter, 1u);
+                    t = __shfl_sync(FULL, t, 0);
+                    if (t >= n_tiles) { exhausted = true; break; }
+                    cur_buf = b; cur_tile = t; pool_next = 0;
+                    if (lane == 0) { ws.tile[b] = (int)t; ws.remaining[b] = TILE_RAYS; }
+                    __syncwarp();
+                }
+                const int rank = __popc(em & lt_mask);
+                const int take = min(__popc(em), TILE_RAYS - pool_next);
+                if (empty && rank < take) {
+                    const uint32_t q = (uint32_t)(pool_next + rank);
+                    const uint32_t pixel = q & 31u, sample = q >> 5;
+                    const uint32_t tx = cur_tile % tiles_x, ty = cur_tile / tiles_x;
+                    const uint32_t px = tx * TILE_W + (pixel & 7u), ry = ty * TILE_H + (pixel >> 3);
+                    empty = false;
+                    if (px < fp.W && ry < fp.nrows) {
+                        float o[3], d[3];
+                        gen_ray(fp, px, fp.row0 + ry, sample, o, d);
+                        if (COUNT) ++c_sample;
+                        if (fp.max_iter > 0) {
+                            rdx[r] = d[0]; rdy[r] = d[1]; rdz[r] = d[2];
+                            dist[r] = 0.0f; iter[r] = 0;
+                            meta[r] = q | ((uint32_t)cur_buf << M_BUF_SHIFT) | M_LIVE;
+                        } else {
+                            ws.codes[cur_buf][q] = miss_code(d[0], d[1], d[2]);
+                            atomicSub(&ws.remaining[cur_buf], 1);
+                        }
+                    } else {  // pixel outside the band: nothing to shade
+                        ws.codes[cur_buf][q] = RM_CODE_SKY;
+                        atomicSub(&ws.remaining[cur_buf], 1);
+                    }
+                }
+                pool_next += take;
+                em = __ballot_sync(FULL, empty && !(meta[r] & M_LIVE));
+                // lanes that spawned a non-live ray (outside band / max_iter 0) keep empty=false for
+                // this round and are picked up again on the next pass
+            }
+        }
+        // ---------------- termination ----------------
+        bool live_any = false;
+#pragma unroll
+        for (int r = 0; r < R; ++r) live_any |= (meta[r] & M_LIVE) != 0;
+        if (!__any_sync(FULL, live_any)) {
+            __syncwarp();
+            bool pending = false;
+#pragma unroll
+            for (int k = 0; k < WF_K; ++k) pending |= (ws.tile[k] >= 0);
+            if (!pending && exhausted) break;
+        }
+
+        // ---------------- evaluation points ----------------
+        float px[R], py[R], pz[R], s[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const uint32_t st = (meta[r] >> M_STATE_SHIFT) & 7u;
+            const float bx = A::mad(rdx[r], dist[r], ro[0]), by = A::mad(rdy[r], dist[r], ro[1]),
+                        bz = A::mad(rdz[r], dist[r], ro[2]);  // wgsl:91
+            // tetrahedron taps wgsl:138-142: (+,-,-) (-,-,+) (-,+,-) (+,+,+)
+            const float e = RM_NORMAL_EPS;
+            const float ox = (st == 1 || st == 4) ? e : -e;
+            const float oy = (st >= 3) ? e : -e;
+            const float oz = (st == 2 || st == 4) ? e : -e;
+            px[r] = st == 0 ? bx : __fadd_rn(bx, ox);
+            py[r] = st == 0 ? by : __fadd_rn(by, oy);
+            pz[r] = st == 0 ? bz : __fadd_rn(bz, oz);
+        }
+        map_evalR<EX, R>(s_prog, fp.n_insn, fp.max_dist, px, py, pz, s, spill);
+
+        // ---------------- per-slot state update ----------------
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            if (!(meta[r] & M_LIVE)) continue;
+            const uint32_t st = (meta[r] >> M_STATE_SHIFT) & 7u;
+            float code = 0.0f;
+            bool done = false;
+            if (st == 0) {
+                if (COUNT) ++c_step;
+                if (s[r] < fp.min_dist) {  // wgsl:97 -> start the normal taps
+                    meta[r] += 1u << M_STATE_SHIFT;
+                } else if (s[r] > fp.max_dist) {  // wgsl:109-111
+                    code = miss_code(rdx[r], rdy[r], rdz[r]);
+                    done = true;
+                } else {
+                    dist[r] = A::add(dist[r], s[r]);  // wgsl:114
+                    if (++iter[r] >= fp.max_iter) {
+                        code = miss_code(rdx[r], rdy[r], rdz[r]);
+                        done = true;
+                    }
+                }
+            } else if (st < 4) {
+                if (st == 1) m0[r] = s[r];
+                else if (st == 2) m1[r] = s[r];
+                else m2[r] = s[r];
+                meta[r] += 1u << M_STATE_SHIFT;
+            } else {
+                const float a0 = m0[r], a1 = m1[r], a2 = m2[r], a3 = s[r];
+                const float nx = A::add(A::add(A::add(a0, -a1), -a2), a3);
+                const float ny = A::add(A::add(A::add(-a0, -a1), a2), a3);
+                const float nz = A::add(A::add(A::add(-a0, a1), -a2), a3);
+                const float hx = A::mad(rdx[r], dist[r], ro[0]), hy = A::mad(rdy[r], dist[r], ro[1]),
+                            hz = A::mad(rdz[r], dist[r], ro[2]);
+                code = shade_diffuse<EX>(nx, ny, nz, hx, hy, hz);  // wgsl:98-105
+                if (COUNT) ++c_hit;
+                done = true;
+            }
+            if (done) {
+                const uint32_t b = (meta[r] >> M_BUF_SHIFT) & 3u;
+                ws.codes[b][meta[r] & M_Q] = code;
+                atomicSub(&ws.remaining[b], 1);
+                meta[r] = 0;
+            }
+        }
+        __syncwarp();
+
+        // ---------------- resolve tiles whose 512 samples are all in ----------------
+#pragma unroll
+        for (int k = 0; k < WF_K; ++k) {
+            const int tile = ws.tile[k];
+            if (tile < 0 || ws.remaining[k] != 0) continue;  // warp-uniform
+            float c16[16];
+#pragma unroll
+            for (int sidx = 0; sidx < 16; ++sidx) c16[sidx] = ws.codes[k][sidx * 32 + lane];
+            const uint32_t pix = resolve_pixel(c16);  // wgsl:44-45,68-75 in sample order
+            const uint32_t tx = (uint32_t)tile % tiles_x, ty = (uint32_t)tile / tiles_x;
+            const uint32_t x0 = tx * TILE_W, y0 = ty * TILE_H;
+            if (x0 + TILE_W <= fp.W && y0 + TILE_H <= fp.nrows) {
+                // lanes 0..7 each gather four pixels of one half-row and issue one 128-bit store
+                const int row = (lane >> 1) & 3, half = lane & 1;
+                const int srcl = row * 8 + half * 4;
+                uint4 v;
+                v.x = __shfl_sync(FULL, pix, srcl);
+                v.y = __shfl_sync(FULL, pix, srcl + 1);
+                v.z = __shfl_sync(FULL, pix, srcl + 2);
+                v.w = __shfl_sync(FULL, pix, srcl + 3);
+                if (lane < 8)
+                    *reinterpret_cast<uint4 *>(dst + (size_t)(y0 + row) * pitch + (size_t)(x0 + half * 4) * 4) = v;
+            } else {
+                const uint32_t x = x0 + (lane & 7), y = y0 + (lane >> 3);
+                if (x < fp.W && y < fp.nrows) *reinterpret_cast<uint32_t *>(dst + (size_t)y * pitch + (size_t)x * 4) = pix;
+            }
+            __syncwarp();
+            if (lane == 0) ws.tile[k] = -1;
+        }
+        __syncwarp();
+    }
+
+    if (COUNT) {
+        const uint32_t a = __reduce_add_sync(FULL, c_step), b = __reduce_add_sync(FULL, c_hit),
+                       c = __reduce_add_sync(FULL, c_floor), d = __reduce_add_sync(FULL, c_sample);
+        if (lane == 0) {
+            atomicAdd(&counters[0], (unsigned long long)a);
+            atomicAdd(&counters[1], (unsigned long long)b);
+            atomicAdd(&counters[2], (unsigned long long)c);
+            atomicAdd(&counters[3], (unsigned long long)d);
+        }
+    }
+}
+
+template <bool EX, int R, bool COUNT>
+cudaError_t launch_t(WavefrontState *ws, const FrameParams &fp, const RmInsn *prog, uint8_t *dst, size_t pitch,
+                     unsigned long long *counters, unsigned int *tc, cudaStream_t st) {
+    auto kern = k_wavefront<EX, R, COUNT>;
+    const size_t smem = (size_t)fp.n_insn * sizeof(RmInsn) + WF_WARPS * sizeof(WarpShared);
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    int per_sm = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, WF_WARPS * 32, smem);
+    if (e != cudaSuccess) return e;
+    if (per_sm < 1) return cudaErrorLaunchOutOfResources;
+    const uint32_t tiles = ((fp.W + TILE_W - 1) / TILE_W) * ((fp.nrows + TILE_H - 1) / TILE_H);
+    unsigned grid = (unsigned)(ws->sm_count * per_sm);
+    const unsigned need = (tiles + WF_WARPS - 1) / WF_WARPS;
+    if (grid > need) grid = need;
+    if (grid == 0) return cudaSuccess;
+    kern<<<grid, WF_WARPS * 32, smem, st>>>(fp, prog, dst, pitch, tc, counters);
+    return cudaGetLastError();
+}
+
+}  // namespace
+
+cudaError_t wavefront_init(WavefrontState *ws, int device) {
+    ws->device = device;
+    cudaError_t e = cudaDeviceGetAttribute(&ws->sm_count, cudaDevAttrMultiProcessorCount, device);
+    if (e != cudaSuccess) return e;
+    e = cudaMalloc(&ws->d_tile_counters, RING * sizeof(unsigned int));
+    if (e != cudaSuccess) return e;
+    return cudaMemset(ws->d_tile_counters, 0, RING * sizeof(unsigned int));
+}
+
+void wavefront_destroy(WavefrontState *ws) {
+    if (ws->d_tile_counters) cudaFree(ws->d_tile_counters);
+    ws->d_tile_counters = nullptr;
+}
+
+cudaError_t launch_wavefront(WavefrontState *ws, bool exact, const FrameParams &fp, const RmInsn *prog_dev,
+                             uint8_t *dst, size_t pitch, unsigned long long *counters, cudaStream_t st) {
+    if (fp.nrows == 0 || fp.W == 0) return cudaSuccess;
+    unsigned int *tc = ws->d_tile_counters + (ws->ring_pos++ % RING);
+    cudaError_t e = cudaMemsetAsync(tc, 0, sizeof(unsigned int), st);
+    if (e != cudaSuccess) return e;
+    static const int kR = [] {
+        const char *s = std::getenv("RM_WF_R");
+        const int v = s ? std::atoi(s) : 4;
+        return (v == 1 || v == 2 || v == 4) ? v : 4;
+    }();
+#define RM_WF_DISPATCH(EXV, RV)                                                                        \
+    (counters ? launch_t<EXV, RV, true>(ws, fp, prog_dev, dst, pitch, counters, tc, st)                \
+              : launch_t<EXV, RV, false>(ws, fp, prog_dev, dst, pitch, counters, tc, st))
+    if (exact) {
+        if (kR == 1) return RM_WF_DISPATCH(true, 1);
+        if (kR == 2) return RM_WF_DISPATCH(true, 2);
+        return RM_WF_DISPATCH(true, 4);
+    } else {
+        if (kR == 1) return RM_WF_DISPATCH(false, 1);
+        if (kR == 2) return RM_WF_DISPATCH(false, 2);
+        return RM_WF_DISPATCH(false, 4);
+    }
+#undef RM_WF_DISPATCH
+}
+
+}  // namespace rm

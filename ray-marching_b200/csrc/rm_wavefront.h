@@ -1,0 +1,25 @@
+// rm_wavefront.h — launch wrapper of the persistent wavefront kernel (rm_wavefront.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "rm_device.cuh"
+
+namespace rm {
+
+struct WavefrontState {
+    unsigned int *d_tile_counters = nullptr;  // ring of global tile-queue heads, one per launch in flight
+    unsigned int ring_pos = 0;
+    int sm_count = 0;
+    int device = 0;
+};
+
+cudaError_t wavefront_init(WavefrontState *ws, int device);
+void wavefront_destroy(WavefrontState *ws);
+
+// Shades the band described by fp into dst (RGBA8, `pitch` bytes between rows).
+// counters: optional device array {N_step, N_hit, N_floor, N_sample} (adds bookkeeping).
+cudaError_t launch_wavefront(WavefrontState *ws, bool exact, const FrameParams &fp, const RmInsn *prog_dev,
+                             uint8_t *dst, size_t pitch, unsigned long long *counters, cudaStream_t st);
+
+}  // namespace rm

@@ -1,0 +1,81 @@
+"""CPU-side checks of the C-ABI library: it loads, exports every declared symbol, and its static
+program validation agrees with the oracle's.  No compute calls (no GPU here)."""
+import ctypes as C
+import re
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+import helpers as h
+import rm_import
+
+ROOT = Path(__file__).resolve().parent.parent
+
+
+@pytest.fixture(scope="module")
+def rm():
+    m = rm_import.load()
+    if not m.LIB_PATH.exists():
+        m.build()
+    return m
+
+
+def test_library_exports_every_declared_symbol(rm):
+    header = (ROOT / "include" / "rm_b200.h").read_text()
+    declared = set(re.findall(r"RM_API\s+[\w \*]+?\b(rm_\w+)\s*\(", header))
+    assert declared == set(rm.ABI_SYMBOLS), declared ^ set(rm.ABI_SYMBOLS)
+    L = rm.lib()
+    for s in declared:
+        assert hasattr(L, s), s
+    assert b"sm_100a" in L.rm_version()
+
+
+def test_strerror_covers_codes(rm):
+    L = rm.lib()
+    for code in range(0, -9, -1):
+        assert L.rm_strerror(code) != b"unknown error"
+
+
+@pytest.mark.parametrize("words,count,code", [
+    ([], 0, 0),
+    (h.sphere((0, 0, 0), 1), 1, 0),
+    ([5], 1, -3),
+    ([100], 1, -5),
+    ([0, 0, 0, 0], 1, -5),
+    (h.sphere((0, 0, 0), 1) * 33, 33, -4),
+    (h.sphere((0, 0, 0), 1) * 32 + [100] * 31, 63, 0),
+    (h.sphere((0, 0, 0), 1) * 60, 60, -2),
+    (h.sphere((0, 0, 0), 1) * 2 + [103, h.fbits(0.0)], 3, -8),
+    (h.sphere((0, 0, 0), 1) * 2 + [103, h.fbits(float("nan"))], 3, -8),
+    (h.sphere((0, 0, 0), 1) * 2 + [103, h.fbits(0.25)], 3, 0),
+])
+def test_validate_program_codes(rm, words, count, code):
+    assert rm.validate_program(count, words) == code
+
+
+def test_validation_agrees_with_oracle_on_random_streams(rm):
+    rng = np.random.default_rng(0)
+    ops = [0, 1, 100, 101, 102, 103, 7]
+    agree = 0
+    for _ in range(3000):
+        n = int(rng.integers(1, 12))
+        words = []
+        for _ in range(n):
+            t = ops[rng.integers(len(ops))]
+            words.append(t)
+            words += [h.fbits(rng.uniform(0.1, 1))] * {0: 4, 1: 6, 103: 1}.get(t, 0)
+        if rng.random() < 0.1:
+            words = words[:-1]
+        a = rm.validate_program(n, words) == 0
+        b = h.oracle_validate(n, words) == 0
+        assert a == b, words
+        agree += a
+    assert agree > 50
+
+
+def test_scene_definitions():
+    c, w = h.scene_s1()
+    assert c == 5 and len(w) == 19
+    c, w = h.scene_s2()
+    assert c == 63 and len(w) == 251 and rm_import.load().validate_program(c, w) == 0

@@ -1,0 +1,235 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the CPU oracle on identical inputs.
+
+Bars (BASELINE.json north_star): RM_MODE_EXACT must be bit-identical to the oracle (image, per-sample
+class, per-sample distance, work counters).  RM_MODE_FAST must meet the north-star gates:
+hit-mask disagreement <= 0.01 % of pixels, |dRGBA8| <= 2 LSB on >= 99.9 % of pixels, hit-distance
+relative error <= 1e-4 (checked on >= 99.9 % of samples hit by both, see DESIGN.md "Parity gates").
+"""
+import numpy as np
+import pytest
+
+import helpers as h
+import rm_import
+
+pytestmark = pytest.mark.gpu
+
+GATE_HITMASK = 1e-4      # <= 0.01 % of pixels
+GATE_RGBA_LSB = 2        # <= 2 LSB ...
+GATE_RGBA_FRAC = 1e-3    # ... on >= 99.9 % of pixels
+GATE_T_REL = 1e-4        # hit-distance relative error
+GATE_T_FRAC = 1e-3
+
+
+@pytest.fixture(scope="module")
+def rm():
+    return rm_import.load()
+
+
+@pytest.fixture()
+def ctx(rm):
+    c = rm.Context(0)
+    yield c
+    c.close()
+
+
+def cases():
+    return [
+        ("S0", 640, 480, 0.0, 0.0),   # config 1
+        ("S1", 480, 270, 0.6, 0.4),   # config 2 at 1/4 resolution
+        ("S2", 384, 216, 0.6, 0.4),   # config 3 at 1/10 resolution
+    ]
+
+
+def gates(img, ref, cls=None, cls_ref=None, t=None, t_ref=None):
+    d = np.abs(img.astype(np.int32) - ref.astype(np.int32)).max(-1)
+    out = {"rgba_frac": float((d > GATE_RGBA_LSB).mean()), "rgba_max": int(d.max())}
+    if cls is not None:
+        hm = (cls == 2)
+        hm_ref = (cls_ref == 2)
+        out["hitmask_pix"] = float((hm != hm_ref).any(-1).mean())
+        both = hm & hm_ref
+        rel = np.abs(t[both] - t_ref[both]) / np.maximum(np.abs(t_ref[both]), 1e-6)
+        out["t_frac"] = float((rel > GATE_T_REL).mean()) if rel.size else 0.0
+        out["t_max"] = float(rel.max()) if rel.size else 0.0
+    return out
+
+
+@pytest.mark.parametrize("name,W,H,yaw,pitch", cases())
+@pytest.mark.parametrize("kernel", ["wavefront", "simple"])
+def test_exact_mode_bit_identical(rm, ctx, name, W, H, yaw, pitch, kernel):
+    cmd, words = h.SCENES[name]()
+    u = h.orbit_uniforms(W, H, yaw=yaw, pitch=pitch)
+    ref = h.oracle_render(u, cmd, words, W, H, aov=True)
+    ctx.set_mode(rm.MODE_EXACT)
+    ctx.set_kernel(rm.KERNEL_WAVEFRONT if kernel == "wavefront" else rm.KERNEL_SIMPLE)
+    ctx.set_counters(True)
+    img = ctx.render(u, cmd, words, W, H)
+    cnt = ctx.get_counters()
+    assert np.array_equal(img, ref["rgba"]), gates(img, ref["rgba"])
+    assert np.array_equal(cnt, ref["counters"]), (cnt, ref["counters"])
+
+
+@pytest.mark.parametrize("name,W,H,yaw,pitch", cases())
+def test_exact_mode_aovs_bit_identical(rm, ctx, name, W, H, yaw, pitch):
+    cmd, words = h.SCENES[name]()
+    u = h.orbit_uniforms(W, H, yaw=yaw, pitch=pitch)
+    ref = h.oracle_render(u, cmd, words, W, H, aov=True)
+    ctx.set_mode(rm.MODE_EXACT)
+    ctx.prepare(u, cmd, words)
+    dbg = ctx.paint_debug(W, H)
+    assert np.array_equal(dbg["cls"], ref["cls"])
+    assert np.array_equal(dbg["t"].view(np.uint32), ref["t"].view(np.uint32))  # bit pattern, NaN/inf included
+    assert np.array_equal(dbg["rgba"], ref["rgba"])
+    assert np.array_equal(dbg["counters"], ref["counters"])
+
+
+@pytest.mark.parametrize("name,W,H,yaw,pitch", cases())
+def test_fast_mode_meets_north_star_gates(rm, ctx, name, W, H, yaw, pitch):
+    cmd, words = h.SCENES[name]()
+    u = h.orbit_uniforms(W, H, yaw=yaw, pitch=pitch)
+    ref = h.oracle_render(u, cmd, words, W, H, aov=True)
+    ctx.set_mode(rm.MODE_FAST)
+    img = ctx.render(u, cmd, words, W, H)
+    dbg = ctx.paint_debug(W, H)
+    assert np.array_equal(dbg["rgba"], img)  # wavefront and simple kernels agree bit for bit
+    g = gates(img, ref["rgba"], dbg["cls"], ref["cls"], dbg["t"], ref["t"])
+    print(name, g)
+    assert g["hitmask_pix"] <= GATE_HITMASK, g
+    assert g["rgba_frac"] <= GATE_RGBA_FRAC, g
+    assert g["t_frac"] <= GATE_T_FRAC, g
+
+
+def random_program(rng, n_leaves, right_bias=0.3):
+    """Random valid postfix program with mixed tree shapes (stack depth <= 32)."""
+    def leaf():
+        c = rng.uniform(-2, 2, 3)
+        if rng.random() < 0.5:
+            return h.sphere(c, rng.uniform(0.2, 1.0)), 1
+        return h.box(c, rng.uniform(0.2, 1.0, 3)), 1
+
+    def op():
+        r = rng.random()
+        if r < 0.3:
+            return [h.OP_UNION]
+        if r < 0.5:
+            return [h.OP_SUBTRACTION]
+        if r < 0.65:
+            return [h.OP_INTERSECTION]
+        k = [0.25, 0.5, 0.3, 0.1, 1.0][rng.integers(5)]
+        return [h.OP_SMOOTH_UNION, h.fbits(k)]
+
+    def tree(n):
+        if n == 1:
+            return leaf()
+        nl = 1 if rng.random() > right_bias else int(rng.integers(1, n))
+        nl = n - nl if rng.random() < 0.5 else nl
+        nl = min(max(nl, 1), n - 1)
+        wa, ca = tree(nl)
+        wb, cb = tree(n - nl)
+        return wa + wb + op(), ca + cb + 1
+
+    return tree(n_leaves)
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_interpreter_property_random_trees(rm, ctx, seed):
+    rng = np.random.default_rng(1234 + seed)
+    for n_leaves in (1, 2, 3, 7, 16, 30):
+        words, cmd = random_program(rng, n_leaves)
+        if len(words) > 255:
+            continue
+        pts = rng.uniform(-4, 4, (4096, 3)).astype(np.float32)
+        ref = h.oracle_map(cmd, words, pts)
+        u = h.orbit_uniforms(64, 64)
+        ctx.set_mode(rm.MODE_EXACT)
+        ctx.prepare(u, cmd, words)
+        got = ctx.map(pts)
+        assert np.array_equal(got, ref), f"n_leaves={n_leaves} max|d|={np.abs(got - ref).max()}"
+        ctx.set_mode(rm.MODE_FAST)
+        got = ctx.map(pts)
+        np.testing.assert_allclose(got, ref, rtol=0, atol=1e-5 * max(1.0, float(np.abs(ref).max())))
+        # image through the wavefront kernel (exercises spill slots with R rays per lane)
+        ctx.set_mode(rm.MODE_EXACT)
+        img = ctx.render(u, cmd, words, 64, 64)
+        assert np.array_equal(img, h.oracle_render(u, cmd, words, 64, 64)["rgba"])
+
+
+def test_right_deep_chain_depth_32(rm, ctx):
+    rng = np.random.default_rng(7)
+    words = []
+    for _ in range(32):
+        words += h.sphere(rng.uniform(-2, 2, 3), rng.uniform(0.2, 0.6))
+    words += [h.OP_UNION] * 31
+    assert len(words) <= 255
+    u = h.orbit_uniforms(96, 64, yaw=0.3, pitch=0.2)
+    ctx.set_mode(rm.MODE_EXACT)
+    img = ctx.render(u, 63, words, 96, 64)
+    assert np.array_equal(img, h.oracle_render(u, 63, words, 96, 64)["rgba"])
+
+
+@pytest.mark.parametrize("W,H", [(37, 23), (8, 4), (1, 1), (9, 5), (130, 3)])
+def test_ragged_sizes(rm, ctx, W, H):
+    cmd, words = h.scene_s1()
+    u = h.orbit_uniforms(W, H, yaw=0.6, pitch=0.4)
+    ctx.set_mode(rm.MODE_EXACT)
+    img = ctx.render(u, cmd, words, W, H)
+    assert np.array_equal(img, h.oracle_render(u, cmd, words, W, H)["rgba"])
+
+
+def test_empty_scene(rm, ctx):
+    u = h.orbit_uniforms(64, 48, pitch=0.3)
+    ctx.set_mode(rm.MODE_EXACT)
+    img = ctx.render(u, 0, [], 64, 48)
+    assert np.array_equal(img, h.oracle_render(u, 0, [], 64, 48)["rgba"])
+
+
+def test_row_bands_bit_identical_to_full_frame(rm, ctx):
+    cmd, words = h.scene_s2()
+    W, H = 256, 144
+    u = h.orbit_uniforms(W, H, yaw=0.6, pitch=0.4)
+    ctx.set_mode(rm.MODE_FAST)
+    full = ctx.render(u, cmd, words, W, H)
+    for bands in ([0, 72, 144], [0, 10, 11, 77, 144], [0, 36, 72, 108, 144]):
+        parts = [ctx.render(u, cmd, words, W, H, row0=a, nrows=b - a) for a, b in zip(bands[:-1], bands[1:])]
+        assert np.array_equal(np.concatenate(parts, 0), full)
+
+
+def test_limits_are_runtime_values(rm, ctx):
+    cmd, words = h.scene_s1()
+    W, H = 96, 64
+    u = h.orbit_uniforms(W, H, yaw=0.6, pitch=0.4)
+    for lim in [(0.05, 50.0, 20), (0.001, 100.0, 7), (0.01, 100.0, 0)]:
+        ctx.set_limits(*lim)
+        ctx.set_mode(rm.MODE_EXACT)
+        img = ctx.render(u, cmd, words, W, H)
+        ref = h.oracle_render(u, cmd, words, W, H, limits=h.limits_bytes(*lim))["rgba"]
+        assert np.array_equal(img, ref), lim
+
+
+def test_pose_batch_matches_single_frames(rm, ctx):
+    import torch
+    cmd, words = h.scene_s1()
+    W, H, n = 128, 72, 5
+    poses = [h.orbit_uniforms(W, H, yaw=2 * np.pi * k / n, pitch=0.4) for k in range(n)]
+    ctx.set_mode(rm.MODE_FAST)
+    singles = [ctx.render(p, cmd, words, W, H) for p in poses]
+    buf = torch.empty((n, H, W, 4), dtype=torch.uint8, device="cuda:0")
+    ctx.prepare(poses[0], cmd, words)
+    ctx.paint_poses(b"".join(poses), n, W, H, buf.data_ptr(), W * 4, W * H * 4)
+    ctx.sync()
+    got = buf.cpu().numpy()
+    for k in range(n):
+        assert np.array_equal(got[k], singles[k])
+
+
+def test_error_codes(rm, ctx):
+    u = h.orbit_uniforms(32, 32)
+    with pytest.raises(rm.RmError) as e:
+        ctx.paint(32, 32)
+    assert e.value.code == -7  # RM_E_NOT_PREPARED
+    for words, cmd, code in [([5], 1, -3), ([100], 1, -5), (h.sphere((0, 0, 0), 1) * 33, 33, -4),
+                             (h.sphere((0, 0, 0), 1) * 60, 60, -2),
+                             (h.sphere((0, 0, 0), 1) * 2 + [103, h.fbits(-1.0)], 3, -8)]:
+        with pytest.raises(rm.RmError) as e:
+            ctx.prepare(u, cmd, words)
+        assert e.value.code == code
