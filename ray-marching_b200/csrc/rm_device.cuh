@@ -134,7 +134,7 @@ __device__ __forceinline__ float map_eval1(const float4 *__restrict__ prog, uint
         const float4 q0 = prog[3 * i], q1 = prog[3 * i + 1], q2 = prog[3 * i + 2];
         const uint32_t op = __float_as_uint(q2.y), slot = __float_as_uint(q2.z);
         const bool k_pow2 = (__float_as_uint(q2.w) & FLAG_K_POW2) != 0;
-        const uint32_t src = op >> 3, cb = op & 7u;
+        const uint32_t src = opcode_src(op), cb = opcode_cb(op);
         float a, b;
         if (src == SRC_SPHERE) {
             b = sd_sphere<EX>(px, py, pz, q0.x, q0.y, q0.z, q0.w);

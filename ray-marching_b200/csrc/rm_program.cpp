@@ -87,20 +87,20 @@ int decode_program(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, 
             if (c.type == RM_OP_BOX) { src = SRC_BOX; in.r1 = c.p[4]; in.r2 = c.p[5]; }
             if (depth >= 1 && i + 1 < cmd_count && is_binary(cmds[i + 1].type)) {
                 const Cmd &o = cmds[i + 1];  // fused: acc = op(acc, prim)
-                in.op = (src << 3) | combine_of(o.type);
+                in.op = opcode(src, combine_of(o.type));
                 if (o.type == RM_OP_SMOOTH_UNION) set_k(in, o.p[0]);
                 ++i;  // the operator is consumed; depth unchanged (push 1, pop 2, push 1)
             } else if (depth == 0) {
-                in.op = (src << 3) | CB_FIRST;
+                in.op = opcode(src, CB_FIRST);
                 depth = 1;
             } else {
-                in.op = (src << 3) | CB_PUSH;
+                in.op = opcode(src, CB_PUSH);
                 in.slot = depth - 1;
                 depth += 1;
             }
         } else {
             if (depth < 2) return RM_E_STACK_UNBALANCED;
-            in.op = (SRC_POP << 3) | combine_of(c.type);
+            in.op = opcode(SRC_POP, combine_of(c.type));
             in.slot = depth - 2;
             if (c.type == RM_OP_SMOOTH_UNION) set_k(in, c.p[0]);
             depth -= 1;

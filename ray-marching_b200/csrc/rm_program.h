@@ -39,12 +39,26 @@ enum : uint32_t {
 };
 enum : uint32_t { FLAG_K_POW2 = 1u };  // 1/k is exact: multiply instead of divide in exact mode
 
+// RmInsn::op is a DENSE fused opcode 0..15 so that the interpreter dispatches through a single
+// jump table:  0..3 = POP x {UNION,SUB,INTER,SMOOTH};  4..9 = SPHERE x {FIRST..SMOOTH};
+// 10..15 = BOX x {FIRST..SMOOTH}.
+#define RM_HD
+#ifdef __CUDACC__
+#undef RM_HD
+#define RM_HD __host__ __device__
+#endif
+RM_HD constexpr uint32_t opcode(uint32_t src, uint32_t cb) {
+    return src == SRC_POP ? cb - CB_UNION : (src == SRC_SPHERE ? 4u + cb : 10u + cb);
+}
+RM_HD constexpr uint32_t opcode_src(uint32_t op) { return op < 4u ? SRC_POP : (op < 10u ? SRC_SPHERE : SRC_BOX); }
+RM_HD constexpr uint32_t opcode_cb(uint32_t op) { return op < 4u ? op + CB_UNION : (op < 10u ? op - 4u : op - 10u); }
+
 // One decoded instruction = 3 x 16 bytes (three broadcast LDS.128).
 struct alignas(16) RmInsn {
     float cx, cy, cz, r0;      // centre, sphere radius / box radius x
     float r1, r2, k, inv_k;    // box radius y,z; smooth-union k and 1/k
     float kq;                  // k * 0.25 (exact scaling)
-    uint32_t op;               // src << 3 | combine
+    uint32_t op;               // dense fused opcode, see opcode()
     uint32_t slot;             // spill slot read (SRC_POP) or written (CB_PUSH)
     uint32_t flags;
 };

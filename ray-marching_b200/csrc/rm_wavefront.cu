@@ -33,76 +33,69 @@ struct WarpShared {
     int tile[WF_K];  // tile id, or -1 when the buffer is free
 };
 
-// map_scene for R points at once: one instruction fetch/decode feeds R evaluations.
+// map_scene for R points at once: one instruction fetch and ONE jump-table dispatch on the fused
+// opcode feed R evaluations; every case folds its source straight into the accumulators.
+template <bool EX, uint32_t SRC>
+__device__ __forceinline__ float prim_eval(float x, float y, float z, const float4 &q0, const float4 &q1) {
+    if (SRC == SRC_SPHERE) return sd_sphere<EX>(x, y, z, q0.x, q0.y, q0.z, q0.w);
+    return sd_box<EX>(x, y, z, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y);
+}
+
+#define RM_OPC(SRC, CB) opcode(SRC, CB)
+#define RM_FOR_R _Pragma("unroll") for (int r = 0; r < R; ++r)
+#define RM_PRIM_CASES(SRC)                                                                                  \
+    case RM_OPC(SRC, CB_FIRST):                                                                             \
+        RM_FOR_R acc[r] = prim_eval<EX, SRC>(px[r], py[r], pz[r], q0, q1);                                  \
+        break;                                                                                              \
+    case RM_OPC(SRC, CB_PUSH):                                                                              \
+        RM_FOR_R { spill[slot][r] = acc[r]; acc[r] = prim_eval<EX, SRC>(px[r], py[r], pz[r], q0, q1); }     \
+        break;                                                                                              \
+    case RM_OPC(SRC, CB_UNION):                                                                             \
+        RM_FOR_R acc[r] = fminf(acc[r], prim_eval<EX, SRC>(px[r], py[r], pz[r], q0, q1));                   \
+        break;                                                                                              \
+    case RM_OPC(SRC, CB_SUB):                                                                               \
+        RM_FOR_R acc[r] = fmaxf(acc[r], -prim_eval<EX, SRC>(px[r], py[r], pz[r], q0, q1));                  \
+        break;                                                                                              \
+    case RM_OPC(SRC, CB_INTER):                                                                             \
+        RM_FOR_R acc[r] = fmaxf(acc[r], prim_eval<EX, SRC>(px[r], py[r], pz[r], q0, q1));                   \
+        break;                                                                                              \
+    case RM_OPC(SRC, CB_SMOOTH):                                                                            \
+        RM_FOR_R acc[r] = op_smooth<EX>(acc[r], prim_eval<EX, SRC>(px[r], py[r], pz[r], q0, q1), q1.z, q1.w, \
+                                        q2.x, k_pow2);                                                      \
+        break;
+
 template <bool EX, int R>
 __device__ __forceinline__ void map_evalR(const float4 *__restrict__ prog, uint32_t n_insn, float max_dist,
                                           const float (&px)[R], const float (&py)[R], const float (&pz)[R],
                                           float (&acc)[R], float (*spill)[R]) {
     if (n_insn == 0) {  // wgsl:189-191
-#pragma unroll
-        for (int r = 0; r < R; ++r) acc[r] = max_dist;
+        RM_FOR_R acc[r] = max_dist;
         return;
     }
-#pragma unroll
-    for (int r = 0; r < R; ++r) acc[r] = 0.0f;
+    RM_FOR_R acc[r] = 0.0f;
 #pragma unroll 1
     for (uint32_t i = 0; i < n_insn; ++i) {
         const float4 q0 = prog[3 * i], q1 = prog[3 * i + 1], q2 = prog[3 * i + 2];
-        const uint32_t op = __float_as_uint(q2.y);
-        const uint32_t src = op >> 3, cb = op & 7u;
-        float a[R], b[R];
-        if (src == SRC_SPHERE) {
-#pragma unroll
-            for (int r = 0; r < R; ++r) {
-                b[r] = sd_sphere<EX>(px[r], py[r], pz[r], q0.x, q0.y, q0.z, q0.w);
-                a[r] = acc[r];
-            }
-        } else if (src == SRC_BOX) {
-#pragma unroll
-            for (int r = 0; r < R; ++r) {
-                b[r] = sd_box<EX>(px[r], py[r], pz[r], q0.x, q0.y, q0.z, q0.w, q1.x, q1.y);
-                a[r] = acc[r];
-            }
-        } else {
-            const uint32_t slot = __float_as_uint(q2.z);
-#pragma unroll
-            for (int r = 0; r < R; ++r) {
-                b[r] = acc[r];
-                a[r] = spill[slot][r];
-            }
-        }
-        switch (cb) {
-            case CB_FIRST:
-#pragma unroll
-                for (int r = 0; r < R; ++r) acc[r] = b[r];
+        const uint32_t op = __float_as_uint(q2.y), slot = __float_as_uint(q2.z);
+        const bool k_pow2 = (__float_as_uint(q2.w) & FLAG_K_POW2) != 0;
+        switch (op) {
+            RM_PRIM_CASES(SRC_SPHERE)
+            RM_PRIM_CASES(SRC_BOX)
+            // binary operator on two subtrees: right operand = accumulator, left = spilled entry
+            case RM_OPC(SRC_POP, CB_UNION):
+                RM_FOR_R acc[r] = fminf(spill[slot][r], acc[r]);
                 break;
-            case CB_PUSH: {
-                const uint32_t slot = __float_as_uint(q2.z);
-#pragma unroll
-                for (int r = 0; r < R; ++r) {
-                    spill[slot][r] = acc[r];
-                    acc[r] = b[r];
-                }
+            case RM_OPC(SRC_POP, CB_SUB):
+                RM_FOR_R acc[r] = fmaxf(spill[slot][r], -acc[r]);
                 break;
-            }
-            case CB_UNION:
-#pragma unroll
-                for (int r = 0; r < R; ++r) acc[r] = fminf(a[r], b[r]);
+            case RM_OPC(SRC_POP, CB_INTER):
+                RM_FOR_R acc[r] = fmaxf(spill[slot][r], acc[r]);
                 break;
-            case CB_SUB:
-#pragma unroll
-                for (int r = 0; r < R; ++r) acc[r] = fmaxf(a[r], -b[r]);
+            case RM_OPC(SRC_POP, CB_SMOOTH):
+                RM_FOR_R acc[r] = op_smooth<EX>(spill[slot][r], acc[r], q1.z, q1.w, q2.x, k_pow2);
                 break;
-            case CB_INTER:
-#pragma unroll
-                for (int r = 0; r < R; ++r) acc[r] = fmaxf(a[r], b[r]);
+            default:
                 break;
-            default: {
-                const bool k_pow2 = (__float_as_uint(q2.w) & FLAG_K_POW2) != 0;
-#pragma unroll
-                for (int r = 0; r < R; ++r) acc[r] = op_smooth<EX>(a[r], b[r], q1.z, q1.w, q2.x, k_pow2);
-                break;
-            }
         }
     }
 }
@@ -238,6 +231,9 @@ k_wavefront(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ p
             px[r] = st == 0 ? bx : __fadd_rn(bx, ox);
             py[r] = st == 0 ? by : __fadd_rn(by, oy);
             pz[r] = st == 0 ? bz : __fadd_rn(bz, oz);
+            // keep the points in registers: without this ptxas rematerialises the select/add
+            // chain above inside every interpreted instruction
+            asm volatile("" : "+f"(px[r]), "+f"(py[r]), "+f"(pz[r]));
         }
         map_evalR<EX, R>(s_prog, fp.n_insn, fp.max_dist, px, py, pz, s, spill);
 
@@ -298,7 +294,7 @@ k_wavefront(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ p
             const uint32_t pix = resolve_pixel(c16);  // wgsl:44-45,68-75 in sample order
             const uint32_t tx = (uint32_t)tile % tiles_x, ty = (uint32_t)tile / tiles_x;
             const uint32_t x0 = tx * TILE_W, y0 = ty * TILE_H;
-            if (x0 + TILE_W <= fp.W && y0 + TILE_H <= fp.nrows) {
+            if (x0 + TILE_W <= fp.W && y0 + TILE_H <= fp.nrows && (pitch & 15) == 0) {
                 // lanes 0..7 each gather four pixels of one half-row and issue one 128-bit store
                 const int row = (lane >> 1) & 3, half = lane & 1;
                 const int srcl = row * 8 + half * 4;
@@ -376,7 +372,7 @@ cudaError_t launch_wavefront(WavefrontState *ws, bool exact, const FrameParams &
     static const int kR = [] {
         const char *s = std::getenv("RM_WF_R");
         const int v = s ? std::atoi(s) : 4;
-        return (v == 1 || v == 2 || v == 4) ? v : 4;
+        return (v == 1 || v == 2 || v == 4 || v == 8) ? v : 4;
     }();
 #define RM_WF_DISPATCH(EXV, RV)                                                                        \
     (counters ? launch_t<EXV, RV, true>(ws, fp, prog_dev, dst, pitch, counters, tc, st)                \
@@ -384,10 +380,12 @@ cudaError_t launch_wavefront(WavefrontState *ws, bool exact, const FrameParams &
     if (exact) {
         if (kR == 1) return RM_WF_DISPATCH(true, 1);
         if (kR == 2) return RM_WF_DISPATCH(true, 2);
+        if (kR == 8) return RM_WF_DISPATCH(true, 8);
         return RM_WF_DISPATCH(true, 4);
     } else {
         if (kR == 1) return RM_WF_DISPATCH(false, 1);
         if (kR == 2) return RM_WF_DISPATCH(false, 2);
+        if (kR == 8) return RM_WF_DISPATCH(false, 8);
         return RM_WF_DISPATCH(false, 4);
     }
 #undef RM_WF_DISPATCH
