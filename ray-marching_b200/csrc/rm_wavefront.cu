@@ -100,6 +100,59 @@ __device__ __forceinline__ void map_evalR(const float4 *__restrict__ prog, uint3
     }
 }
 
+// ---- rare per-ray events, kept OUT OF LINE (one copy each) so that the per-iteration instruction
+// footprint of the persistent loop stays inside the instruction cache (profiles/r1_v1_*: the fully
+// inlined R=4 kernel stalled 4.7 cycles per issue on no_instruction) ------------------------------
+#define RM_CODE_LIVE (-4.0f)  // wf_spawn: the ray is alive (no result yet)
+struct Spawn { float x, y, z, code; };
+
+__device__ __noinline__ float wf_miss(float rox, float roy, float roz, float dx, float dy, float dz);
+
+// Creates sample ray q (= sample*32 + pixel) of tile `tile`: direction + RM_CODE_LIVE, or its
+// final code when there is nothing to march (pixel outside the band, max_iter == 0).
+__device__ __noinline__ Spawn wf_spawn(const FrameParams &fp, uint32_t q, uint32_t tile, uint32_t tiles_x) {
+    const uint32_t pixel = q & 31u, sample = q >> 5;
+    const uint32_t tx = tile % tiles_x, ty = tile / tiles_x;
+    const uint32_t px = tx * TILE_W + (pixel & 7u), ry = ty * TILE_H + (pixel >> 3);
+    if (px >= fp.W || ry >= fp.nrows) return Spawn{0.f, 0.f, 0.f, RM_CODE_SKY};
+    float o[3], d[3];
+    gen_ray(fp, px, fp.row0 + ry, sample, o, d);
+    if (fp.max_iter == 0) return Spawn{d[0], d[1], d[2], wf_miss(o[0], o[1], o[2], d[0], d[1], d[2])};
+    return Spawn{d[0], d[1], d[2], RM_CODE_LIVE};
+}
+
+// floor / sky of a missed ray (wgsl:117-130) -> sample code
+__device__ __noinline__ float wf_miss(float rox, float roy, float roz, float dx, float dy, float dz) {
+    const float ro[3] = {rox, roy, roz}, rd[3] = {dx, dy, dz};
+    float c[3], t;
+    const int cls = shade_miss(ro, rd, c, t);
+    if (cls == 0) return RM_CODE_SKY;
+    return c[0] > 0.2f ? RM_CODE_FLOOR_LIGHT : RM_CODE_FLOOR_DARK;
+}
+
+// normal from the four tetrahedron taps + diffuse term (wgsl:98-105, 138-143) -> sample code
+template <bool EX>
+__device__ __noinline__ float wf_shade(float a0, float a1, float a2, float a3, float hx, float hy, float hz) {
+    using A = Arith<EX>;
+    const float nx = A::add(A::add(A::add(a0, -a1), -a2), a3);
+    const float ny = A::add(A::add(A::add(-a0, -a1), a2), a3);
+    const float nz = A::add(A::add(A::add(-a0, a1), -a2), a3);
+    return shade_diffuse<EX>(nx, ny, nz, hx, hy, hz);
+}
+
+// in-order 16-sample resolve of one pixel of a finished tile (codes[sample*32 + pixel])
+__device__ __noinline__ uint32_t wf_resolve(const float *codes, int lane) {
+    float sr = 0.0f, sg = 0.0f, sb = 0.0f;
+#pragma unroll 1
+    for (int sidx = 0; sidx < 16; ++sidx) {
+        float g[3];
+        code_to_gamma(codes[sidx * 32 + lane], g);
+        sr = __fadd_rn(sr, g[0]); sg = __fadd_rn(sg, g[1]); sb = __fadd_rn(sb, g[2]);
+    }
+    return unorm8(__fdiv_rn(sr, 16.0f)) | (unorm8(__fdiv_rn(sg, 16.0f)) << 8) |
+           (unorm8(__fdiv_rn(sb, 16.0f)) << 16) | 0xff000000u;
+}
+
 template <bool EX, int R, bool COUNT>
 __global__ void __launch_bounds__(WF_WARPS * 32)
 k_wavefront(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ prog_g, uint8_t *__restrict__ dst,
@@ -134,80 +187,58 @@ k_wavefront(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ p
     float rdx[R], rdy[R], rdz[R], dist[R], m0[R], m1[R], m2[R];
     uint32_t meta[R], iter[R];
     float spill[RM_STACK_MAX - 1][R];
-#pragma unroll
-    for (int r = 0; r < R; ++r) { meta[r] = 0; iter[r] = 0; dist[r] = 0.f; rdx[r] = rdy[r] = rdz[r] = 0.f; m0[r] = m1[r] = m2[r] = 0.f; }
+    RM_FOR_R { meta[r] = 0; iter[r] = 0; dist[r] = 0.f; rdx[r] = rdy[r] = rdz[r] = 0.f; m0[r] = m1[r] = m2[r] = 0.f; }
 
     int cur_buf = 0, pool_next = TILE_RAYS;
     uint32_t cur_tile = 0;
     bool exhausted = false;
     uint32_t c_step = 0, c_hit = 0, c_floor = 0, c_sample = 0;
 
-    // finishes a ray as a miss (floor / sky, wgsl:117-130)
-    auto miss_code = [&](float dx, float dy, float dz) -> float {
-        const float rd[3] = {dx, dy, dz};
-        float c[3], t;
-        const int cls = shade_miss(ro, rd, c, t);
-        if (COUNT && cls == 1) ++c_floor;
-        if (cls == 0) return RM_CODE_SKY;
-        return c[0] > 0.2f ? RM_CODE_FLOOR_LIGHT : RM_CODE_FLOOR_DARK;
-    };
-
     for (;;) {
         // ---------------- refill empty slots from the tile pool (ballot compaction) ----------------
+        if (pool_next >= TILE_RAYS && !exhausted) {  // open the next tile if a buffer is free
+            int b = -1;
 #pragma unroll
-        for (int r = 0; r < R; ++r) {
-            bool empty = !(meta[r] & M_LIVE);
-            unsigned em = __ballot_sync(FULL, empty);
-            while (em) {
-                if (pool_next >= TILE_RAYS) {
-                    if (exhausted) break;
-                    int b = -1;
-#pragma unroll
-                    for (int k = WF_K - 1; k >= 0; --k) if (ws.tile[k] < 0) b = k;
-                    if (b < 0) break;  // every tile buffer still has rays in flight
-                    unsigned t = 0;
-                    if (lane == 0) t = atomicAdd(tile_counter, 1u);
-                    t = __shfl_sync(FULL, t, 0);
-                    if (t >= n_tiles) { exhausted = true; break; }
+            for (int k = WF_K - 1; k >= 0; --k) if (ws.tile[k] < 0) b = k;
+            if (b >= 0) {
+                unsigned t = 0;
+                if (lane == 0) t = atomicAdd(tile_counter, 1u);
+                t = __shfl_sync(FULL, t, 0);
+                if (t >= n_tiles) {
+                    exhausted = true;
+                } else {
                     cur_buf = b; cur_tile = t; pool_next = 0;
                     if (lane == 0) { ws.tile[b] = (int)t; ws.remaining[b] = TILE_RAYS; }
                     __syncwarp();
                 }
+            }
+        }
+        RM_FOR_R {
+            const bool empty = !(meta[r] & M_LIVE);
+            const unsigned em = __ballot_sync(FULL, empty);
+            if (em != 0 && pool_next < TILE_RAYS) {  // warp-uniform
                 const int rank = __popc(em & lt_mask);
                 const int take = min(__popc(em), TILE_RAYS - pool_next);
                 if (empty && rank < take) {
                     const uint32_t q = (uint32_t)(pool_next + rank);
-                    const uint32_t pixel = q & 31u, sample = q >> 5;
-                    const uint32_t tx = cur_tile % tiles_x, ty = cur_tile / tiles_x;
-                    const uint32_t px = tx * TILE_W + (pixel & 7u), ry = ty * TILE_H + (pixel >> 3);
-                    empty = false;
-                    if (px < fp.W && ry < fp.nrows) {
-                        float o[3], d[3];
-                        gen_ray(fp, px, fp.row0 + ry, sample, o, d);
-                        if (COUNT) ++c_sample;
-                        if (fp.max_iter > 0) {
-                            rdx[r] = d[0]; rdy[r] = d[1]; rdz[r] = d[2];
-                            dist[r] = 0.0f; iter[r] = 0;
-                            meta[r] = q | ((uint32_t)cur_buf << M_BUF_SHIFT) | M_LIVE;
-                        } else {
-                            ws.codes[cur_buf][q] = miss_code(d[0], d[1], d[2]);
-                            atomicSub(&ws.remaining[cur_buf], 1);
-                        }
-                    } else {  // pixel outside the band: nothing to shade
-                        ws.codes[cur_buf][q] = RM_CODE_SKY;
+                    const Spawn sp = wf_spawn(fp, q, cur_tile, tiles_x);
+                    if (COUNT && sp.code != RM_CODE_SKY) ++c_sample;
+                    if (sp.code == RM_CODE_LIVE) {
+                        rdx[r] = sp.x; rdy[r] = sp.y; rdz[r] = sp.z;
+                        dist[r] = 0.0f; iter[r] = 0;
+                        meta[r] = q | ((uint32_t)cur_buf << M_BUF_SHIFT) | M_LIVE;
+                    } else {
+                        if (COUNT && (sp.code == RM_CODE_FLOOR_DARK || sp.code == RM_CODE_FLOOR_LIGHT)) ++c_floor;
+                        ws.codes[cur_buf][q] = sp.code;
                         atomicSub(&ws.remaining[cur_buf], 1);
                     }
                 }
                 pool_next += take;
-                em = __ballot_sync(FULL, empty && !(meta[r] & M_LIVE));
-                // lanes that spawned a non-live ray (outside band / max_iter 0) keep empty=false for
-                // this round and are picked up again on the next pass
             }
         }
         // ---------------- termination ----------------
         bool live_any = false;
-#pragma unroll
-        for (int r = 0; r < R; ++r) live_any |= (meta[r] & M_LIVE) != 0;
+        RM_FOR_R live_any |= (meta[r] & M_LIVE) != 0;
         if (!__any_sync(FULL, live_any)) {
             __syncwarp();
             bool pending = false;
@@ -218,8 +249,7 @@ k_wavefront(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ p
 
         // ---------------- evaluation points ----------------
         float px[R], py[R], pz[R], s[R];
-#pragma unroll
-        for (int r = 0; r < R; ++r) {
+        RM_FOR_R {
             const uint32_t st = (meta[r] >> M_STATE_SHIFT) & 7u;
             const float bx = A::mad(rdx[r], dist[r], ro[0]), by = A::mad(rdy[r], dist[r], ro[1]),
                         bz = A::mad(rdz[r], dist[r], ro[2]);  // wgsl:91
@@ -238,8 +268,7 @@ k_wavefront(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ p
         map_evalR<EX, R>(s_prog, fp.n_insn, fp.max_dist, px, py, pz, s, spill);
 
         // ---------------- per-slot state update ----------------
-#pragma unroll
-        for (int r = 0; r < R; ++r) {
+        RM_FOR_R {
             if (!(meta[r] & M_LIVE)) continue;
             const uint32_t st = (meta[r] >> M_STATE_SHIFT) & 7u;
             float code = 0.0f;
@@ -248,13 +277,15 @@ k_wavefront(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ p
                 if (COUNT) ++c_step;
                 if (s[r] < fp.min_dist) {  // wgsl:97 -> start the normal taps
                     meta[r] += 1u << M_STATE_SHIFT;
-                } else if (s[r] > fp.max_dist) {  // wgsl:109-111
-                    code = miss_code(rdx[r], rdy[r], rdz[r]);
-                    done = true;
                 } else {
-                    dist[r] = A::add(dist[r], s[r]);  // wgsl:114
-                    if (++iter[r] >= fp.max_iter) {
-                        code = miss_code(rdx[r], rdy[r], rdz[r]);
+                    bool miss = s[r] > fp.max_dist;  // wgsl:109-111
+                    if (!miss) {
+                        dist[r] = A::add(dist[r], s[r]);  // wgsl:114
+                        miss = ++iter[r] >= fp.max_iter;
+                    }
+                    if (miss) {
+                        code = wf_miss(ro[0], ro[1], ro[2], rdx[r], rdy[r], rdz[r]);
+                        if (COUNT && code != RM_CODE_SKY) ++c_floor;
                         done = true;
                     }
                 }
@@ -264,13 +295,9 @@ k_wavefront(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ p
                 else m2[r] = s[r];
                 meta[r] += 1u << M_STATE_SHIFT;
             } else {
-                const float a0 = m0[r], a1 = m1[r], a2 = m2[r], a3 = s[r];
-                const float nx = A::add(A::add(A::add(a0, -a1), -a2), a3);
-                const float ny = A::add(A::add(A::add(-a0, -a1), a2), a3);
-                const float nz = A::add(A::add(A::add(-a0, a1), -a2), a3);
                 const float hx = A::mad(rdx[r], dist[r], ro[0]), hy = A::mad(rdy[r], dist[r], ro[1]),
                             hz = A::mad(rdz[r], dist[r], ro[2]);
-                code = shade_diffuse<EX>(nx, ny, nz, hx, hy, hz);  // wgsl:98-105
+                code = wf_shade<EX>(m0[r], m1[r], m2[r], s[r], hx, hy, hz);
                 if (COUNT) ++c_hit;
                 done = true;
             }
@@ -284,14 +311,11 @@ k_wavefront(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ p
         __syncwarp();
 
         // ---------------- resolve tiles whose 512 samples are all in ----------------
-#pragma unroll
+#pragma unroll 1
         for (int k = 0; k < WF_K; ++k) {
             const int tile = ws.tile[k];
             if (tile < 0 || ws.remaining[k] != 0) continue;  // warp-uniform
-            float c16[16];
-#pragma unroll
-            for (int sidx = 0; sidx < 16; ++sidx) c16[sidx] = ws.codes[k][sidx * 32 + lane];
-            const uint32_t pix = resolve_pixel(c16);  // wgsl:44-45,68-75 in sample order
+            const uint32_t pix = wf_resolve(ws.codes[k], lane);  // wgsl:44-45,68-75 in sample order
             const uint32_t tx = (uint32_t)tile % tiles_x, ty = (uint32_t)tile / tiles_x;
             const uint32_t x0 = tx * TILE_W, y0 = ty * TILE_H;
             if (x0 + TILE_W <= fp.W && y0 + TILE_H <= fp.nrows && (pitch & 15) == 0) {
