@@ -27,8 +27,10 @@ constexpr uint32_t M_BUF_SHIFT = 9;       // 2 bits
 constexpr uint32_t M_STATE_SHIFT = 11;    // 3 bits: 0 MARCH, 1..4 TAP0..TAP3
 constexpr uint32_t M_LIVE = 1u << 14;
 
+constexpr int RING_N = 64;  // ready-ray ring: two batches of 32
 struct WarpShared {
-    float codes[WF_K][TILE_RAYS];
+    float codes[WF_K][TILE_RAYS];  // per-sample result codes; pre-set to the ray's miss code
+    float4 ring[RING_N];           // generated rays waiting for a slot: dir.xyz + meta bits
     int remaining[WF_K];
     int tile[WF_K];  // tile id, or -1 when the buffer is free
 };
@@ -103,33 +105,6 @@ __device__ __forceinline__ void map_evalR(const float4 *__restrict__ prog, uint3
 // ---- rare per-ray events, kept OUT OF LINE (one copy each) so that the per-iteration instruction
 // footprint of the persistent loop stays inside the instruction cache (profiles/r1_v1_*: the fully
 // inlined R=4 kernel stalled 4.7 cycles per issue on no_instruction) ------------------------------
-#define RM_CODE_LIVE (-4.0f)  // wf_spawn: the ray is alive (no result yet)
-struct Spawn { float x, y, z, code; };
-
-__device__ __noinline__ float wf_miss(float rox, float roy, float roz, float dx, float dy, float dz);
-
-// Creates sample ray q (= sample*32 + pixel) of tile `tile`: direction + RM_CODE_LIVE, or its
-// final code when there is nothing to march (pixel outside the band, max_iter == 0).
-__device__ __noinline__ Spawn wf_spawn(const FrameParams &fp, uint32_t q, uint32_t tile, uint32_t tiles_x) {
-    const uint32_t pixel = q & 31u, sample = q >> 5;
-    const uint32_t tx = tile % tiles_x, ty = tile / tiles_x;
-    const uint32_t px = tx * TILE_W + (pixel & 7u), ry = ty * TILE_H + (pixel >> 3);
-    if (px >= fp.W || ry >= fp.nrows) return Spawn{0.f, 0.f, 0.f, RM_CODE_SKY};
-    float o[3], d[3];
-    gen_ray(fp, px, fp.row0 + ry, sample, o, d);
-    if (fp.max_iter == 0) return Spawn{d[0], d[1], d[2], wf_miss(o[0], o[1], o[2], d[0], d[1], d[2])};
-    return Spawn{d[0], d[1], d[2], RM_CODE_LIVE};
-}
-
-// floor / sky of a missed ray (wgsl:117-130) -> sample code
-__device__ __noinline__ float wf_miss(float rox, float roy, float roz, float dx, float dy, float dz) {
-    const float ro[3] = {rox, roy, roz}, rd[3] = {dx, dy, dz};
-    float c[3], t;
-    const int cls = shade_miss(ro, rd, c, t);
-    if (cls == 0) return RM_CODE_SKY;
-    return c[0] > 0.2f ? RM_CODE_FLOOR_LIGHT : RM_CODE_FLOOR_DARK;
-}
-
 // normal from the four tetrahedron taps + diffuse term (wgsl:98-105, 138-143) -> sample code
 template <bool EX>
 __device__ __noinline__ float wf_shade(float a0, float a1, float a2, float a3, float hx, float hy, float hz) {
@@ -189,51 +164,78 @@ k_wavefront(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ p
     float spill[RM_STACK_MAX - 1][R];
     RM_FOR_R { meta[r] = 0; iter[r] = 0; dist[r] = 0.f; rdx[r] = rdy[r] = rdz[r] = 0.f; m0[r] = m1[r] = m2[r] = 0.f; }
 
-    int cur_buf = 0, pool_next = TILE_RAYS;
+    int cur_buf = 0, pool_next = TILE_RAYS, ring_head = 0, ring_count = 0;
     uint32_t cur_tile = 0;
     bool exhausted = false;
     uint32_t c_step = 0, c_hit = 0, c_floor = 0, c_sample = 0;
 
     for (;;) {
-        // ---------------- refill empty slots from the tile pool (ballot compaction) ----------------
-        if (pool_next >= TILE_RAYS && !exhausted) {  // open the next tile if a buffer is free
-            int b = -1;
+        // ---------------- ray generation: 32 rays per pass, one per lane, into the ready ring -------
+        // (full-lane work; the miss colour depends only on the ray, so it is computed here too and
+        // parked as the sample's default result — a ray that misses later has nothing left to do)
+        if (ring_count <= RING_N - 32) {  // warp-uniform
+            if (pool_next >= TILE_RAYS && !exhausted) {  // open the next tile if a buffer is free
+                int b = -1;
 #pragma unroll
-            for (int k = WF_K - 1; k >= 0; --k) if (ws.tile[k] < 0) b = k;
-            if (b >= 0) {
-                unsigned t = 0;
-                if (lane == 0) t = atomicAdd(tile_counter, 1u);
-                t = __shfl_sync(FULL, t, 0);
-                if (t >= n_tiles) {
-                    exhausted = true;
-                } else {
-                    cur_buf = b; cur_tile = t; pool_next = 0;
-                    if (lane == 0) { ws.tile[b] = (int)t; ws.remaining[b] = TILE_RAYS; }
-                    __syncwarp();
+                for (int k = WF_K - 1; k >= 0; --k) if (ws.tile[k] < 0) b = k;
+                if (b >= 0) {
+                    unsigned t = 0;
+                    if (lane == 0) t = atomicAdd(tile_counter, 1u);
+                    t = __shfl_sync(FULL, t, 0);
+                    if (t >= n_tiles) {
+                        exhausted = true;
+                    } else {
+                        cur_buf = b; cur_tile = t; pool_next = 0;
+                        if (lane == 0) { ws.tile[b] = (int)t; ws.remaining[b] = TILE_RAYS; }
+                        __syncwarp();
+                    }
                 }
             }
+            if (pool_next < TILE_RAYS) {
+                const uint32_t q = (uint32_t)pool_next + lane;  // sample = pool_next/32, pixel = lane
+                const uint32_t tx = cur_tile % tiles_x, ty = cur_tile / tiles_x;
+                const uint32_t px = tx * TILE_W + (lane & 7u), ry = ty * TILE_H + (lane >> 3);
+                const bool inside = px < fp.W && ry < fp.nrows;
+                float code = RM_CODE_SKY;
+                float o[3], d[3] = {0.f, 0.f, 0.f};
+                if (inside) {
+                    gen_ray(fp, px, fp.row0 + ry, q >> 5, o, d);
+                    float c[3], t;
+                    const int cls = shade_miss(ro, d, c, t);  // wgsl:117-130
+                    code = cls == 0 ? RM_CODE_SKY : (c[0] > 0.2f ? RM_CODE_FLOOR_LIGHT : RM_CODE_FLOOR_DARK);
+                    if (COUNT) ++c_sample;
+                }
+                ws.codes[cur_buf][q] = code;
+                const bool live = inside && fp.max_iter > 0;
+                const unsigned lm = __ballot_sync(FULL, live);
+                if (live) {
+                    const int pos = (ring_head + ring_count + __popc(lm & lt_mask)) & (RING_N - 1);
+                    ws.ring[pos] = make_float4(d[0], d[1], d[2],
+                                               __uint_as_float(q | ((uint32_t)cur_buf << M_BUF_SHIFT) | M_LIVE));
+                } else {
+                    if (COUNT && code != RM_CODE_SKY) ++c_floor;
+                    atomicSub(&ws.remaining[cur_buf], 1);  // nothing to march
+                }
+                ring_count += __popc(lm);
+                pool_next += 32;
+                __syncwarp();
+            }
         }
+        // ---------------- refill empty slots from the ready ring (ballot compaction) ----------------
         RM_FOR_R {
             const bool empty = !(meta[r] & M_LIVE);
             const unsigned em = __ballot_sync(FULL, empty);
-            if (em != 0 && pool_next < TILE_RAYS) {  // warp-uniform
+            if (em != 0 && ring_count > 0) {  // warp-uniform
                 const int rank = __popc(em & lt_mask);
-                const int take = min(__popc(em), TILE_RAYS - pool_next);
+                const int take = min(__popc(em), ring_count);
                 if (empty && rank < take) {
-                    const uint32_t q = (uint32_t)(pool_next + rank);
-                    const Spawn sp = wf_spawn(fp, q, cur_tile, tiles_x);
-                    if (COUNT && sp.code != RM_CODE_SKY) ++c_sample;
-                    if (sp.code == RM_CODE_LIVE) {
-                        rdx[r] = sp.x; rdy[r] = sp.y; rdz[r] = sp.z;
-                        dist[r] = 0.0f; iter[r] = 0;
-                        meta[r] = q | ((uint32_t)cur_buf << M_BUF_SHIFT) | M_LIVE;
-                    } else {
-                        if (COUNT && (sp.code == RM_CODE_FLOOR_DARK || sp.code == RM_CODE_FLOOR_LIGHT)) ++c_floor;
-                        ws.codes[cur_buf][q] = sp.code;
-                        atomicSub(&ws.remaining[cur_buf], 1);
-                    }
+                    const float4 e = ws.ring[(ring_head + rank) & (RING_N - 1)];
+                    rdx[r] = e.x; rdy[r] = e.y; rdz[r] = e.z;
+                    dist[r] = 0.0f; iter[r] = 0;
+                    meta[r] = __float_as_uint(e.w);
                 }
-                pool_next += take;
+                ring_head = (ring_head + take) & (RING_N - 1);
+                ring_count -= take;
             }
         }
         // ---------------- termination ----------------
@@ -283,10 +285,11 @@ k_wavefront(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ p
                         dist[r] = A::add(dist[r], s[r]);  // wgsl:114
                         miss = ++iter[r] >= fp.max_iter;
                     }
-                    if (miss) {
-                        code = wf_miss(ro[0], ro[1], ro[2], rdx[r], rdy[r], rdz[r]);
-                        if (COUNT && code != RM_CODE_SKY) ++c_floor;
-                        done = true;
+                    if (miss) {  // floor / sky colour was parked at generation time
+                        const uint32_t b = (meta[r] >> M_BUF_SHIFT) & 3u;
+                        if (COUNT && ws.codes[b][meta[r] & M_Q] != RM_CODE_SKY) ++c_floor;
+                        atomicSub(&ws.remaining[b], 1);
+                        meta[r] = 0;
                     }
                 }
             } else if (st < 4) {
