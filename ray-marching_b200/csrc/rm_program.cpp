@@ -105,6 +105,11 @@ int decode_program(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, 
             if (c.type == RM_OP_SMOOTH_UNION) set_k(in, c.p[0]);
             depth -= 1;
         }
+        {
+            const uint32_t src = opcode_src(in.op), cb = opcode_cb(in.op);
+            static const uint32_t cb_flag[6] = {FLAG_FIRST, FLAG_PUSH, FLAG_UNION, FLAG_SUB, FLAG_INTER, FLAG_SMOOTH};
+            in.flags |= cb_flag[cb] | (src == SRC_BOX ? FLAG_BOX : 0u) | (src == SRC_POP ? FLAG_POP : 0u);
+        }
         prog.insns.push_back(in);
     }
     if (depth < 1) return RM_E_STACK_UNBALANCED;

@@ -37,7 +37,19 @@ enum : uint32_t {
     SRC_SPHERE = 1,  // b = sphere(p), a = acc       wgsl:229-233
     SRC_BOX = 2,     // b = box(p),    a = acc       wgsl:235-240
 };
-enum : uint32_t { FLAG_K_POW2 = 1u };  // 1/k is exact: multiply instead of divide in exact mode
+// RmInsn::flags: one-hot description of the fused op, so that the interpreter dispatches with
+// single-bit tests (LOP3 -> predicate, branch) in frequency order instead of a jump table.
+enum : uint32_t {
+    FLAG_K_POW2 = 1u << 0,  // 1/k is exact: multiply instead of divide in exact mode
+    FLAG_BOX = 1u << 1,
+    FLAG_POP = 1u << 2,
+    FLAG_SMOOTH = 1u << 3,
+    FLAG_UNION = 1u << 4,
+    FLAG_SUB = 1u << 5,
+    FLAG_INTER = 1u << 6,
+    FLAG_PUSH = 1u << 7,
+    FLAG_FIRST = 1u << 8,
+};
 
 // RmInsn::op is a DENSE fused opcode 0..15 so that the interpreter dispatches through a single
 // jump table:  0..3 = POP x {UNION,SUB,INTER,SMOOTH};  4..9 = SPHERE x {FIRST..SMOOTH};

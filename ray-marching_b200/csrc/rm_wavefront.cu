@@ -26,11 +26,14 @@ constexpr uint32_t M_Q = 0x1ffu;          // sample slot in tile: sample*32 + pi
 constexpr uint32_t M_BUF_SHIFT = 9;       // 2 bits
 constexpr uint32_t M_STATE_SHIFT = 11;    // 3 bits: 0 MARCH, 1..4 TAP0..TAP3
 constexpr uint32_t M_LIVE = 1u << 14;
+constexpr uint32_t M_ITER_SHIFT = 16;      // 16 bits: march iterations done (max_iter <= 65535)
 
 constexpr int RING_N = 64;  // ready-ray ring: two batches of 32
+template <int R>
 struct WarpShared {
     float codes[WF_K][TILE_RAYS];  // per-sample result codes; pre-set to the ray's miss code
     float4 ring[RING_N];           // generated rays waiting for a slot: dir.xyz + meta bits
+    float taps[3][32 * R];         // first three normal taps of rays that hit (rarely touched)
     int remaining[WF_K];
     int tile[WF_K];  // tile id, or -1 when the buffer is free
 };
@@ -66,6 +69,10 @@ __device__ __forceinline__ float prim_eval(float x, float y, float z, const floa
                                         q2.x, k_pow2);                                                      \
         break;
 
+// acc = min(acc, v) etc. with the accumulator tied to one register (no copies around the loop)
+__device__ __forceinline__ void acc_min(float &acc, float v) { asm("min.f32 %0, %0, %1;" : "+f"(acc) : "f"(v)); }
+__device__ __forceinline__ void acc_max(float &acc, float v) { asm("max.f32 %0, %0, %1;" : "+f"(acc) : "f"(v)); }
+
 template <bool EX, int R>
 __device__ __forceinline__ void map_evalR(const float4 *__restrict__ prog, uint32_t n_insn, float max_dist,
                                           const float (&px)[R], const float (&py)[R], const float (&pz)[R],
@@ -78,26 +85,43 @@ __device__ __forceinline__ void map_evalR(const float4 *__restrict__ prog, uint3
 #pragma unroll 1
     for (uint32_t i = 0; i < n_insn; ++i) {
         const float4 q0 = prog[3 * i], q1 = prog[3 * i + 1], q2 = prog[3 * i + 2];
-        const uint32_t op = __float_as_uint(q2.y), slot = __float_as_uint(q2.z);
-        const bool k_pow2 = (__float_as_uint(q2.w) & FLAG_K_POW2) != 0;
-        switch (op) {
-            RM_PRIM_CASES(SRC_SPHERE)
-            RM_PRIM_CASES(SRC_BOX)
+        const uint32_t fl = __float_as_uint(q2.w);
+        // Dispatch on one-hot flag bits, most frequent fused ops first (primitive kind, then
+        // smooth-union / union / subtraction / intersection / push / first).
+        if (!(fl & FLAG_POP)) {
+            float v[R];
+            if (fl & FLAG_BOX) {
+                RM_FOR_R v[r] = sd_box<EX>(px[r], py[r], pz[r], q0.x, q0.y, q0.z, q0.w, q1.x, q1.y);
+            } else {
+                RM_FOR_R v[r] = sd_sphere<EX>(px[r], py[r], pz[r], q0.x, q0.y, q0.z, q0.w);
+            }
+            if (fl & FLAG_SMOOTH) {
+                RM_FOR_R acc[r] = op_smooth<EX>(acc[r], v[r], q1.z, q1.w, q2.x, (fl & FLAG_K_POW2) != 0);
+            } else if (fl & FLAG_UNION) {
+                RM_FOR_R acc_min(acc[r], v[r]);
+            } else if (fl & FLAG_SUB) {
+                RM_FOR_R acc_max(acc[r], -v[r]);
+            } else if (fl & FLAG_INTER) {
+                RM_FOR_R acc_max(acc[r], v[r]);
+            } else {
+                if (fl & FLAG_PUSH) {
+                    const uint32_t slot = __float_as_uint(q2.z);
+                    RM_FOR_R spill[slot][r] = acc[r];
+                }
+                RM_FOR_R acc[r] = v[r];
+            }
+        } else {
             // binary operator on two subtrees: right operand = accumulator, left = spilled entry
-            case RM_OPC(SRC_POP, CB_UNION):
+            const uint32_t slot = __float_as_uint(q2.z);
+            if (fl & FLAG_SMOOTH) {
+                RM_FOR_R acc[r] = op_smooth<EX>(spill[slot][r], acc[r], q1.z, q1.w, q2.x, (fl & FLAG_K_POW2) != 0);
+            } else if (fl & FLAG_UNION) {
                 RM_FOR_R acc[r] = fminf(spill[slot][r], acc[r]);
-                break;
-            case RM_OPC(SRC_POP, CB_SUB):
+            } else if (fl & FLAG_SUB) {
                 RM_FOR_R acc[r] = fmaxf(spill[slot][r], -acc[r]);
-                break;
-            case RM_OPC(SRC_POP, CB_INTER):
+            } else {
                 RM_FOR_R acc[r] = fmaxf(spill[slot][r], acc[r]);
-                break;
-            case RM_OPC(SRC_POP, CB_SMOOTH):
-                RM_FOR_R acc[r] = op_smooth<EX>(spill[slot][r], acc[r], q1.z, q1.w, q2.x, k_pow2);
-                break;
-            default:
-                break;
+            }
         }
     }
 }
@@ -129,17 +153,17 @@ __device__ __noinline__ uint32_t wf_resolve(const float *codes, int lane) {
 }
 
 template <bool EX, int R, bool COUNT>
-__global__ void __launch_bounds__(WF_WARPS * 32)
+__global__ void __launch_bounds__(WF_WARPS * 32, (R >= 8 ? 4 : (R == 4 ? 5 : 6)))
 k_wavefront(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ prog_g, uint8_t *__restrict__ dst,
             size_t pitch, unsigned int *__restrict__ tile_counter, unsigned long long *__restrict__ counters) {
     using A = Arith<EX>;
     extern __shared__ float4 smem_f4[];
     float4 *s_prog = smem_f4;
     const uint32_t nq = fp.n_insn * 3;
-    WarpShared *s_warps = reinterpret_cast<WarpShared *>(smem_f4 + nq);
+    WarpShared<R> *s_warps = reinterpret_cast<WarpShared<R> *>(smem_f4 + nq);
     for (uint32_t i = threadIdx.x; i < nq; i += blockDim.x) s_prog[i] = reinterpret_cast<const float4 *>(prog_g)[i];
     const int lane = threadIdx.x & 31;
-    WarpShared &ws = s_warps[threadIdx.x >> 5];
+    WarpShared<R> &ws = s_warps[threadIdx.x >> 5];
     if (lane < WF_K) {
         ws.remaining[lane] = 0;
         ws.tile[lane] = -1;
@@ -159,10 +183,10 @@ k_wavefront(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ p
         ro[0] = ro4[0]; ro[1] = ro4[1]; ro[2] = ro4[2];
     }
 
-    float rdx[R], rdy[R], rdz[R], dist[R], m0[R], m1[R], m2[R];
-    uint32_t meta[R], iter[R];
+    float rdx[R], rdy[R], rdz[R], dist[R];
+    uint32_t meta[R];
     float spill[RM_STACK_MAX - 1][R];
-    RM_FOR_R { meta[r] = 0; iter[r] = 0; dist[r] = 0.f; rdx[r] = rdy[r] = rdz[r] = 0.f; m0[r] = m1[r] = m2[r] = 0.f; }
+    RM_FOR_R { meta[r] = 0; dist[r] = 0.f; rdx[r] = rdy[r] = rdz[r] = 0.f; }
 
     int cur_buf = 0, pool_next = TILE_RAYS, ring_head = 0, ring_count = 0;
     uint32_t cur_tile = 0;
@@ -231,7 +255,7 @@ k_wavefront(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ p
                 if (empty && rank < take) {
                     const float4 e = ws.ring[(ring_head + rank) & (RING_N - 1)];
                     rdx[r] = e.x; rdy[r] = e.y; rdz[r] = e.z;
-                    dist[r] = 0.0f; iter[r] = 0;
+                    dist[r] = 0.0f;
                     meta[r] = __float_as_uint(e.w);
                 }
                 ring_head = (ring_head + take) & (RING_N - 1);
@@ -283,7 +307,8 @@ k_wavefront(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ p
                     bool miss = s[r] > fp.max_dist;  // wgsl:109-111
                     if (!miss) {
                         dist[r] = A::add(dist[r], s[r]);  // wgsl:114
-                        miss = ++iter[r] >= fp.max_iter;
+                        meta[r] += 1u << M_ITER_SHIFT;
+                        miss = (meta[r] >> M_ITER_SHIFT) >= fp.max_iter;
                     }
                     if (miss) {  // floor / sky colour was parked at generation time
                         const uint32_t b = (meta[r] >> M_BUF_SHIFT) & 3u;
@@ -293,14 +318,13 @@ k_wavefront(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ p
                     }
                 }
             } else if (st < 4) {
-                if (st == 1) m0[r] = s[r];
-                else if (st == 2) m1[r] = s[r];
-                else m2[r] = s[r];
+                ws.taps[st - 1][r * 32 + lane] = s[r];
                 meta[r] += 1u << M_STATE_SHIFT;
             } else {
                 const float hx = A::mad(rdx[r], dist[r], ro[0]), hy = A::mad(rdy[r], dist[r], ro[1]),
                             hz = A::mad(rdz[r], dist[r], ro[2]);
-                code = wf_shade<EX>(m0[r], m1[r], m2[r], s[r], hx, hy, hz);
+                code = wf_shade<EX>(ws.taps[0][r * 32 + lane], ws.taps[1][r * 32 + lane], ws.taps[2][r * 32 + lane], s[r],
+                                    hx, hy, hz);
                 if (COUNT) ++c_hit;
                 done = true;
             }
@@ -358,7 +382,7 @@ template <bool EX, int R, bool COUNT>
 cudaError_t launch_t(WavefrontState *ws, const FrameParams &fp, const RmInsn *prog, uint8_t *dst, size_t pitch,
                      unsigned long long *counters, unsigned int *tc, cudaStream_t st) {
     auto kern = k_wavefront<EX, R, COUNT>;
-    const size_t smem = (size_t)fp.n_insn * sizeof(RmInsn) + WF_WARPS * sizeof(WarpShared);
+    const size_t smem = (size_t)fp.n_insn * sizeof(RmInsn) + WF_WARPS * sizeof(WarpShared<R>);
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     int per_sm = 0;
@@ -398,8 +422,8 @@ cudaError_t launch_wavefront(WavefrontState *ws, bool exact, const FrameParams &
     if (e != cudaSuccess) return e;
     static const int kR = [] {
         const char *s = std::getenv("RM_WF_R");
-        const int v = s ? std::atoi(s) : 4;
-        return (v == 1 || v == 2 || v == 4 || v == 8) ? v : 4;
+        const int v = s ? std::atoi(s) : 8;
+        return (v == 1 || v == 2 || v == 4 || v == 8) ? v : 8;
     }();
 #define RM_WF_DISPATCH(EXV, RV)                                                                        \
     (counters ? launch_t<EXV, RV, true>(ws, fp, prog_dev, dst, pitch, counters, tc, st)                \

@@ -198,7 +198,7 @@ def test_limits_are_runtime_values(rm, ctx):
     cmd, words = h.scene_s1()
     W, H = 96, 64
     u = h.orbit_uniforms(W, H, yaw=0.6, pitch=0.4)
-    for lim in [(0.05, 50.0, 20), (0.001, 100.0, 7), (0.01, 100.0, 0)]:
+    for lim in [(0.05, 50.0, 20), (0.001, 100.0, 7), (0.01, 100.0, 0), (0.01, 100.0, 70000)]:
         ctx.set_limits(*lim)
         ctx.set_mode(rm.MODE_EXACT)
         img = ctx.render(u, cmd, words, W, H)
