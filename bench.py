@@ -1,19 +1,24 @@
 #!/usr/bin/env python
-"""bench.py — headline benchmark of the sphere-tracing render pass (BASELINE.json metric).
+"""bench.py — headline benchmark of the sphere-tracing render pass (BASELINE.json metric:
+"Mrays/s and FPS at 4K on fixed CSG scene, 1/2/4/8 B200; % FP32 roofline").
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--mode fast|exact]
-                  [--workload cfg3|cfg2|cfg1] [--kernel wavefront|simple]
+                  [--workload cfg3|cfg2|cfg1|cfg4|cfg5] [--kernel wavefront|simple]
 
-A "step" is one pass of the hot path over one frame: rm_paint of the workload's frame.  Workload at
-N=1 = BASELINE.json configs[2]: the deep CSG scene S2 (64 graph nodes, smooth-min blends) at
-3840x2160 on 1 B200 — the configuration the metric "Mrays/s and FPS at 4K" is quoted on.
-N>1 (torchrun, one rank per GPU): every rank renders its own 4K frame of an orbit-pose batch
-(frame-parallel, no data-path collective) -> "scaling": "weak".
-Prints ONE JSON line on rank 0 (contract in the task statement).
+A "step" is one pass of the hot path over one batch: rm_paint of the workload's frame(s).
+  cfg3 (default)  configs[2]: deep CSG scene S2 (64 graph nodes, smooth-min) at 3840x2160 — the config
+                  the metric is quoted on.  N>1: every rank renders its own 4K frame of an orbit-pose
+                  batch per step (frame-parallel, no data-path collective)      -> "scaling": "weak"
+  cfg4            configs[3]: ONE 7680x4320 S2 frame per step, interleaved 16-row strips over the ranks,
+                  packed bands gathered to rank 0 over NCCL and re-ordered        -> "scaling": "strong"
+  cfg5            configs[4]: 1024 orbit poses of S1 at 1080p per step, poses sharded by frame -> "strong"
+  cfg1 / cfg2     configs[0] / configs[1] single-GPU parity-sized cases
+Prints ONE JSON line on rank 0.
 """
 from __future__ import annotations
 
 import argparse
+import importlib
 import json
 import math
 import os
@@ -27,34 +32,30 @@ import numpy as np
 
 ROOT = Path(__file__).resolve().parent
 sys.path.insert(0, str(ROOT))
-sys.path.insert(0, str(ROOT / "tests"))
 
 WORKLOADS = {
-    # name: (scene, W, H, description)
-    "cfg1": ("S0", 640, 480, "configs[0]: single-sphere S0 640x480"),
-    "cfg2": ("S1", 1920, 1080, "configs[1]: editor CSG scene S1 (box U sphere \\ sphere) 1920x1080"),
-    "cfg3": ("S2", 3840, 2160, "configs[2]: deep CSG S2 (32 leaves, 28 smooth-unions, 3 subtractions; 251 words) 3840x2160"),
+    "cfg1": ("S0", 640, 480, 1, "configs[0]: single-sphere S0 640x480"),
+    "cfg2": ("S1", 1920, 1080, 1, "configs[1]: editor CSG scene S1 (box U sphere \\ sphere) 1920x1080"),
+    "cfg3": ("S2", 3840, 2160, 1, "configs[2]: deep CSG S2 (32 leaves, 28 smooth-unions, 3 subtractions; 251 words) 3840x2160"),
+    "cfg4": ("S2", 7680, 4320, 1, "configs[3]: S2 at 7680x4320, one frame row-sharded in interleaved 16-row strips, NCCL gather to rank 0"),
+    "cfg5": ("S1", 1920, 1080, 1024, "configs[4]: 1024 orbit poses of S1 at 1920x1080, frame-parallel"),
 }
-# algorithmic FLOP table, SURVEY.md §8(a)/(d)
-F_STEP, F_HIT, F_SAMPLE, F_FLOOR, F_PIXEL = 9, 75, 87, 14, 31
+F_STEP, F_HIT, F_SAMPLE, F_FLOOR, F_PIXEL = 9, 75, 87, 14, 31  # SURVEY.md §8(a) FLOP table
+OP_FLOPS = {0: (10, 4), 1: (22, 6), 100: (1, 0), 101: (2, 0), 102: (1, 0), 103: (10, 1)}  # opcode: (flops, params)
 
 
 def f_map(words, cmd_count) -> int:
-    import helpers as h
-    per = {h.OP_SPHERE: (10, 4), h.OP_BOX: (22, 6), h.OP_UNION: (1, 0), h.OP_SUBTRACTION: (2, 0),
-           h.OP_INTERSECTION: (1, 0), h.OP_SMOOTH_UNION: (10, 1)}
     i = fl = 0
     for _ in range(cmd_count):
-        f, n = per[int(words[i])]
+        f, n = OP_FLOPS[int(words[i])]
         fl += f
         i += 1 + n
     return fl
 
 
-def frame_flops(counters, fmap, W, H) -> float:
+def frame_flops(counters, fmap, n_pixels) -> float:
     n_step, n_hit, n_floor, n_sample = (float(x) for x in counters)
-    n_eval = n_step + 4 * n_hit
-    return n_eval * fmap + F_STEP * n_step + F_HIT * n_hit + F_SAMPLE * n_sample + F_FLOOR * n_floor + F_PIXEL * W * H
+    return (n_step + 4 * n_hit) * fmap + F_STEP * n_step + F_HIT * n_hit + F_SAMPLE * n_sample + F_FLOOR * n_floor + F_PIXEL * n_pixels
 
 
 class ClockSampler:
@@ -74,7 +75,7 @@ class ClockSampler:
                     self.rows.append([x.strip() for x in out.split(",")])
             except Exception:
                 pass
-            self._stop.wait(0.1)
+            self._stop.wait(0.05)
 
     def __enter__(self):
         self._t = threading.Thread(target=self._run, daemon=True)
@@ -96,22 +97,22 @@ class ClockSampler:
                 "samples": len(self.rows), "power_w_max": max(pw) if pw else None}
 
 
-def cpu_sample_rows(H: int, n: int = 108):
+def cpu_sample_rows(H: int, n: int):
     step = max(1, H // n)
     return list(range(step // 2, H, step))[:n]
 
 
-def run_cpu_oracle(scene, W, H, uniforms, rows):
-    """Times the CPU oracle (all host threads) on single rows of the workload frame."""
+def run_cpu_oracle(cmd, words, W, H, uniforms, rows):
+    """Times the CPU oracle (all host threads) on single rows of the workload frame.  The oracle is
+    test infrastructure: this is the cpu_baseline / --impl reference leg, never the product path."""
+    sys.path.insert(0, str(ROOT / "tests"))
     import helpers as h
-    cmd, words = h.SCENES[scene]()
     nthreads = h.oracle_lib().rmo_num_threads()
     t0 = time.perf_counter()
     for r in rows:
         h.oracle_render(uniforms, cmd, words, W, H, row0=r, nrows=1)
     dt = time.perf_counter() - t0
-    rays = len(rows) * W * 16
-    return rays / dt / 1e6, nthreads, dt
+    return len(rows) * W * 16 / dt / 1e6, nthreads, dt
 
 
 def main():
@@ -123,32 +124,36 @@ def main():
     ap.add_argument("--mode", default="fast", choices=["fast", "exact"])
     ap.add_argument("--kernel", default="wavefront", choices=["wavefront", "simple"])
     ap.add_argument("--workload", default="cfg3", choices=list(WORKLOADS))
+    ap.add_argument("--poses", type=int, default=0, help="cfg5: override the 1024-pose batch size")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
 
-    import helpers as h
+    import rm_import
+    rm = rm_import.load()
+    scenes = importlib.import_module("ray_marching_b200.scenes")
+    sharding = importlib.import_module("ray_marching_b200.sharding")
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
-    scene, W, H, desc = WORKLOADS[args.workload]
-    cmd, words = h.SCENES[scene]()
+    scene, W, H, n_poses, desc = WORKLOADS[args.workload]
+    if args.workload == "cfg5" and args.poses:
+        n_poses = args.poses
+    cmd, words = scenes.program(scene)  # flattened by the C++ host (BuildCommands)
     warm = max(args.warmup, 3)
     yaw0, pitch = (0.0, 0.0) if scene == "S0" else (0.6, 0.4)
-    yaw = yaw0 + 2 * math.pi * rank / max(world, 1)
-    uniforms = h.orbit_uniforms(W, H, yaw=yaw, pitch=pitch)
-    rays_per_frame = W * H * 16
-    config = {"workload": desc, "scene": scene, "width": W, "height": H, "samples_per_pixel": 16,
-              "rays_per_step": rays_per_frame, "limits": [0.01, 100.0, 100], "pose": "orbit yaw=0.6+2pi*rank/N pitch=0.4 r=5",
-              "sharding": "one frame per rank per step (frame-parallel), no collective", "l2": "flushed between timed steps (256 MiB memset, untimed)"}
+    strong = args.workload in ("cfg4", "cfg5")
+    config = {"workload": desc, "scene": scene, "width": W, "height": H, "samples_per_pixel": 16, "frames_per_step": n_poses if strong else world,
+              "limits": [0.01, 100.0, 100], "l2": "flushed between timed steps (256 MiB memset, untimed)"}
 
-    # ------------------------------------------------------------------ reference arm (CPU)
+    # ------------------------------------------------------------------ reference arm (CPU oracle)
     if args.impl == "reference":
         if rank != 0:
             return 0
+        u = scenes.orbit_uniforms(W, H, yaw=yaw0, pitch=pitch)
         rows = cpu_sample_rows(H, 54)
         vals = []
         for s in range(warm + args.steps):
-            v, nthreads, dt = run_cpu_oracle(scene, W, H, h.orbit_uniforms(W, H, yaw=yaw0, pitch=pitch), rows)
+            v, nthreads, dt = run_cpu_oracle(cmd, words, W, H, u, rows)
             if s >= warm:
                 vals.append((v, dt))
             if s == 0 and dt * (warm + args.steps) > 240:  # keep the whole run within a few minutes
@@ -156,113 +161,179 @@ def main():
         v = float(np.mean([x[0] for x in vals]))
         ms = float(np.mean([x[1] for x in vals])) * 1e3
         sample = f"{len(rows)} evenly spaced rows of the {W}x{H} {scene} frame per step ({len(rows) * W * 16} rays)"
-        line = {"impl": "reference", "metric": "Mrays/s", "value": v, "unit": "Mrays/s", "n_gpus": args.gpus,
-                "steps": args.steps, "warmup": warm, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
-                "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config,
-                "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": nthreads, "kind": "port", "sample": sample},
-                "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-                "note": "reference = CPU oracle port of ray_marching.wgsl (the Rust/WGSL reference cannot run here: no rustc, no graphics stack)"}
-        print(json.dumps(line))
+        print(json.dumps({
+            "impl": "reference", "metric": "Mrays/s", "value": v, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": warm, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong" if strong else "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config,
+            "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": nthreads, "kind": "port", "sample": sample},
+            "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "note": "reference arm = CPU oracle port of ray_marching.wgsl; the Rust/WGSL reference itself cannot run on this box "
+                    "(no rustc, no graphics stack: wgpu-on-lavapipe unavailable)"}))
         return 0
 
     # ------------------------------------------------------------------ B200 arm
     import torch
-    import rm_import
-    rm = rm_import.load()
     dist = None
+    torch.cuda.set_device(local_rank)
     if world > 1:
         import torch.distributed as dist
-        torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    dev = torch.device("cuda", local_rank)
     ctx = rm.Context(local_rank)
     ctx.set_mode(rm.MODE_FAST if args.mode == "fast" else rm.MODE_EXACT)
     ctx.set_kernel(rm.KERNEL_WAVEFRONT if args.kernel == "wavefront" else rm.KERNEL_SIMPLE)
+    stream = torch.cuda.current_stream(dev)
+    sp = stream.cuda_stream
 
     def barrier():
         if dist is not None:
             dist.barrier()
-        torch.cuda.synchronize(local_rank)
+        torch.cuda.synchronize(dev)
         ctx.sync()
 
-    # work counters of this rank's frame (untimed) -> algorithmic FLOPs of one step
-    ctx.prepare(uniforms, cmd, words)
+    # ---- per-workload step --------------------------------------------------------------------
+    if args.workload == "cfg4":
+        strip = sharding.DEFAULT_STRIP_ROWS
+        rows_max = sharding.max_local_rows(H, strip, world)
+        band = torch.zeros((rows_max, W, 4), dtype=torch.uint8, device=dev)
+        gathered = [torch.zeros_like(band) for _ in range(world)] if (rank == 0 and world > 1) else None
+        uniforms = scenes.orbit_uniforms(W, H, yaw=yaw0, pitch=pitch)
+        ctx.prepare(uniforms, cmd, words)
+        rays_local = sharding.local_rows(H, strip, rank, world) * W * 16
+        rays_step_total = W * H * 16
+        config.update(sharding=f"interleaved strips of {strip} rows, strip s -> rank s % N; NCCL gather + indexed re-order on rank 0")
+        frame_out = {}
+
+        def step():
+            ctx.paint_strips(W, H, strip, rank, world, band.data_ptr(), W * 4, sp)
+            if dist is not None:
+                dist.gather(band, gathered, dst=0)
+                if rank == 0:
+                    frame_out["f"] = sharding.reassemble(torch.stack(gathered), H, strip, world)
+            else:
+                frame_out["f"] = band
+
+        def count_step():
+            ctx.paint_strips(W, H, strip, rank, world, band.data_ptr(), W * 4, sp)
+        n_pixels_local = rays_local // 16
+    elif args.workload == "cfg5":
+        my = list(sharding.pose_slice(n_poses, rank, world))
+        all_u = scenes.orbit_pose_batch(W, H, n_poses, pitch=0.4)
+        my_u = b"".join(all_u[k * 144:(k + 1) * 144] for k in my)
+        ctx.prepare(all_u[:144], cmd, words)
+        rays_local = len(my) * W * H * 16
+        rays_step_total = n_poses * W * H * 16
+        config.update(sharding="pose k -> rank k % N; frames stay on their GPU (throughput mode)", poses=n_poses)
+
+        def step():
+            ctx.paint_poses(my_u, len(my), W, H, None, 0, 0, sp)
+        count_step = step
+        n_pixels_local = len(my) * W * H
+    else:
+        yaw = yaw0 + 2 * math.pi * rank / max(world, 1)
+        uniforms = scenes.orbit_uniforms(W, H, yaw=yaw, pitch=pitch)
+        ctx.prepare(uniforms, cmd, words)
+        rays_local = W * H * 16
+        rays_step_total = rays_local * world
+        config.update(sharding="one frame per rank per step (orbit yaw = 0.6 + 2*pi*rank/N), no collective")
+
+        def step():
+            ctx.paint(W, H, 0, H, None, 0, sp)
+        count_step = step
+        n_pixels_local = W * H
+
+    # work counters of this rank's step (untimed) -> algorithmic FLOPs
     ctx.set_counters(True)
-    ctx.paint(W, H)
+    count_step()
     counters = ctx.get_counters()
     ctx.set_counters(False)
     fmap = f_map(words, cmd)
-    flops = frame_flops(counters, fmap, W, H)
+    flops = frame_flops(counters, fmap, n_pixels_local)
     peak = ctx.fp32_peak()
 
     for _ in range(warm):
-        ctx.paint(W, H)
+        step()
     barrier()
     launches0 = ctx.launch_count
-    per_step = []
+    ev0 = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+    ev1 = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     with ClockSampler(local_rank) as clk:
         t_wall0 = time.perf_counter()
-        for _ in range(args.steps):
-            ctx.flush_l2()
-            ctx.mark(0)
-            ctx.paint(W, H)
-            ctx.mark(1)
-            per_step.append(ctx.elapsed_ms(0, 1))
+        for i in range(args.steps):
+            flush.zero_()                 # L2 flush, outside the timed event pair
+            ev0[i].record(stream)
+            step()
+            ev1[i].record(stream)
         barrier()
         t_wall = time.perf_counter() - t_wall0
     launches = ctx.launch_count - launches0
+    per_step = [a.elapsed_time(b) for a, b in zip(ev0, ev1)]
     ms_local = float(np.mean(per_step))
 
-    # e2e: host buffers in, host framebuffer out, through the C ABI (prepare + paint + download)
-    pinned = rm.PinnedBuffer(W * H * 4)
-    for _ in range(2):
-        ctx.prepare(uniforms, cmd, words)
-        ctx.paint(W, H)
-        ctx.download(pinned)
-    barrier()
-    n_e2e = max(3, min(args.steps, 10))
-    t0 = time.perf_counter()
-    for _ in range(n_e2e):
-        ctx.prepare(uniforms, cmd, words)
-        ctx.paint(W, H)
-        ctx.download(pinned)
-    e2e_ms_local = (time.perf_counter() - t0) * 1e3 / n_e2e
+    # ---- e2e: host buffers in, host result out, through the public C-ABI calls (cfg1-3: prepare + paint + download)
+    e2e_ms_local, h2d, d2h = None, 0, 0
+    if not strong:
+        pinned = rm.PinnedBuffer(W * H * 4)
+        n_e2e = max(3, min(args.steps, 10))
+        for it in range(2 + n_e2e):
+            if it == 2:
+                barrier()
+                t0 = time.perf_counter()
+            ctx.prepare(uniforms, cmd, words)      # H2D: uniforms + decoded program
+            ctx.paint(W, H)
+            ctx.download(pinned)                   # D2H: the RGBA8 frame (synchronises)
+        e2e_ms_local = (time.perf_counter() - t0) * 1e3 / n_e2e
+        h2d, d2h = 144 + 12 + 4 + int(len(words)) * 4, W * H * 4
+        pinned.free()
+    elif args.workload == "cfg4":
+        host_frame = torch.empty((H, W, 4), dtype=torch.uint8).pin_memory() if rank == 0 else None
+        n_e2e = max(3, min(args.steps, 5))
+        for it in range(1 + n_e2e):
+            if it == 1:
+                barrier()
+                t0 = time.perf_counter()
+            ctx.prepare(uniforms, cmd, words)
+            step()
+            if rank == 0:
+                host_frame.copy_(frame_out["f"][:H], non_blocking=False)
+            barrier()
+        e2e_ms_local = (time.perf_counter() - t0) * 1e3 / n_e2e
+        h2d, d2h = 144 + 12 + 4 + int(len(words)) * 4, W * H * 4
 
     if dist is not None:
-        tt = torch.tensor([ms_local, e2e_ms_local], device=f"cuda:{local_rank}", dtype=torch.float64)
+        tt = torch.tensor([ms_local, e2e_ms_local or 0.0], device=dev, dtype=torch.float64)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         ms, e2e_ms = float(tt[0]), float(tt[1])
-        ff = torch.tensor([flops], device=f"cuda:{local_rank}", dtype=torch.float64)
-        dist.all_reduce(ff, op=dist.ReduceOp.SUM)
-        flops_total = float(ff[0])
     else:
-        ms, e2e_ms, flops_total = ms_local, e2e_ms_local, flops
+        ms, e2e_ms = ms_local, e2e_ms_local or 0.0
     if rank == 0:
-        total_rays = rays_per_frame * world
-        value = total_rays / (ms * 1e-3) / 1e6
-        e2e = total_rays / (e2e_ms * 1e-3) / 1e6
-        achieved = flops / (ms_local * 1e-3) / 1e12  # this rank's kernel
-        n_insn = 0
-        roof = {"bound": "fp32", "achieved": achieved, "peak": peak["tflops"], "unit": "TFLOP/s",
-                "frac": achieved / peak["tflops"], "traffic": None,
-                "peak_source": "FFMA micro-benchmark run live on this GPU (rm_fp32_peak); MEASURED_PEAKS.json has no FP32 ALU peak",
+        value = rays_step_total / (ms * 1e-3) / 1e6
+        achieved = flops / (ms_local * 1e-3) / 1e12  # rank 0's kernel work over rank 0's device time
+        fb_bytes = n_pixels_local * 4
+        roof = {"bound": "fp32", "achieved": achieved, "peak": peak["tflops"], "unit": "TFLOP/s", "frac": achieved / peak["tflops"],
+                "traffic": None,
+                "peak_source": "FFMA micro-benchmark run live on this GPU (rm_fp32_peak); MEASURED_PEAKS.json has no FP32 ALU peak; "
+                               "nominal 148 SM x 128 lanes x 2 x 1.965 GHz = 74.4",
                 "algorithmic_flops_per_step": flops, "f_map_flops_per_eval": fmap,
                 "counters": {"n_step": int(counters[0]), "n_hit": int(counters[1]), "n_floor": int(counters[2]), "n_sample": int(counters[3])},
-                "framebuffer_gbs": W * H * 4 / (ms_local * 1e-3) / 1e9,
-                "hbm_frac_of_measured": (W * H * 4 / (ms_local * 1e-3) / 1e9) / 6531.9}
+                "framebuffer_gbs": fb_bytes / (ms_local * 1e-3) / 1e9,
+                "hbm_frac_of_measured_6531.9": fb_bytes / (ms_local * 1e-3) / 1e9 / 6531.9}
         line = {"metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": warm,
-                "ms_per_step": ms, "fps": 1e3 / ms * world, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-                "dtype": "f32", "data": "synthetic", "config": dict(config, mode=args.mode, kernel=args.kernel),
-                "clocks": clk.summary(), "gpu_launches": int(launches),
-                "e2e": {"value": e2e, "unit": "Mrays/s", "ms_per_step": e2e_ms, "h2d_bytes_per_step": 144 + 12 + 4 + int(len(words)) * 4,
-                        "d2h_bytes_per_step": W * H * 4},
+                "ms_per_step": ms, "fps": (n_poses if strong else world) * 1e3 / ms, "higher_is_better": True,
+                "scaling": "strong" if strong else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": dict(config, mode=args.mode, kernel=args.kernel), "clocks": clk.summary(), "gpu_launches": int(launches),
                 "roofline": roof, "wall_s_timed_region": t_wall}
+        if e2e_ms:
+            line["e2e"] = {"value": rays_step_total / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": e2e_ms,
+                           "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h}
         if not args.no_cpu_baseline and world == 1:
+            u0 = scenes.orbit_uniforms(W, H, yaw=yaw0, pitch=pitch)
             rows = cpu_sample_rows(H, 108)
-            v, nthreads, dt = run_cpu_oracle(scene, W, H, uniforms, rows)
+            v, nthreads, dt = run_cpu_oracle(cmd, words, W, H, u0, rows)
             line["cpu_baseline"] = {"value": v, "unit": "Mrays/s", "cores": nthreads, "kind": "port",
-                                    "sample": f"{len(rows)} evenly spaced rows of the same {W}x{H} {scene} frame ({len(rows) * W * 16} rays, {dt:.1f} s)"}
+                                    "sample": f"{len(rows)} evenly spaced rows of the {W}x{H} {scene} frame ({len(rows) * W * 16} rays, {dt:.1f} s)"}
         print(json.dumps(line))
-    pinned.free()
     ctx.close()
     if dist is not None:
         dist.barrier()

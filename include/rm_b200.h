@@ -113,6 +113,13 @@ RM_API int rm_validate_program(uint32_t cmd_count, const uint32_t *words, uint32
  * cuda_stream: a cudaStream_t, or NULL for the ctx's own stream.  Asynchronous. */
 RM_API int rm_paint(rm_ctx *ctx, uint32_t W, uint32_t H, uint32_t row0, uint32_t nrows,
                     void *dst_rgba8_dev, size_t pitch_bytes, void *cuda_stream);
+/* Interleaved strips (multi-GPU load balance): shades strips first_strip,
+ * first_strip + strip_step, ... of `strip_rows` rows each (the last strip of the frame may be short)
+ * and packs them contiguously into dst.  *rows_painted receives the number of rows written.
+ * Every pixel is bit-identical to the same pixel of a full-frame rm_paint. */
+RM_API int rm_paint_strips(rm_ctx *ctx, uint32_t W, uint32_t H, uint32_t strip_rows, uint32_t first_strip,
+                           uint32_t strip_step, void *dst_rgba8_dev, size_t pitch_bytes, void *cuda_stream,
+                           uint32_t *rows_painted);
 /* Pose batch (config 5): paints n_poses frames from an array of 144-byte uniform blocks held in
  * HOST memory; frame p goes to dst + p*frame_stride_bytes (device memory), or, when dst is NULL,
  * every frame overwrites the ctx-owned buffer (throughput mode). */

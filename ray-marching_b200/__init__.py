@@ -27,7 +27,7 @@ UNIFORMS_BYTES, LIMITS_BYTES = 144, 12
 # every symbol include/rm_b200.h declares (checked by tests/test_abi_symbols.py)
 ABI_SYMBOLS = [
     "rm_create", "rm_create_ex", "rm_destroy", "rm_set_limits", "rm_set_mode", "rm_get_mode", "rm_set_kernel",
-    "rm_prepare", "rm_prepare_uniforms", "rm_validate_program", "rm_paint", "rm_paint_poses", "rm_download",
+    "rm_prepare", "rm_prepare_uniforms", "rm_validate_program", "rm_paint", "rm_paint_strips", "rm_paint_poses", "rm_download",
     "rm_sync", "rm_paint_debug", "rm_map", "rm_set_counters", "rm_get_counters", "rm_mark", "rm_elapsed_ms",
     "rm_flush_l2", "rm_fp32_peak", "rm_launch_count", "rm_host_alloc", "rm_host_free", "rm_last_error",
     "rm_strerror", "rm_version",
@@ -76,6 +76,7 @@ def lib() -> C.CDLL:
             "rm_validate_program": (i, [u32, vp, u32, u32]),
             "rm_paint": (i, [vp, u32, u32, u32, u32, vp, sz, vp]),
             "rm_paint_poses": (i, [vp, vp, u32, u32, u32, vp, sz, sz, vp]),
+            "rm_paint_strips": (i, [vp, u32, u32, u32, u32, u32, vp, sz, vp, C.POINTER(u32)]),
             "rm_download": (i, [vp, vp, sz]),
             "rm_sync": (i, [vp]),
             "rm_paint_debug": (i, [vp, u32, u32, u32, u32, vp, vp, vp, vp]),
@@ -186,6 +187,14 @@ class Context:
               pitch: int = 0, stream: int | None = None):
         nrows = H - row0 if nrows is None else nrows
         self._chk(self._L.rm_paint(self._h, W, H, row0, nrows, dst_ptr, pitch, stream))
+
+    def paint_strips(self, W: int, H: int, strip_rows: int, first_strip: int, strip_step: int,
+                     dst_ptr: int | None = None, pitch: int = 0, stream: int | None = None) -> int:
+        """Shades strips first_strip, first_strip+strip_step, ... packed contiguously; returns rows painted."""
+        n = C.c_uint32()
+        self._chk(self._L.rm_paint_strips(self._h, W, H, strip_rows, first_strip, strip_step, dst_ptr, pitch, stream,
+                                          C.byref(n)))
+        return int(n.value)
 
     def paint_poses(self, uniforms_array: bytes, n_poses: int, W: int, H: int, dst_ptr: int | None = None,
                     pitch: int = 0, frame_stride: int = 0, stream: int | None = None):

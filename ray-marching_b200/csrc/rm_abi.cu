@@ -88,6 +88,7 @@ FrameParams make_params(const rm_ctx *c, const float *u, uint32_t W, uint32_t H,
     fp.max_dist = c->limits_f[1];
     fp.max_iter = c->max_iter;
     fp.W = W; fp.H = H; fp.row0 = row0; fp.nrows = nrows;
+    fp.strip_rows = 0; fp.strip_pitch = 0;
     fp.n_insn = (uint32_t)c->prog.insns.size();
     return fp;
 }

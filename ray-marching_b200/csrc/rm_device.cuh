@@ -31,8 +31,16 @@ struct FrameParams {
     float min_dist, max_dist;  // RayMarchLimits         wgsl:78-82
     uint32_t max_iter;
     uint32_t W, H, row0, nrows;
+    // interleaved strips (multi-GPU load balance): local row ry of the band maps to frame row
+    // row0 + (ry / strip_rows) * strip_pitch + ry % strip_rows; strip_pitch == 0 = contiguous band
+    uint32_t strip_rows, strip_pitch;
     uint32_t n_insn;     // decoded instruction count (0 = empty scene)
 };
+
+__device__ __forceinline__ uint32_t frame_row(const FrameParams &fp, uint32_t ry) {
+    if (fp.strip_pitch == 0) return fp.row0 + ry;
+    return fp.row0 + (ry / fp.strip_rows) * fp.strip_pitch + ry % fp.strip_rows;
+}
 
 template <bool EX>
 struct Arith;

@@ -59,7 +59,7 @@ k_samples_simple(const __grid_constant__ FrameParams fp, const RmInsn *__restric
     if (idx < total) {
         const unsigned long long pix = idx >> 4;
         const uint32_t sample = (uint32_t)(idx & 15u);
-        const uint32_t px = (uint32_t)(pix % fp.W), py = fp.row0 + (uint32_t)(pix / fp.W);
+        const uint32_t px = (uint32_t)(pix % fp.W), py = frame_row(fp, (uint32_t)(pix / fp.W));
         float ro[3], rd[3], t;
         gen_ray(fp, px, py, sample, ro, rd);
         const float code = march_one<EX>(fp, s_prog, ro, rd, cls, t, n_step);

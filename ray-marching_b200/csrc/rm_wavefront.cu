@@ -223,7 +223,7 @@ k_wavefront(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ p
                 float code = RM_CODE_SKY;
                 float o[3], d[3] = {0.f, 0.f, 0.f};
                 if (inside) {
-                    gen_ray(fp, px, fp.row0 + ry, q >> 5, o, d);
+                    gen_ray(fp, px, frame_row(fp, ry), q >> 5, o, d);
                     float c[3], t;
                     const int cls = shade_miss(ro, d, c, t);  // wgsl:117-130
                     code = cls == 0 ? RM_CODE_SKY : (c[0] > 0.2f ? RM_CODE_FLOOR_LIGHT : RM_CODE_FLOOR_DARK);

@@ -1,0 +1,49 @@
+"""Multi-GPU sharding plans for the render pass — pure index arithmetic, no compute.
+
+Row-band sharding of one large frame uses *interleaved strips* (strip s goes to rank s % world): equal
+contiguous bands do not balance (sky rows are cheap, silhouette rows expensive), fine
+interleaving does.  Each rank renders its strips packed contiguously (`rm_paint_strips`), the packed
+bands are gathered to rank 0 (NCCL) and re-ordered with one indexed copy.
+Pose batches shard by frame: rank r renders poses r, r + world, ...
+"""
+from __future__ import annotations
+
+import numpy as np
+
+DEFAULT_STRIP_ROWS = 16
+
+
+def n_strips(H: int, strip_rows: int) -> int:
+    return (H + strip_rows - 1) // strip_rows
+
+
+def local_rows(H: int, strip_rows: int, rank: int, world: int) -> int:
+    """Rows rank `rank` renders (what rm_paint_strips reports in *rows_painted)."""
+    rows = 0
+    for s in range(rank, n_strips(H, strip_rows), world):
+        rows += min(strip_rows, H - s * strip_rows)
+    return rows
+
+
+def max_local_rows(H: int, strip_rows: int, world: int) -> int:
+    return max(local_rows(H, strip_rows, r, world) for r in range(world))
+
+
+def row_index(H: int, strip_rows: int, world: int):
+    """For every frame row y: (owner rank, row inside that rank's packed band)."""
+    y = np.arange(H)
+    s = y // strip_rows
+    return (s % world).astype(np.int64), ((s // world) * strip_rows + y % strip_rows).astype(np.int64)
+
+
+def reassemble(gathered, H: int, strip_rows: int, world: int):
+    """gathered: [world, rows_max, W, 4] (numpy array or torch tensor) -> frame [H, W, 4]."""
+    rank_idx, loc_idx = row_index(H, strip_rows, world)
+    if isinstance(gathered, np.ndarray):
+        return gathered[rank_idx, loc_idx]
+    import torch
+    return gathered[torch.as_tensor(rank_idx, device=gathered.device), torch.as_tensor(loc_idx, device=gathered.device)]
+
+
+def pose_slice(n_poses: int, rank: int, world: int) -> range:
+    return range(rank, n_poses, world)

@@ -194,6 +194,25 @@ def test_row_bands_bit_identical_to_full_frame(rm, ctx):
         assert np.array_equal(np.concatenate(parts, 0), full)
 
 
+@pytest.mark.parametrize("H,strip,world", [(144, 16, 8), (50, 16, 3), (43, 4, 2)])
+def test_interleaved_strips_bit_identical_to_full_frame(rm, ctx, H, strip, world):
+    import importlib
+    sh = importlib.import_module("ray_marching_b200.sharding")
+    cmd, words = h.scene_s2()
+    W = 256
+    u = h.orbit_uniforms(W, H, yaw=0.6, pitch=0.4)
+    ctx.set_mode(rm.MODE_FAST)
+    full = ctx.render(u, cmd, words, W, H)
+    rows_max = sh.max_local_rows(H, strip, world)
+    gathered = np.zeros((world, rows_max, W, 4), np.uint8)
+    for r in range(world):  # what each rank does
+        n = ctx.paint_strips(W, H, strip, r, world)
+        assert n == sh.local_rows(H, strip, r, world)
+        if n:
+            ctx.download(gathered[r, :n])
+    assert np.array_equal(sh.reassemble(gathered, H, strip, world), full)
+
+
 def test_limits_are_runtime_values(rm, ctx):
     cmd, words = h.scene_s1()
     W, H = 96, 64
