@@ -182,8 +182,12 @@ def main():
     ctx = rm.Context(local_rank)
     ctx.set_mode(rm.MODE_FAST if args.mode == "fast" else rm.MODE_EXACT)
     ctx.set_kernel(rm.KERNEL_WAVEFRONT if args.kernel == "wavefront" else rm.KERNEL_SIMPLE)
-    stream = torch.cuda.current_stream(dev)
+    # a dedicated non-default stream: the ABI reads a NULL stream as "the ctx's own stream", and the
+    # CUDA events that time the steps must sit on the stream the kernels are launched on
+    stream = torch.cuda.Stream(dev)
+    torch.cuda.set_stream(stream)
     sp = stream.cuda_stream
+    assert sp != 0
 
     def barrier():
         if dist is not None:
