@@ -1,0 +1,140 @@
+// rm_wavefront_common.cuh — pieces shared by the two persistent wavefront kernels
+// (rm_wavefront.cu: per-slot state machine; rm_wavefront2.cu: march slots + hit queue):
+// tile geometry, ray-slot meta word, the R-wide decoded-program interpreter (wgsl:187-252),
+// and the out-of-line shade / resolve helpers (wgsl:98-105,138-143 and wgsl:44-45,68-75).
+#pragma once
+#include "rm_wavefront.h"
+
+namespace rm {
+namespace {
+
+constexpr int WF_WARPS = 4;      // warps per CTA
+constexpr int WF_K = 4;          // tiles in flight per warp
+constexpr int TILE_W = 8, TILE_H = 4;
+constexpr int TILE_RAYS = TILE_W * TILE_H * 16;  // 512
+constexpr unsigned FULL = 0xffffffffu;
+constexpr int RING = 1024;
+
+constexpr uint32_t M_Q = 0x1ffu;          // sample slot in tile: sample*32 + pixel
+constexpr uint32_t M_BUF_SHIFT = 9;       // 2 bits
+constexpr uint32_t M_STATE_SHIFT = 11;    // 3 bits: 0 MARCH, 1..4 TAP0..TAP3
+constexpr uint32_t M_LIVE = 1u << 14;
+constexpr uint32_t M_ITER_SHIFT = 16;      // 16 bits: march iterations done (max_iter <= 65535)
+
+constexpr int RING_N = 64;  // ready-ray ring: two batches of 32
+// map_scene for R points at once: one instruction fetch and ONE jump-table dispatch on the fused
+// opcode feed R evaluations; every case folds its source straight into the accumulators.
+template <bool EX, uint32_t SRC>
+__device__ __forceinline__ float prim_eval(float x, float y, float z, const float4 &q0, const float4 &q1) {
+    if (SRC == SRC_SPHERE) return sd_sphere<EX>(x, y, z, q0.x, q0.y, q0.z, q0.w);
+    return sd_box<EX>(x, y, z, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y);
+}
+
+#define RM_OPC(SRC, CB) opcode(SRC, CB)
+#define RM_FOR_R _Pragma("unroll") for (int r = 0; r < R; ++r)
+#define RM_PRIM_CASES(SRC)                                                                                  \
+    case RM_OPC(SRC, CB_FIRST):                                                                             \
+        RM_FOR_R acc[r] = prim_eval<EX, SRC>(px[r], py[r], pz[r], q0, q1);                                  \
+        break;                                                                                              \
+    case RM_OPC(SRC, CB_PUSH):                                                                              \
+        RM_FOR_R { spill[slot][r] = acc[r]; acc[r] = prim_eval<EX, SRC>(px[r], py[r], pz[r], q0, q1); }     \
+        break;                                                                                              \
+    case RM_OPC(SRC, CB_UNION):                                                                             \
+        RM_FOR_R acc[r] = fminf(acc[r], prim_eval<EX, SRC>(px[r], py[r], pz[r], q0, q1));                   \
+        break;                                                                                              \
+    case RM_OPC(SRC, CB_SUB):                                                                               \
+        RM_FOR_R acc[r] = fmaxf(acc[r], -prim_eval<EX, SRC>(px[r], py[r], pz[r], q0, q1));                  \
+        break;                                                                                              \
+    case RM_OPC(SRC, CB_INTER):                                                                             \
+        RM_FOR_R acc[r] = fmaxf(acc[r], prim_eval<EX, SRC>(px[r], py[r], pz[r], q0, q1));                   \
+        break;                                                                                              \
+    case RM_OPC(SRC, CB_SMOOTH):                                                                            \
+        RM_FOR_R acc[r] = op_smooth<EX>(acc[r], prim_eval<EX, SRC>(px[r], py[r], pz[r], q0, q1), q1.z, q1.w, \
+                                        q2.x, k_pow2);                                                      \
+        break;
+
+// acc = min(acc, v) etc. with the accumulator tied to one register (no copies around the loop)
+__device__ __forceinline__ void acc_min(float &acc, float v) { asm("min.f32 %0, %0, %1;" : "+f"(acc) : "f"(v)); }
+__device__ __forceinline__ void acc_max(float &acc, float v) { asm("max.f32 %0, %0, %1;" : "+f"(acc) : "f"(v)); }
+
+template <bool EX, int R>
+__device__ __forceinline__ void map_evalR(const float4 *__restrict__ prog, uint32_t n_insn, float max_dist,
+                                          const float (&px)[R], const float (&py)[R], const float (&pz)[R],
+                                          float (&acc)[R], float (*spill)[R]) {
+    if (n_insn == 0) {  // wgsl:189-191
+        RM_FOR_R acc[r] = max_dist;
+        return;
+    }
+    RM_FOR_R acc[r] = 0.0f;
+#pragma unroll 1
+    for (uint32_t i = 0; i < n_insn; ++i) {
+        const float4 q0 = prog[3 * i], q1 = prog[3 * i + 1], q2 = prog[3 * i + 2];
+        const uint32_t fl = __float_as_uint(q2.w);
+        // Dispatch on one-hot flag bits, most frequent fused ops first (primitive kind, then
+        // smooth-union / union / subtraction / intersection / push / first).
+        if (!(fl & FLAG_POP)) {
+            float v[R];
+            if (fl & FLAG_BOX) {
+                RM_FOR_R v[r] = sd_box<EX>(px[r], py[r], pz[r], q0.x, q0.y, q0.z, q0.w, q1.x, q1.y);
+            } else {
+                RM_FOR_R v[r] = sd_sphere<EX>(px[r], py[r], pz[r], q0.x, q0.y, q0.z, q0.w);
+            }
+            if (fl & FLAG_SMOOTH) {
+                RM_FOR_R acc[r] = op_smooth<EX>(acc[r], v[r], q1.z, q1.w, q2.x, (fl & FLAG_K_POW2) != 0);
+            } else if (fl & FLAG_UNION) {
+                RM_FOR_R acc_min(acc[r], v[r]);
+            } else if (fl & FLAG_SUB) {
+                RM_FOR_R acc_max(acc[r], -v[r]);
+            } else if (fl & FLAG_INTER) {
+                RM_FOR_R acc_max(acc[r], v[r]);
+            } else {
+                if (fl & FLAG_PUSH) {
+                    const uint32_t slot = __float_as_uint(q2.z);
+                    RM_FOR_R spill[slot][r] = acc[r];
+                }
+                RM_FOR_R acc[r] = v[r];
+            }
+        } else {
+            // binary operator on two subtrees: right operand = accumulator, left = spilled entry
+            const uint32_t slot = __float_as_uint(q2.z);
+            if (fl & FLAG_SMOOTH) {
+                RM_FOR_R acc[r] = op_smooth<EX>(spill[slot][r], acc[r], q1.z, q1.w, q2.x, (fl & FLAG_K_POW2) != 0);
+            } else if (fl & FLAG_UNION) {
+                RM_FOR_R acc[r] = fminf(spill[slot][r], acc[r]);
+            } else if (fl & FLAG_SUB) {
+                RM_FOR_R acc[r] = fmaxf(spill[slot][r], -acc[r]);
+            } else {
+                RM_FOR_R acc[r] = fmaxf(spill[slot][r], acc[r]);
+            }
+        }
+    }
+}
+
+// ---- rare per-ray events, kept OUT OF LINE (one copy each) so that the per-iteration instruction
+// footprint of the persistent loop stays inside the instruction cache (profiles/r1_v1_*: the fully
+// inlined R=4 kernel stalled 4.7 cycles per issue on no_instruction) ------------------------------
+// normal from the four tetrahedron taps + diffuse term (wgsl:98-105, 138-143) -> sample code
+template <bool EX>
+__device__ __noinline__ float wf_shade(float a0, float a1, float a2, float a3, float hx, float hy, float hz) {
+    using A = Arith<EX>;
+    const float nx = A::add(A::add(A::add(a0, -a1), -a2), a3);
+    const float ny = A::add(A::add(A::add(-a0, -a1), a2), a3);
+    const float nz = A::add(A::add(A::add(-a0, a1), -a2), a3);
+    return shade_diffuse<EX>(nx, ny, nz, hx, hy, hz);
+}
+
+// in-order 16-sample resolve of one pixel of a finished tile (codes[sample*32 + pixel])
+__device__ __noinline__ uint32_t wf_resolve(const float *codes, int lane) {
+    float sr = 0.0f, sg = 0.0f, sb = 0.0f;
+#pragma unroll 1
+    for (int sidx = 0; sidx < 16; ++sidx) {
+        float g[3];
+        code_to_gamma(codes[sidx * 32 + lane], g);
+        sr = __fadd_rn(sr, g[0]); sg = __fadd_rn(sg, g[1]); sb = __fadd_rn(sb, g[2]);
+    }
+    return unorm8(__fdiv_rn(sr, 16.0f)) | (unorm8(__fdiv_rn(sg, 16.0f)) << 8) |
+           (unorm8(__fdiv_rn(sb, 16.0f)) << 16) | 0xff000000u;
+}
+
+}  // namespace
+}  // namespace rm
