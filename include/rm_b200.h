@@ -74,7 +74,8 @@ enum {
 /* ---- kernel selection -------------------------------------------------------------------------- */
 enum {
     RM_KERNEL_WAVEFRONT = 0, /* persistent warps over 8x4 tiles with ballot refill of ray slots (default) */
-    RM_KERNEL_SIMPLE = 1     /* one thread per sample ray + resolve pass (verification path) */
+    RM_KERNEL_SIMPLE = 1,    /* one thread per sample ray + resolve pass (verification path) */
+    RM_KERNEL_WAVEFRONT2 = 2 /* persistent warps, march-only ray slots + per-warp hit queue for the normals */
 };
 
 /* sample classes of the debug AOV */

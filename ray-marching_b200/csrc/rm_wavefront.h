@@ -22,4 +22,8 @@ void wavefront_destroy(WavefrontState *ws);
 cudaError_t launch_wavefront(WavefrontState *ws, bool exact, const FrameParams &fp, const RmInsn *prog_dev,
                              uint8_t *dst, size_t pitch, unsigned long long *counters, cudaStream_t st);
 
+// Same contract, second-generation kernel (rm_wavefront2.cu): march-only slots + hit queue.
+cudaError_t launch_wavefront2(WavefrontState *ws, bool exact, const FrameParams &fp, const RmInsn *prog_dev,
+                              uint8_t *dst, size_t pitch, unsigned long long *counters, cudaStream_t st);
+
 }  // namespace rm
