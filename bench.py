@@ -122,7 +122,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--mode", default="fast", choices=["fast", "exact"])
-    ap.add_argument("--kernel", default="wavefront", choices=["wavefront", "simple", "wavefront2"])
+    ap.add_argument("--kernel", default="wavefront2", choices=["wavefront", "simple", "wavefront2"])
     ap.add_argument("--workload", default="cfg3", choices=list(WORKLOADS))
     ap.add_argument("--poses", type=int, default=0, help="cfg5: override the 1024-pose batch size")
     ap.add_argument("--no-cpu-baseline", action="store_true")

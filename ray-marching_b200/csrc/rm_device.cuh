@@ -107,8 +107,10 @@ __device__ __forceinline__ float sd_box(float px, float py, float pz, float cx, 
 
 // ---- binary operators: a = left operand (deeper stack entry), b = right (top) ----------------
 // X2: h = max(k-|a-b|,0)/k ; min(a,b) - h*h*k*0.25
+// Fast mode uses the algebraically equal h*h*k*0.25 = e*e/(4k) with c4k = 1/(4k) precomputed per
+// instruction: one multiply fewer per blend (exact mode keeps the literal operation order).
 template <bool EX>
-__device__ __forceinline__ float op_smooth(float a, float b, float k, float inv_k, float kq, bool k_pow2) {
+__device__ __forceinline__ float op_smooth(float a, float b, float k, float inv_k, float c4k, bool k_pow2) {
     using A = Arith<EX>;
     float e = fmaxf(A::sub(k, fabsf(A::sub(a, b))), 0.0f);
     float m = fminf(a, b);
@@ -116,17 +118,32 @@ __device__ __forceinline__ float op_smooth(float a, float b, float k, float inv_
         float h = k_pow2 ? __fmul_rn(e, inv_k) : __fdiv_rn(e, k);
         return __fsub_rn(m, __fmul_rn(__fmul_rn(__fmul_rn(h, h), k), 0.25f));
     } else {
-        float h = e * inv_k;
-        return fmaf(-(h * h), kq, m);
+        return fmaf(-(e * e), c4k, m);
+    }
+}
+// acc = smooth-min(acc, b), same operations, with the result tied to acc's register so that the
+// interpreter loop carries no accumulator copies around its back-edge.
+template <bool EX>
+__device__ __forceinline__ void op_smooth_acc(float &acc, float b, float k, float inv_k, float c4k, bool k_pow2) {
+    using A = Arith<EX>;
+    const float e = fmaxf(A::sub(k, fabsf(A::sub(acc, b))), 0.0f);
+    asm("min.f32 %0, %0, %1;" : "+f"(acc) : "f"(b));
+    if (EX) {
+        const float h = k_pow2 ? __fmul_rn(e, inv_k) : __fdiv_rn(e, k);
+        const float t = __fmul_rn(__fmul_rn(__fmul_rn(h, h), k), 0.25f);
+        asm("sub.rn.f32 %0, %0, %1;" : "+f"(acc) : "f"(t));
+    } else {
+        const float t = -(e * e);
+        asm("fma.rn.f32 %0, %1, %2, %0;" : "+f"(acc) : "f"(t), "f"(c4k));
     }
 }
 template <bool EX>
-__device__ __forceinline__ float combine(uint32_t cb, float a, float b, const float4 &q1, float kq, bool k_pow2) {
+__device__ __forceinline__ float combine(uint32_t cb, float a, float b, const float4 &q1, float c4k, bool k_pow2) {
     switch (cb) {
         case CB_UNION: return fminf(a, b);   // wgsl:242-246
         case CB_SUB: return fmaxf(a, -b);    // wgsl:248-252
         case CB_INTER: return fmaxf(a, b);   // X1
-        default: return op_smooth<EX>(a, b, q1.z, q1.w, kq, k_pow2);
+        default: return op_smooth<EX>(a, b, q1.z, q1.w, c4k, k_pow2);
     }
 }
 

@@ -32,7 +32,7 @@ inline uint32_t combine_of(uint32_t t) {
 inline void set_k(RmInsn &in, float k) {
     in.k = k;
     in.inv_k = 1.0f / k;
-    in.kq = k * 0.25f;
+    in.c4k = 0.25f / k;  // fast mode folds h*h*k*0.25 = e*e/(4k) into one constant
     int e = 0;
     float m = std::frexp(k, &e);
     // 1/k and x*(1/k) == x/k bit for bit when k is a normal power of two with a normal reciprocal

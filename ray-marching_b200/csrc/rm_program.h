@@ -69,7 +69,7 @@ RM_HD constexpr uint32_t opcode_cb(uint32_t op) { return op < 4u ? op + CB_UNION
 struct alignas(16) RmInsn {
     float cx, cy, cz, r0;      // centre, sphere radius / box radius x
     float r1, r2, k, inv_k;    // box radius y,z; smooth-union k and 1/k
-    float kq;                  // k * 0.25 (exact scaling)
+    float c4k;                 // 1/(4k): fast mode evaluates min(a,b) - e*e*c4k (exact mode does not read it)
     uint32_t op;               // dense fused opcode, see opcode()
     uint32_t slot;             // spill slot read (SRC_POP) or written (CB_PUSH)
     uint32_t flags;

@@ -66,6 +66,8 @@ __device__ __forceinline__ void map_evalR(const float4 *__restrict__ prog, uint3
         return;
     }
     RM_FOR_R acc[r] = 0.0f;
+    // not unrolled: unrolling by 2 removes the 8 accumulator copies ptxas leaves at the back-edge, but measured
+    // slower on B200 (cfg3 48.94 vs 48.64 ms, cfg2 2.77 vs 2.32 ms: larger code, remainder loop) — profiles/r1_s2_NOTES.md
 #pragma unroll 1
     for (uint32_t i = 0; i < n_insn; ++i) {
         const float4 q0 = prog[3 * i], q1 = prog[3 * i + 1], q2 = prog[3 * i + 2];
@@ -80,7 +82,7 @@ __device__ __forceinline__ void map_evalR(const float4 *__restrict__ prog, uint3
                 RM_FOR_R v[r] = sd_sphere<EX>(px[r], py[r], pz[r], q0.x, q0.y, q0.z, q0.w);
             }
             if (fl & FLAG_SMOOTH) {
-                RM_FOR_R acc[r] = op_smooth<EX>(acc[r], v[r], q1.z, q1.w, q2.x, (fl & FLAG_K_POW2) != 0);
+                RM_FOR_R op_smooth_acc<EX>(acc[r], v[r], q1.z, q1.w, q2.x, (fl & FLAG_K_POW2) != 0);
             } else if (fl & FLAG_UNION) {
                 RM_FOR_R acc_min(acc[r], v[r]);
             } else if (fl & FLAG_SUB) {
