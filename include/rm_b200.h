@@ -127,6 +127,14 @@ RM_API int rm_paint_strips(rm_ctx *ctx, uint32_t W, uint32_t H, uint32_t strip_r
 RM_API int rm_paint_poses(rm_ctx *ctx, const void *uniforms144_array, uint32_t n_poses, uint32_t W,
                           uint32_t H, void *dst_rgba8_dev, size_t pitch_bytes,
                           size_t frame_stride_bytes, void *cuda_stream);
+/* Pose batch with the frames returned to HOST memory (the reference hands every frame to its surface,
+ * renderer.rs:244-255): frame p is rendered on the ctx stream into a 3-deep device ring and copied to
+ * host_rgba8 + (p % host_ring_frames) * host_frame_stride_bytes on a second stream, so the copy of frame p
+ * overlaps the render of frame p+1 (pinned host memory, e.g. rm_host_alloc, is needed for the overlap).
+ * host_ring_frames == 0 means one host slot per pose.  Synchronises: all frames are in host memory on return. */
+RM_API int rm_paint_poses_host(rm_ctx *ctx, const void *uniforms144_array, uint32_t n_poses, uint32_t W,
+                               uint32_t H, void *host_rgba8, size_t host_frame_stride_bytes,
+                               uint32_t host_ring_frames);
 /* Copies the ctx-owned framebuffer of the last rm_paint(dst=NULL) to host memory; synchronises. */
 RM_API int rm_download(rm_ctx *ctx, void *host_rgba8, size_t bytes);
 RM_API int rm_sync(rm_ctx *ctx);

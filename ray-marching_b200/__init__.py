@@ -27,7 +27,7 @@ UNIFORMS_BYTES, LIMITS_BYTES = 144, 12
 # every symbol include/rm_b200.h declares (checked by tests/test_abi_symbols.py)
 ABI_SYMBOLS = [
     "rm_create", "rm_create_ex", "rm_destroy", "rm_set_limits", "rm_set_mode", "rm_get_mode", "rm_set_kernel",
-    "rm_prepare", "rm_prepare_uniforms", "rm_validate_program", "rm_paint", "rm_paint_strips", "rm_paint_poses", "rm_download",
+    "rm_prepare", "rm_prepare_uniforms", "rm_validate_program", "rm_paint", "rm_paint_strips", "rm_paint_poses", "rm_paint_poses_host", "rm_download",
     "rm_sync", "rm_paint_debug", "rm_map", "rm_set_counters", "rm_get_counters", "rm_mark", "rm_elapsed_ms",
     "rm_flush_l2", "rm_fp32_peak", "rm_launch_count", "rm_host_alloc", "rm_host_free", "rm_last_error",
     "rm_strerror", "rm_version",
@@ -76,6 +76,7 @@ def lib() -> C.CDLL:
             "rm_validate_program": (i, [u32, vp, u32, u32]),
             "rm_paint": (i, [vp, u32, u32, u32, u32, vp, sz, vp]),
             "rm_paint_poses": (i, [vp, vp, u32, u32, u32, vp, sz, sz, vp]),
+            "rm_paint_poses_host": (i, [vp, vp, u32, u32, u32, vp, sz, u32]),
             "rm_paint_strips": (i, [vp, u32, u32, u32, u32, u32, vp, sz, vp, C.POINTER(u32)]),
             "rm_download": (i, [vp, vp, sz]),
             "rm_sync": (i, [vp]),
@@ -200,6 +201,13 @@ class Context:
                     pitch: int = 0, frame_stride: int = 0, stream: int | None = None):
         assert len(uniforms_array) >= n_poses * UNIFORMS_BYTES
         self._chk(self._L.rm_paint_poses(self._h, uniforms_array, n_poses, W, H, dst_ptr, pitch, frame_stride, stream))
+
+    def paint_poses_host(self, uniforms_array: bytes, n_poses: int, W: int, H: int, host_ptr: int,
+                         host_frame_stride: int | None = None, host_ring_frames: int = 0):
+        """Pose batch with every frame returned to host memory (D2H of frame p overlaps the render of p+1)."""
+        assert len(uniforms_array) >= n_poses * UNIFORMS_BYTES
+        self._chk(self._L.rm_paint_poses_host(self._h, uniforms_array, n_poses, W, H, host_ptr,
+                                              host_frame_stride or W * H * 4, host_ring_frames))
 
     def download(self, out: np.ndarray | PinnedBuffer | None = None, nbytes: int | None = None) -> np.ndarray:
         if isinstance(out, PinnedBuffer):

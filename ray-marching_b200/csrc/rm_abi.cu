@@ -47,6 +47,12 @@ struct rm_ctx {
     unsigned long long *d_counters = nullptr;
     WavefrontState wf;
     cudaStream_t last_paint_stream = nullptr;
+    // rm_paint_poses_host: device frame ring + copy stream so that frame p's D2H overlaps frame p+1's render
+    static constexpr int kRing = 3;
+    cudaStream_t copy_stream = nullptr;
+    uint8_t *d_ring = nullptr;
+    size_t ring_cap = 0;
+    cudaEvent_t ring_rendered[kRing] = {}, ring_copied[kRing] = {};
     uint64_t launches = 0;
     std::string err;
 };
@@ -167,6 +173,10 @@ void rm_destroy(rm_ctx *c) {
     if (c->d_prog) cudaFree(c->d_prog);
     if (c->h_prog) cudaFreeHost(c->h_prog);
     if (c->d_fb) cudaFree(c->d_fb);
+    if (c->copy_stream) { cudaStreamSynchronize(c->copy_stream); cudaStreamDestroy(c->copy_stream); }
+    if (c->d_ring) cudaFree(c->d_ring);
+    for (auto &e : c->ring_rendered) if (e) cudaEventDestroy(e);
+    for (auto &e : c->ring_copied) if (e) cudaEventDestroy(e);
     if (c->d_codes) cudaFree(c->d_codes);
     if (c->d_flush) cudaFree(c->d_flush);
     if (c->d_counters) cudaFree(c->d_counters);

@@ -241,6 +241,27 @@ def test_pose_batch_matches_single_frames(rm, ctx):
         assert np.array_equal(got[k], singles[k])
 
 
+def test_pose_batch_to_host_matches_single_frames(rm, ctx):
+    """rm_paint_poses_host: frames come back through the device ring + copy stream, more poses than ring slots,
+    both with one host slot per pose and with a wrapping host ring."""
+    cmd, words = h.scene_s1()
+    W, H, n = 96, 64, 7
+    us = [h.orbit_uniforms(W, H, yaw=0.9 * k, pitch=0.4) for k in range(n)]
+    ctx.set_mode(rm.MODE_FAST)
+    singles = [ctx.render(u, cmd, words, W, H) for u in us]
+    ctx.prepare(us[0], cmd, words)
+    buf = rm.PinnedBuffer(n * W * H * 4)
+    ctx.paint_poses_host(b"".join(us), n, W, H, buf.ptr)
+    got = buf.array.reshape(n, H, W, 4)
+    for k in range(n):
+        assert np.array_equal(got[k], singles[k]), k
+    ring = 3
+    ctx.paint_poses_host(b"".join(us), n, W, H, buf.ptr, W * H * 4, ring)
+    for k in range(n - ring, n):  # the last `ring` poses are the ones left in the wrapping host ring
+        assert np.array_equal(got[k % ring], singles[k]), k
+    buf.free()
+
+
 def test_error_codes(rm, ctx):
     u = h.orbit_uniforms(32, 32)
     with pytest.raises(rm.RmError) as e:
