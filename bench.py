@@ -97,6 +97,20 @@ class ClockSampler:
                 "samples": len(self.rows), "power_w_max": max(pw) if pw else None}
 
 
+def ncu_traffic(workload: str, kernel: str):
+    """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture of this exact
+    workload + kernel (profiles/*.ncu_summary.csv), or None.  Not measured live: a profiler is never in a timed run."""
+    name = {("cfg3", "wavefront2"): "r1_s3_wavefront2_R8_cfg3.ncu_summary.csv"}.get((workload, kernel))
+    if not name or not (ROOT / "profiles" / name).exists():
+        return None, None
+    tot, unit_scale = 0.0, {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    for line in (ROOT / "profiles" / name).read_text().splitlines():
+        parts = [p.strip('"') for p in line.split('","')]
+        if len(parts) == 3 and parts[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+            tot += float(parts[1].replace(",", "")) * unit_scale.get(parts[2], 1.0)
+    return (tot or None), f"profiles/{name}"
+
+
 def cpu_sample_rows(H: int, n: int):
     step = max(1, H // n)
     return list(range(step // 2, H, step))[:n]
@@ -331,8 +345,9 @@ def main():
         value = rays_step_total / (ms * 1e-3) / 1e6
         achieved = flops / (ms_local * 1e-3) / 1e12  # rank 0's kernel work over rank 0's device time
         fb_bytes = n_pixels_local * 4
+        traffic, traffic_src = ncu_traffic(args.workload, args.kernel) if args.mode == "fast" and world == 1 else (None, None)
         roof = {"bound": "fp32", "achieved": achieved, "peak": peak["tflops"], "unit": "TFLOP/s", "frac": achieved / peak["tflops"],
-                "traffic": None,
+                "traffic": traffic, "traffic_unit": "bytes of DRAM read+write per launch", "traffic_source": traffic_src,
                 "peak_source": "FFMA micro-benchmark run live on this GPU (rm_fp32_peak); MEASURED_PEAKS.json has no FP32 ALU peak; "
                                "nominal 148 SM x 128 lanes x 2 x 1.965 GHz = 74.4",
                 "algorithmic_flops_per_step": flops, "f_map_flops_per_eval": fmap,
