@@ -103,6 +103,9 @@ RM_API int rm_prepare(rm_ctx *ctx, const void *uniforms144, uint32_t cmd_count, 
                       uint32_t n_words);
 /* Uniform-only update (new camera pose, program unchanged) — SURVEY.md §8(f) N2/N3. */
 RM_API int rm_prepare_uniforms(rm_ctx *ctx, const void *uniforms144);
+/* How many times rm_prepare decoded and uploaded a program: a call whose cmd_count and words equal the last
+ * uploaded ones only replaces the uniforms (resolves the per-frame re-upload of renderer.rs:224-239). */
+RM_API uint64_t rm_program_uploads(rm_ctx *ctx);
 /* Static validation only (no device work): same codes as rm_prepare. */
 RM_API int rm_validate_program(uint32_t cmd_count, const uint32_t *words, uint32_t n_words,
                                uint32_t max_words);

@@ -27,7 +27,7 @@ UNIFORMS_BYTES, LIMITS_BYTES = 144, 12
 # every symbol include/rm_b200.h declares (checked by tests/test_abi_symbols.py)
 ABI_SYMBOLS = [
     "rm_create", "rm_create_ex", "rm_destroy", "rm_set_limits", "rm_set_mode", "rm_get_mode", "rm_set_kernel",
-    "rm_prepare", "rm_prepare_uniforms", "rm_validate_program", "rm_paint", "rm_paint_strips", "rm_paint_poses", "rm_paint_poses_host", "rm_download",
+    "rm_prepare", "rm_prepare_uniforms", "rm_program_uploads", "rm_validate_program", "rm_paint", "rm_paint_strips", "rm_paint_poses", "rm_paint_poses_host", "rm_download",
     "rm_sync", "rm_paint_debug", "rm_map", "rm_set_counters", "rm_get_counters", "rm_mark", "rm_elapsed_ms",
     "rm_flush_l2", "rm_fp32_peak", "rm_launch_count", "rm_host_alloc", "rm_host_free", "rm_last_error",
     "rm_strerror", "rm_version",
@@ -77,6 +77,7 @@ def lib() -> C.CDLL:
             "rm_paint": (i, [vp, u32, u32, u32, u32, vp, sz, vp]),
             "rm_paint_poses": (i, [vp, vp, u32, u32, u32, vp, sz, sz, vp]),
             "rm_paint_poses_host": (i, [vp, vp, u32, u32, u32, vp, sz, u32]),
+            "rm_program_uploads": (u64, [vp]),
             "rm_paint_strips": (i, [vp, u32, u32, u32, u32, u32, vp, sz, vp, C.POINTER(u32)]),
             "rm_download": (i, [vp, vp, sz]),
             "rm_sync": (i, [vp]),
@@ -178,6 +179,10 @@ class Context:
         assert len(uniforms) == UNIFORMS_BYTES
         w = _words_arr(words)
         self._chk(self._L.rm_prepare(self._h, uniforms, cmd_count, w.ctypes.data if w.size else None, w.size))
+
+    @property
+    def program_uploads(self) -> int:
+        return int(self._L.rm_program_uploads(self._h))
 
     def prepare_uniforms(self, uniforms: bytes):
         assert len(uniforms) == UNIFORMS_BYTES

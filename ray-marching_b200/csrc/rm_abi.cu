@@ -54,6 +54,10 @@ struct rm_ctx {
     size_t ring_cap = 0;
     cudaEvent_t ring_rendered[kRing] = {}, ring_copied[kRing] = {};
     uint64_t launches = 0;
+    // last uploaded command stream: rm_prepare re-uses the decoded program on the device when the words are unchanged
+    std::vector<uint32_t> last_words;
+    uint32_t last_cmd_count = 0;
+    uint64_t prog_uploads = 0;
     std::string err;
 };
 
@@ -213,6 +217,14 @@ int rm_prepare_uniforms(rm_ctx *c, const void *uniforms144) {
 
 int rm_prepare(rm_ctx *c, const void *uniforms144, uint32_t cmd_count, const uint32_t *words, uint32_t n_words) {
     if (!c || !uniforms144) return RM_E_INVALID_ARG;
+    if (n_words && !words) return fail(c, RM_E_INVALID_ARG, "null words");
+    // Same command stream as the one already on the device (the reference re-flattens and re-uploads the tree every
+    // frame, renderer.rs:224-239; an editor frame usually changes only the camera): only the uniforms change.
+    if (c->prepared && cmd_count == c->last_cmd_count && n_words == c->last_words.size() &&
+        (n_words == 0 || std::memcmp(words, c->last_words.data(), (size_t)n_words * sizeof(uint32_t)) == 0)) {
+        std::memcpy(c->uniforms, uniforms144, RM_UNIFORMS_BYTES);
+        return RM_OK;
+    }
     Program p;
     int rc = decode_program(cmd_count, words, n_words, c->max_words, &p);
     if (rc != RM_OK) return fail(c, rc, rm_strerror(rc));
@@ -227,9 +239,14 @@ int rm_prepare(rm_ctx *c, const void *uniforms144, uint32_t cmd_count, const uin
     }
     RM_CUDA(c, cudaEventRecord(c->upload_done, c->stream));
     std::memcpy(c->uniforms, uniforms144, RM_UNIFORMS_BYTES);
+    c->last_words.assign(words, words + n_words);
+    c->last_cmd_count = cmd_count;
+    ++c->prog_uploads;
     c->prepared = true;
     return RM_OK;
 }
+
+uint64_t rm_program_uploads(rm_ctx *c) { return c ? c->prog_uploads : 0; }
 
 }  // extern "C"
 

@@ -262,6 +262,29 @@ def test_pose_batch_to_host_matches_single_frames(rm, ctx):
     buf.free()
 
 
+def test_program_is_uploaded_only_when_the_words_change(rm, ctx):
+    """N3: rm_prepare with the command stream already on the device replaces only the uniforms."""
+    W, H = 96, 64
+    cmd1, w1 = h.scene_s1()
+    cmd2, w2 = h.scene_s2()
+    ua, ub = h.orbit_uniforms(W, H, yaw=0.6, pitch=0.4), h.orbit_uniforms(W, H, yaw=2.0, pitch=0.2)
+    ctx.set_mode(rm.MODE_EXACT)
+    n0 = ctx.program_uploads
+    a = ctx.render(ua, cmd1, w1, W, H)
+    b = ctx.render(ub, cmd1, w1, W, H)          # new camera, same words: no upload
+    assert ctx.program_uploads == n0 + 1
+    assert np.array_equal(a, h.oracle_render(ua, cmd1, w1, W, H)["rgba"])
+    assert np.array_equal(b, h.oracle_render(ub, cmd1, w1, W, H)["rgba"])
+    c = ctx.render(ub, cmd2, w2, W, H)          # different program: uploaded
+    assert ctx.program_uploads == n0 + 2
+    assert np.array_equal(c, h.oracle_render(ub, cmd2, w2, W, H)["rgba"])
+    w1b = list(w1); w1b[-2] = w1[-2] ^ 1        # one bit of one float differs: uploaded, and the image follows
+    ctx.render(ub, cmd1, w1b, W, H)
+    assert ctx.program_uploads == n0 + 3
+    d = ctx.render(ub, cmd1, w1, W, H)
+    assert ctx.program_uploads == n0 + 4 and np.array_equal(d, b)
+
+
 def test_error_codes(rm, ctx):
     u = h.orbit_uniforms(32, 32)
     with pytest.raises(rm.RmError) as e:
