@@ -136,7 +136,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--mode", default="fast", choices=["fast", "exact"])
-    ap.add_argument("--kernel", default="wavefront2", choices=["wavefront", "simple", "wavefront2"])
+    ap.add_argument("--kernel", default="direct", choices=["wavefront", "simple", "wavefront2", "direct"])
     ap.add_argument("--workload", default="cfg3", choices=list(WORKLOADS))
     ap.add_argument("--poses", type=int, default=0, help="cfg5: override the 1024-pose batch size")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -195,7 +195,7 @@ def main():
     dev = torch.device("cuda", local_rank)
     ctx = rm.Context(local_rank)
     ctx.set_mode(rm.MODE_FAST if args.mode == "fast" else rm.MODE_EXACT)
-    ctx.set_kernel({"wavefront": rm.KERNEL_WAVEFRONT, "simple": rm.KERNEL_SIMPLE, "wavefront2": rm.KERNEL_WAVEFRONT2}[args.kernel])
+    ctx.set_kernel({"wavefront": rm.KERNEL_WAVEFRONT, "simple": rm.KERNEL_SIMPLE, "wavefront2": rm.KERNEL_WAVEFRONT2, "direct": rm.KERNEL_DIRECT}[args.kernel])
     # a dedicated non-default stream: the ABI reads a NULL stream as "the ctx's own stream", and the
     # CUDA events that time the steps must sit on the stream the kernels are launched on
     stream = torch.cuda.Stream(dev)

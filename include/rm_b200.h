@@ -75,7 +75,8 @@ enum {
 enum {
     RM_KERNEL_WAVEFRONT = 0, /* persistent warps over 8x4 tiles, per-slot march/normal state machine (first generation) */
     RM_KERNEL_SIMPLE = 1,    /* one thread per sample ray + resolve pass (verification path) */
-    RM_KERNEL_WAVEFRONT2 = 2 /* persistent warps, march-only ray slots + per-warp hit queue for the normals (default) */
+    RM_KERNEL_WAVEFRONT2 = 2, /* persistent warps, march-only ray slots + per-warp hit queue for the normals */
+    RM_KERNEL_DIRECT = 3      /* no ray queues: a thread marches 4 or 8 samples of its pixel in lock-step, fused in-order resolve (default) */
 };
 
 /* sample classes of the debug AOV */

@@ -21,7 +21,7 @@ HOST_LIB_PATH = PKG_DIR / "librm_host.so"
 
 RM_OK = 0
 MODE_EXACT, MODE_FAST = 0, 1
-KERNEL_WAVEFRONT, KERNEL_SIMPLE, KERNEL_WAVEFRONT2 = 0, 1, 2
+KERNEL_WAVEFRONT, KERNEL_SIMPLE, KERNEL_WAVEFRONT2, KERNEL_DIRECT = 0, 1, 2, 3
 UNIFORMS_BYTES, LIMITS_BYTES = 144, 12
 
 # every symbol include/rm_b200.h declares (checked by tests/test_abi_symbols.py)

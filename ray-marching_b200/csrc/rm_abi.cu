@@ -29,7 +29,7 @@ struct rm_ctx {
     cudaEvent_t events[kEventSlots] = {};
     cudaEvent_t upload_done = nullptr;
     int mode = RM_MODE_EXACT;
-    int kernel = RM_KERNEL_WAVEFRONT2;
+    int kernel = RM_KERNEL_DIRECT;
     bool prepared = false;
     bool counters_on = false;
     float limits_f[2] = {0.01f, 100.0f};  // renderer.rs:133-137

@@ -26,4 +26,8 @@ cudaError_t launch_wavefront(WavefrontState *ws, bool exact, const FrameParams &
 cudaError_t launch_wavefront2(WavefrontState *ws, bool exact, const FrameParams &fp, const RmInsn *prog_dev,
                               uint8_t *dst, size_t pitch, unsigned long long *counters, cudaStream_t st);
 
+// Shallow-program kernel (rm_direct.cu): 4 sample rays per thread, fused in-order resolve, no queues.
+cudaError_t launch_direct(bool exact, const FrameParams &fp, const RmInsn *prog_dev, uint8_t *dst, size_t pitch,
+                          unsigned long long *counters, cudaStream_t st);
+
 }  // namespace rm

@@ -55,13 +55,13 @@ def gates(img, ref, cls=None, cls_ref=None, t=None, t_ref=None):
 
 
 @pytest.mark.parametrize("name,W,H,yaw,pitch", cases())
-@pytest.mark.parametrize("kernel", ["wavefront", "simple", "wavefront2"])
+@pytest.mark.parametrize("kernel", ["wavefront", "simple", "wavefront2", "direct"])
 def test_exact_mode_bit_identical(rm, ctx, name, W, H, yaw, pitch, kernel):
     cmd, words = h.SCENES[name]()
     u = h.orbit_uniforms(W, H, yaw=yaw, pitch=pitch)
     ref = h.oracle_render(u, cmd, words, W, H, aov=True)
     ctx.set_mode(rm.MODE_EXACT)
-    ctx.set_kernel({"wavefront": rm.KERNEL_WAVEFRONT, "simple": rm.KERNEL_SIMPLE, "wavefront2": rm.KERNEL_WAVEFRONT2}[kernel])
+    ctx.set_kernel({"wavefront": rm.KERNEL_WAVEFRONT, "simple": rm.KERNEL_SIMPLE, "wavefront2": rm.KERNEL_WAVEFRONT2, "direct": rm.KERNEL_DIRECT}[kernel])
     ctx.set_counters(True)
     img = ctx.render(u, cmd, words, W, H)
     cnt = ctx.get_counters()

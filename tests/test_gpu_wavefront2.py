@@ -1,5 +1,5 @@
 """GPU parity of the second-generation wavefront kernel (csrc/rm_wavefront2.cu: march-only ray slots +
-per-warp hit queue).  Per-ray arithmetic is the same operation for operation as in rm_wavefront.cu, so
+per-warp hit queue) and of the shallow-program kernel (csrc/rm_direct.cu: 4 sample rays per thread, no queues).  Per-ray arithmetic is the same operation for operation as in rm_wavefront.cu, so
 the bar is bit-identity with that kernel in BOTH arithmetic modes — image and work counters — on the
 cases that stress its bookkeeping: ragged bands, interleaved strips, tiny and zero iteration budgets,
 deep and right-leaning trees (spill slots), the empty scene; and bit-identity with the CPU oracle in
@@ -12,6 +12,12 @@ import rm_import
 from test_gpu_parity import random_program
 
 pytestmark = pytest.mark.gpu
+
+KUT = ["wavefront2", "direct"]  # kernels under test; the reference point is the first-generation wavefront kernel
+
+
+def kid(rm, name):
+    return getattr(rm, "KERNEL_" + name.upper())
 
 
 @pytest.fixture(scope="module")
@@ -26,10 +32,10 @@ def ctx(rm):
     c.close()
 
 
-def both_kernels(rm, ctx, mode, u, cmd, words, W, H, **kw):
+def both_kernels(rm, ctx, kut, mode, u, cmd, words, W, H, **kw):
     out = []
     ctx.set_mode(mode)
-    for k in (rm.KERNEL_WAVEFRONT, rm.KERNEL_WAVEFRONT2):
+    for k in (rm.KERNEL_WAVEFRONT, kid(rm, kut)):
         ctx.set_kernel(k)
         ctx.set_counters(True)
         img = ctx.render(u, cmd, words, W, H, **kw)
@@ -41,29 +47,32 @@ def both_kernels(rm, ctx, mode, u, cmd, words, W, H, **kw):
 @pytest.mark.parametrize("name,W,H,yaw,pitch", [("S0", 320, 240, 0.0, 0.0), ("S1", 480, 270, 0.6, 0.4),
                                                 ("S2", 384, 216, 0.6, 0.4), ("S2", 250, 141, 2.1, 0.15)])
 @pytest.mark.parametrize("mode", ["exact", "fast"])
-def test_matches_first_generation_kernel_bit_for_bit(rm, ctx, name, W, H, yaw, pitch, mode):
+@pytest.mark.parametrize("kut", KUT)
+def test_matches_first_generation_kernel_bit_for_bit(rm, ctx, name, W, H, yaw, pitch, mode, kut):
     cmd, words = h.SCENES[name]()
     u = h.orbit_uniforms(W, H, yaw=yaw, pitch=pitch)
-    (a, ca), (b, cb) = both_kernels(rm, ctx, rm.MODE_EXACT if mode == "exact" else rm.MODE_FAST, u, cmd, words, W, H)
+    (a, ca), (b, cb) = both_kernels(rm, ctx, kut, rm.MODE_EXACT if mode == "exact" else rm.MODE_FAST, u, cmd, words, W, H)
     assert np.array_equal(a, b), int((a != b).any(-1).sum())
     assert np.array_equal(ca, cb), (ca, cb)
 
 
 @pytest.mark.parametrize("W,H", [(37, 23), (8, 4), (1, 1), (9, 5), (130, 3)])
-def test_ragged_sizes_against_oracle(rm, ctx, W, H):
+@pytest.mark.parametrize("kut", KUT)
+def test_ragged_sizes_against_oracle(rm, ctx, W, H, kut):
     cmd, words = h.scene_s1()
     u = h.orbit_uniforms(W, H, yaw=0.6, pitch=0.4)
     ctx.set_mode(rm.MODE_EXACT)
-    ctx.set_kernel(rm.KERNEL_WAVEFRONT2)
+    ctx.set_kernel(kid(rm, kut))
     img = ctx.render(u, cmd, words, W, H)
     assert np.array_equal(img, h.oracle_render(u, cmd, words, W, H)["rgba"])
 
 
-def test_empty_scene_and_iteration_budgets(rm, ctx):
+@pytest.mark.parametrize("kut", KUT)
+def test_empty_scene_and_iteration_budgets(rm, ctx, kut):
     W, H = 96, 64
     u = h.orbit_uniforms(W, H, yaw=0.6, pitch=0.4)
     ctx.set_mode(rm.MODE_EXACT)
-    ctx.set_kernel(rm.KERNEL_WAVEFRONT2)
+    ctx.set_kernel(kid(rm, kut))
     assert np.array_equal(ctx.render(u, 0, [], W, H), h.oracle_render(u, 0, [], W, H)["rgba"])
     cmd, words = h.scene_s1()
     for lim in [(0.05, 50.0, 20), (0.001, 100.0, 7), (0.01, 100.0, 0), (0.01, 100.0, 1), (0.5, 100.0, 100)]:
@@ -77,11 +86,12 @@ def test_empty_scene_and_iteration_budgets(rm, ctx):
 
 
 @pytest.mark.parametrize("seed", range(4))
-def test_random_trees_with_spill_slots(rm, ctx, seed):
+@pytest.mark.parametrize("kut", KUT)
+def test_random_trees_with_spill_slots(rm, ctx, seed, kut):
     rng = np.random.default_rng(4321 + seed)
     u = h.orbit_uniforms(64, 64, yaw=0.3 * seed, pitch=0.35)
     ctx.set_mode(rm.MODE_EXACT)
-    ctx.set_kernel(rm.KERNEL_WAVEFRONT2)
+    ctx.set_kernel(kid(rm, kut))
     for n_leaves in (1, 3, 7, 16, 30):
         words, cmd = random_program(rng, n_leaves, right_bias=0.5)
         if len(words) > 255:
@@ -90,30 +100,32 @@ def test_random_trees_with_spill_slots(rm, ctx, seed):
         assert np.array_equal(img, h.oracle_render(u, cmd, words, 64, 64)["rgba"]), n_leaves
 
 
-def test_hit_dense_view_overflows_the_hit_queue(rm, ctx):
+@pytest.mark.parametrize("kut", KUT)
+def test_hit_dense_view_overflows_the_hit_queue(rm, ctx, kut):
     """A close-up where almost every ray hits within a few steps: many more than HQ_CAP hits arrive in
     one iteration, so the 'queue full -> retry next iteration' path runs.  Counters must not double count."""
     cmd, words = h.SCENES["S0"]()
     W, H = 256, 128
     u = h.orbit_uniforms(W, H, yaw=0.0, pitch=0.0, radius=1.6)
     for mode in (rm.MODE_EXACT, rm.MODE_FAST):
-        (a, ca), (b, cb) = both_kernels(rm, ctx, mode, u, cmd, words, W, H)
+        (a, ca), (b, cb) = both_kernels(rm, ctx, kut, mode, u, cmd, words, W, H)
         assert np.array_equal(a, b)
         assert np.array_equal(ca, cb), (ca, cb)
     ctx.set_mode(rm.MODE_EXACT)
-    ctx.set_kernel(rm.KERNEL_WAVEFRONT2)
+    ctx.set_kernel(kid(rm, kut))
     assert np.array_equal(ctx.render(u, cmd, words, W, H), h.oracle_render(u, cmd, words, W, H)["rgba"])
 
 
 @pytest.mark.parametrize("H,strip,world", [(144, 16, 8), (50, 16, 3)])
-def test_bands_and_strips_bit_identical_to_full_frame(rm, ctx, H, strip, world):
+@pytest.mark.parametrize("kut", KUT)
+def test_bands_and_strips_bit_identical_to_full_frame(rm, ctx, H, strip, world, kut):
     import importlib
     sharding = importlib.import_module("ray_marching_b200.sharding")
     cmd, words = h.SCENES["S2"]()
     W = 160
     u = h.orbit_uniforms(W, H, yaw=0.6, pitch=0.4)
     ctx.set_mode(rm.MODE_FAST)
-    ctx.set_kernel(rm.KERNEL_WAVEFRONT2)
+    ctx.set_kernel(kid(rm, kut))
     full = ctx.render(u, cmd, words, W, H)
     band = ctx.render(u, cmd, words, W, H, row0=H // 3, nrows=H // 2)
     assert np.array_equal(band, full[H // 3:H // 3 + H // 2])
