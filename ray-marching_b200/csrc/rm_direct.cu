@@ -22,8 +22,14 @@ namespace {
 constexpr int DIRECT_THREADS = 128;
 // R = sample rays per thread (4 or 8); a pixel's 16 samples are held by TPP = 16/R neighbouring lanes, so a warp covers
 // 32/TPP pixels = ROWS rows of 8, and the 4-warp block an 8 x (4*ROWS) pixel tile.
+// Resident blocks per SM asked of ptxas.  8-ray variant: 6 (80 registers, 148 B of spill) measured 45.19 ms on cfg3 against
+// 45.41 at 5 (96 registers) and 45.99 at 4 (123 registers, no spill) — one more warp per scheduler is worth the spill.
+// 4-ray variant: no hint (69 registers, 7 blocks); an explicit hint of 1 let ptxas take 77 and cost 6 % on cfg2.
+#ifndef RM_DIRECT_MINB8
+#define RM_DIRECT_MINB8 6
+#endif
 template <bool EX, int R, bool COUNT>
-__global__ void __launch_bounds__(DIRECT_THREADS)
+__global__ void __launch_bounds__(DIRECT_THREADS, (R == 8 ? RM_DIRECT_MINB8 : 0))
 k_direct(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ prog_g, uint8_t *__restrict__ dst, size_t pitch,
          unsigned long long *__restrict__ counters) {
     static_assert(R == 4 || R == 8, "4 or 8 rays per thread");
@@ -182,14 +188,15 @@ cudaError_t launch_direct(bool exact, const FrameParams &fp, const RmInsn *prog_
                           unsigned long long *counters, cudaStream_t st) {
     if (fp.nrows == 0 || fp.W == 0) return cudaSuccess;
     // Rays per thread: 4 for shallow programs (more threads, less lock-step waste), 8 for deep ones (fetch/dispatch
-    // amortised over more rays).  Measured on B200: S1 (3 instructions) 1.32 vs 1.57 ms, S2 (32) 47.8 vs 46.0 ms; the
-    // switch-over at 8 instructions sits between those two points and is not itself measured.  RM_DIRECT_R overrides.
+    // amortised over more rays).  Measured on B200 on truncated S2 chains at 1080p (tools/crossover.py, ms per frame,
+    // R=4 / R=8): 1 instruction 0.72/0.85, 3: 1.38/1.47, 4: 1.80/1.82, 5: 2.10/2.09, 8: 3.21/3.14, 32: 12.39/11.87.
+    // RM_DIRECT_R overrides.
     static const int kForce = [] {
         const char *s = std::getenv("RM_DIRECT_R");
         const int v = s ? std::atoi(s) : 0;
         return (v == 4 || v == 8) ? v : 0;
     }();
-    const int kR = kForce ? kForce : (fp.n_insn <= 8 ? 4 : 8);
+    const int kR = kForce ? kForce : (fp.n_insn <= 4 ? 4 : 8);
 #define RM_DIRECT_DISPATCH(EXV, RV)                                                        \
     (counters ? launch_direct_t<EXV, RV, true>(fp, prog_dev, dst, pitch, counters, st)    \
               : launch_direct_t<EXV, RV, false>(fp, prog_dev, dst, pitch, counters, st))
