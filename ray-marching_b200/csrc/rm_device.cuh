@@ -35,6 +35,11 @@ struct FrameParams {
     // row0 + (ry / strip_rows) * strip_pitch + ry % strip_rows; strip_pitch == 0 = contiguous band
     uint32_t strip_rows, strip_pitch;
     uint32_t n_insn;     // decoded instruction count (0 = empty scene)
+    // Per-frame constants of ray generation, computed once on the host with the same IEEE float operations the
+    // shader's expressions denote (rm_abi.cu make_params), so they are bit-identical to evaluating them per ray:
+    float ro4[4];        // inv_view * (0,0,0,1)                        wgsl:39-40
+    float sample_ax[4];  // ((i + 0.5)/4 - 0.5) / extent.x * 2, i = 0..3   wgsl:52-53
+    float sample_ay[4];  // ((j + 0.5)/4 - 0.5) / extent.y * 2, j = 0..3
 };
 
 __device__ __forceinline__ uint32_t frame_row(const FrameParams &fp, uint32_t ry) {
@@ -190,28 +195,40 @@ __device__ __forceinline__ void mat4_mul(const float *m, float x, float y, float
         out[r] = acc;
     }
 }
-// Ray generation is ~80 flops per sample (<0.5 % of the work) and feeds every threshold
-// decision downstream, so it is evaluated with exact roundings in both modes.
+// Matrix * vector in the arithmetic mode of the caller: exact = one rounding per operation, left to right (rule 3).
+template <bool EX>
+__device__ __forceinline__ void mat4_mul_t(const float *m, float x, float y, float z, float w, float out[4]) {
+    if (EX) {
+        mat4_mul(m, x, y, z, w, out);
+    } else {
+#pragma unroll
+        for (int r = 0; r < 4; ++r) out[r] = fmaf(m[12 + r], w, fmaf(m[8 + r], z, fmaf(m[4 + r], y, m[r] * x)));
+    }
+}
+// Ray generation (wgsl:39-62).  Exact mode evaluates it with one rounding per operation.  Fast mode uses FMA matrix
+// products and a reciprocal square root: for a 3-instruction program ray generation is ~20 % of the frame
+// (profiles/r1_s6_NOTES.md), not the ~0.5 % it is for the deep scene.  The pixel -> pt_screen mapping stays exact in
+// both modes (one division per pixel), and so do the per-frame constants in FrameParams.
+template <bool EX>
 __device__ __forceinline__ void gen_ray(const FrameParams &fp, uint32_t px, uint32_t py, uint32_t sample,
                                         float ro[3], float rd[3]) {
     const float sx = __fsub_rn(__fmul_rn(__fdiv_rn(__fadd_rn((float)px, 0.5f), (float)fp.W), 2.0f), 1.0f);
     const float sy = __fsub_rn(1.0f, __fmul_rn(__fdiv_rn(__fadd_rn((float)py, 0.5f), (float)fp.H), 2.0f));
-    float ro4[4];
-    mat4_mul(fp.inv_view, 0.0f, 0.0f, 0.0f, 1.0f, ro4);  // wgsl:39-40
-    const uint32_t i = sample >> 2, j = sample & 3u;     // wgsl:44-45: i outer (x), j inner (y)
-    const float offx = __fsub_rn(__fdiv_rn(__fadd_rn((float)i, 0.5f), 4.0f), 0.5f);  // wgsl:52
-    const float offy = __fsub_rn(__fdiv_rn(__fadd_rn((float)j, 0.5f), 4.0f), 0.5f);
-    const float ax = __fmul_rn(__fdiv_rn(offx, fp.extent[0]), 2.0f);  // wgsl:53
-    const float ay = __fmul_rn(__fdiv_rn(offy, fp.extent[1]), 2.0f);
+    const float ax = fp.sample_ax[sample >> 2], ay = fp.sample_ay[sample & 3u];  // wgsl:44-45: i outer (x), j inner (y)
     float pv[4], pw[4];
-    mat4_mul(fp.inv_proj, __fadd_rn(sx, ax), __fadd_rn(sy, ay), -1.0f, 1.0f, pv);  // wgsl:56-58
-    mat4_mul(fp.inv_view, pv[0], pv[1], pv[2], pv[3], pw);                          // wgsl:59
-    const float dx = __fsub_rn(pw[0], ro4[0]), dy = __fsub_rn(pw[1], ro4[1]);
-    const float dz = __fsub_rn(pw[2], ro4[2]), dw = __fsub_rn(pw[3], ro4[3]);
-    const float len = __fsqrt_rn(__fadd_rn(
-        __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz)), __fmul_rn(dw, dw)));
-    rd[0] = __fdiv_rn(dx, len); rd[1] = __fdiv_rn(dy, len); rd[2] = __fdiv_rn(dz, len);  // wgsl:62
-    ro[0] = ro4[0]; ro[1] = ro4[1]; ro[2] = ro4[2];
+    mat4_mul_t<EX>(fp.inv_proj, __fadd_rn(sx, ax), __fadd_rn(sy, ay), -1.0f, 1.0f, pv);  // wgsl:56-58
+    mat4_mul_t<EX>(fp.inv_view, pv[0], pv[1], pv[2], pv[3], pw);                          // wgsl:59
+    const float dx = __fsub_rn(pw[0], fp.ro4[0]), dy = __fsub_rn(pw[1], fp.ro4[1]);
+    const float dz = __fsub_rn(pw[2], fp.ro4[2]), dw = __fsub_rn(pw[3], fp.ro4[3]);
+    if (EX) {
+        const float len = __fsqrt_rn(__fadd_rn(
+            __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz)), __fmul_rn(dw, dw)));
+        rd[0] = __fdiv_rn(dx, len); rd[1] = __fdiv_rn(dy, len); rd[2] = __fdiv_rn(dz, len);  // wgsl:62
+    } else {
+        const float inv = rsqrtf(fmaf(dw, dw, fmaf(dz, dz, fmaf(dy, dy, dx * dx))));
+        rd[0] = dx * inv; rd[1] = dy * inv; rd[2] = dz * inv;
+    }
+    ro[0] = fp.ro4[0]; ro[1] = fp.ro4[1]; ro[2] = fp.ro4[2];
 }
 
 // ---- hit shading wgsl:100-105 given the un-normalised tetrahedron sum n (wgsl:138-143) --------

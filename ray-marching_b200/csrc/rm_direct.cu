@@ -58,7 +58,7 @@ k_direct(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ prog
         const uint32_t fy = frame_row(fp, ry);
         RM_FOR_R {
             float o[3], d[3], c[3], t;
-            gen_ray(fp, px, fy, grp * R + (uint32_t)r, o, d);  // wgsl:39-62
+            gen_ray<EX>(fp, px, fy, grp * R + (uint32_t)r, o, d);  // wgsl:39-62
             ro[0] = o[0]; ro[1] = o[1]; ro[2] = o[2];
             rdx[r] = d[0]; rdy[r] = d[1]; rdz[r] = d[2];
             const int cls = shade_miss(o, d, c, t);  // wgsl:117-130: what the ray gets if it never hits

@@ -61,7 +61,7 @@ k_samples_simple(const __grid_constant__ FrameParams fp, const RmInsn *__restric
         const uint32_t sample = (uint32_t)(idx & 15u);
         const uint32_t px = (uint32_t)(pix % fp.W), py = frame_row(fp, (uint32_t)(pix / fp.W));
         float ro[3], rd[3], t;
-        gen_ray(fp, px, py, sample, ro, rd);
+        gen_ray<EX>(fp, px, py, sample, ro, rd);
         const float code = march_one<EX>(fp, s_prog, ro, rd, cls, t, n_step);
         codes[idx] = code;
         if (dbg.cls) dbg.cls[idx] = (uint8_t)cls;

@@ -51,9 +51,7 @@ k_wavefront(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ p
     // ray origin = inv_view * (0,0,0,1)  (wgsl:39-40) — identical for every ray of the frame
     float ro[3];
     {
-        float ro4[4];
-        mat4_mul(fp.inv_view, 0.0f, 0.0f, 0.0f, 1.0f, ro4);
-        ro[0] = ro4[0]; ro[1] = ro4[1]; ro[2] = ro4[2];
+        ro[0] = fp.ro4[0]; ro[1] = fp.ro4[1]; ro[2] = fp.ro4[2];
     }
 
     float rdx[R], rdy[R], rdz[R], dist[R];
@@ -96,7 +94,7 @@ k_wavefront(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ p
                 float code = RM_CODE_SKY;
                 float o[3], d[3] = {0.f, 0.f, 0.f};
                 if (inside) {
-                    gen_ray(fp, px, frame_row(fp, ry), q >> 5, o, d);
+                    gen_ray<EX>(fp, px, frame_row(fp, ry), q >> 5, o, d);
                     float c[3], t;
                     const int cls = shade_miss(ro, d, c, t);  // wgsl:117-130
                     code = cls == 0 ? RM_CODE_SKY : (c[0] > 0.2f ? RM_CODE_FLOOR_LIGHT : RM_CODE_FLOOR_DARK);
