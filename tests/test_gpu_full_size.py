@@ -1,0 +1,92 @@
+"""Full-size parity (BASELINE.json configs 3-5) through properties that do not need the CPU oracle at that size:
+the four CUDA kernels — production, both wavefront generations, one-thread-per-sample — must produce the same bytes; a row
+band must equal the same rows of the full frame; interleaved strips must reassemble to it; a pose batch returned to the
+host must equal single frames.  (The oracle itself pins the kernels bit for bit at reduced sizes, tests/test_gpu_parity.py;
+these tests carry that pin to 3840x2160 and 7680x4320.)"""
+import hashlib
+import importlib
+
+import numpy as np
+import pytest
+
+import helpers as h
+import rm_import
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def rm():
+    return rm_import.load()
+
+
+@pytest.fixture()
+def ctx(rm):
+    c = rm.Context(0)
+    yield c
+    c.close()
+
+
+def digest(a: np.ndarray) -> str:
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+@pytest.mark.parametrize("mode", ["exact", "fast"])
+def test_cfg3_all_kernels_same_bytes_at_3840x2160(rm, ctx, mode):
+    W, H = 3840, 2160
+    cmd, words = h.scene_s2()
+    u = h.orbit_uniforms(W, H, yaw=0.6, pitch=0.4)
+    ctx.set_mode(rm.MODE_EXACT if mode == "exact" else rm.MODE_FAST)
+    got = {}
+    for name in ("DIRECT", "WAVEFRONT2", "WAVEFRONT", "SIMPLE"):
+        ctx.set_kernel(getattr(rm, "KERNEL_" + name))
+        ctx.set_counters(True)
+        img = ctx.render(u, cmd, words, W, H)
+        got[name] = (digest(img), tuple(int(x) for x in ctx.get_counters()))
+        ctx.set_counters(False)
+        assert img[..., 3].min() == 255 and img[..., :3].max() > 0
+    assert len({v for v in got.values()}) == 1, got
+    n_step, n_hit, n_floor, n_sample = got["DIRECT"][1]
+    assert n_sample == W * H * 16 and 0 < n_hit < n_sample and n_step > n_sample
+
+
+def test_cfg3_band_equals_rows_of_the_full_frame(rm, ctx):
+    W, H = 3840, 2160
+    cmd, words = h.scene_s2()
+    u = h.orbit_uniforms(W, H, yaw=0.6, pitch=0.4)
+    ctx.set_mode(rm.MODE_FAST)
+    full = ctx.render(u, cmd, words, W, H)
+    for row0, nrows in ((0, 270), (1003, 517), (2159, 1)):
+        band = ctx.render(u, cmd, words, W, H, row0=row0, nrows=nrows)
+        assert np.array_equal(band, full[row0:row0 + nrows]), (row0, nrows)
+
+
+def test_cfg4_strips_reassemble_the_7680x4320_frame(rm, ctx):
+    sh = importlib.import_module("ray_marching_b200.sharding")
+    W, H, strip, world = 7680, 4320, 16, 8
+    cmd, words = h.scene_s2()
+    u = h.orbit_uniforms(W, H, yaw=0.6, pitch=0.4)
+    ctx.set_mode(rm.MODE_FAST)
+    full = ctx.render(u, cmd, words, W, H)
+    rows_max = sh.max_local_rows(H, strip, world)
+    gathered = np.zeros((world, rows_max, W, 4), np.uint8)
+    ctx.prepare(u, cmd, words)
+    for r in range(world):
+        n = ctx.paint_strips(W, H, strip, r, world)
+        assert n == sh.local_rows(H, strip, r, world)
+        ctx.download(gathered[r, :n])
+    assert np.array_equal(sh.reassemble(gathered, H, strip, world), full)
+
+
+def test_cfg5_pose_batch_to_host_equals_single_frames_at_1080p(rm, ctx):
+    W, H, n = 1920, 1080, 9
+    cmd, words = h.scene_s1()
+    us = [h.orbit_uniforms(W, H, yaw=2 * np.pi * k / 1024 * 113, pitch=0.4) for k in range(n)]
+    ctx.set_mode(rm.MODE_FAST)
+    singles = [digest(ctx.render(u, cmd, words, W, H)) for u in us]
+    buf = rm.PinnedBuffer(n * W * H * 4)
+    ctx.prepare(us[0], cmd, words)
+    ctx.paint_poses_host(b"".join(us), n, W, H, buf.ptr)
+    got = buf.array.reshape(n, H, W, 4)
+    assert [digest(got[k]) for k in range(n)] == singles
+    buf.free()
