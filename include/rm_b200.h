@@ -125,6 +125,22 @@ RM_API int rm_paint(rm_ctx *ctx, uint32_t W, uint32_t H, uint32_t row0, uint32_t
 RM_API int rm_paint_strips(rm_ctx *ctx, uint32_t W, uint32_t H, uint32_t strip_rows, uint32_t first_strip,
                            uint32_t strip_step, void *dst_rgba8_dev, size_t pitch_bytes, void *cuda_stream,
                            uint32_t *rows_painted);
+/* Strips of this shard stored straight into a WHOLE-frame buffer at their frame rows — typically GPU 0's frame, opened
+ * in this process with rm_shared_frame_open, so the render kernel's 128-bit stores travel over NVLink and the frame
+ * needs no gather and no re-order (config 4; SURVEY.md 8(e) "direct P2P stores into GPU0's framebuffer").  Pixels are
+ * bit-identical to a full-frame rm_paint.  Completion across processes is the caller's barrier (e.g. an all-reduce
+ * enqueued after this call on every rank). */
+RM_API int rm_paint_strips_into(rm_ctx *ctx, uint32_t W, uint32_t H, uint32_t strip_rows, uint32_t first_strip,
+                                uint32_t strip_step, void *frame_rgba8_dev, size_t pitch_bytes, void *cuda_stream,
+                                uint32_t *rows_painted);
+/* A device allocation other processes (one per GPU) can map: create on the owner, send the 64 handle bytes to the
+ * peers by any channel, open there.  close releases a mapping (peer) or the allocation (owner); rm_destroy closes all. */
+#define RM_IPC_HANDLE_BYTES 64u
+RM_API int rm_shared_frame_create(rm_ctx *ctx, size_t bytes, void **dev_ptr, void *handle64);
+RM_API int rm_shared_frame_open(rm_ctx *ctx, const void *handle64, void **dev_ptr);
+RM_API int rm_shared_frame_close(rm_ctx *ctx, void *dev_ptr);
+/* Device -> host copy of any device pointer this process can address; synchronises the stream. */
+RM_API int rm_copy_to_host(rm_ctx *ctx, const void *dev_ptr, void *host, size_t bytes, void *cuda_stream);
 /* Pose batch (config 5): paints n_poses frames from an array of 144-byte uniform blocks held in
  * HOST memory; frame p goes to dst + p*frame_stride_bytes (device memory), or, when dst is NULL,
  * every frame overwrites the ctx-owned buffer (throughput mode). */

@@ -27,7 +27,8 @@ UNIFORMS_BYTES, LIMITS_BYTES = 144, 12
 # every symbol include/rm_b200.h declares (checked by tests/test_abi_symbols.py)
 ABI_SYMBOLS = [
     "rm_create", "rm_create_ex", "rm_destroy", "rm_set_limits", "rm_set_mode", "rm_get_mode", "rm_set_kernel",
-    "rm_prepare", "rm_prepare_uniforms", "rm_program_uploads", "rm_validate_program", "rm_paint", "rm_paint_strips", "rm_paint_poses", "rm_paint_poses_host", "rm_download",
+    "rm_prepare", "rm_prepare_uniforms", "rm_program_uploads", "rm_validate_program", "rm_paint", "rm_paint_strips", "rm_paint_strips_into", "rm_shared_frame_create", "rm_shared_frame_open",
+    "rm_shared_frame_close", "rm_copy_to_host", "rm_paint_poses", "rm_paint_poses_host", "rm_download",
     "rm_sync", "rm_paint_debug", "rm_map", "rm_set_counters", "rm_get_counters", "rm_mark", "rm_elapsed_ms",
     "rm_flush_l2", "rm_fp32_peak", "rm_launch_count", "rm_host_alloc", "rm_host_free", "rm_last_error",
     "rm_strerror", "rm_version",
@@ -79,6 +80,11 @@ def lib() -> C.CDLL:
             "rm_paint_poses_host": (i, [vp, vp, u32, u32, u32, vp, sz, u32]),
             "rm_program_uploads": (u64, [vp]),
             "rm_paint_strips": (i, [vp, u32, u32, u32, u32, u32, vp, sz, vp, C.POINTER(u32)]),
+            "rm_paint_strips_into": (i, [vp, u32, u32, u32, u32, u32, vp, sz, vp, C.POINTER(u32)]),
+            "rm_shared_frame_create": (i, [vp, sz, C.POINTER(vp), vp]),
+            "rm_shared_frame_open": (i, [vp, vp, C.POINTER(vp)]),
+            "rm_shared_frame_close": (i, [vp, vp]),
+            "rm_copy_to_host": (i, [vp, vp, vp, sz, vp]),
             "rm_download": (i, [vp, vp, sz]),
             "rm_sync": (i, [vp]),
             "rm_paint_debug": (i, [vp, u32, u32, u32, u32, vp, vp, vp, vp]),
@@ -201,6 +207,38 @@ class Context:
         self._chk(self._L.rm_paint_strips(self._h, W, H, strip_rows, first_strip, strip_step, dst_ptr, pitch, stream,
                                           C.byref(n)))
         return int(n.value)
+
+    def paint_strips_into(self, W: int, H: int, strip_rows: int, first_strip: int, strip_step: int, frame_ptr: int,
+                          pitch: int | None = None, stream: int | None = None) -> int:
+        """This shard's strips stored at their frame rows in a whole-frame buffer (possibly another GPU's)."""
+        n = C.c_uint32()
+        self._chk(self._L.rm_paint_strips_into(self._h, W, H, strip_rows, first_strip, strip_step, frame_ptr,
+                                               pitch or W * 4, stream, C.byref(n)))
+        return int(n.value)
+
+    def shared_frame_create(self, nbytes: int) -> tuple[int, bytes]:
+        """-> (device pointer, 64-byte handle to send to the other processes)."""
+        p, hnd = C.c_void_p(), C.create_string_buffer(64)
+        self._chk(self._L.rm_shared_frame_create(self._h, nbytes, C.byref(p), hnd))
+        return int(p.value), hnd.raw
+
+    def shared_frame_open(self, handle: bytes) -> int:
+        assert len(handle) == 64
+        p = C.c_void_p()
+        self._chk(self._L.rm_shared_frame_open(self._h, C.create_string_buffer(handle, 64), C.byref(p)))
+        return int(p.value)
+
+    def shared_frame_close(self, ptr: int):
+        self._chk(self._L.rm_shared_frame_close(self._h, ptr))
+
+    def copy_to_host(self, dev_ptr: int, out, nbytes: int | None = None, stream: int | None = None):
+        """Device -> host copy of any addressable device pointer into a PinnedBuffer or a C-contiguous array."""
+        if isinstance(out, PinnedBuffer):
+            self._chk(self._L.rm_copy_to_host(self._h, dev_ptr, out.ptr, nbytes or out.nbytes, stream))
+            return out.array
+        assert out.flags["C_CONTIGUOUS"]
+        self._chk(self._L.rm_copy_to_host(self._h, dev_ptr, out.ctypes.data, nbytes or out.nbytes, stream))
+        return out
 
     def paint_poses(self, uniforms_array: bytes, n_poses: int, W: int, H: int, dst_ptr: int | None = None,
                     pitch: int = 0, frame_stride: int = 0, stream: int | None = None):

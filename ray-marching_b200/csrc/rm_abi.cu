@@ -58,6 +58,8 @@ struct rm_ctx {
     std::vector<uint32_t> last_words;
     uint32_t last_cmd_count = 0;
     uint64_t prog_uploads = 0;
+    // shared frames (rm_shared_frame_*): allocations this ctx owns, and peer allocations it has opened over CUDA IPC
+    std::vector<void *> shared_owned, shared_opened;
     std::string err;
 };
 
@@ -99,6 +101,7 @@ FrameParams make_params(const rm_ctx *c, const float *u, uint32_t W, uint32_t H,
     fp.max_iter = c->max_iter;
     fp.W = W; fp.H = H; fp.row0 = row0; fp.nrows = nrows;
     fp.strip_rows = 0; fp.strip_pitch = 0;
+    fp.dst_frame_rows = 0;
     fp.n_insn = (uint32_t)c->prog.insns.size();
     // per-frame ray-generation constants: the shader's expressions, one IEEE float operation at a time
     // (this file is compiled with -ffp-contract=off; volatile keeps the compiler from folding x*0)
@@ -191,6 +194,8 @@ void rm_destroy(rm_ctx *c) {
     if (c->upload_done) cudaEventDestroy(c->upload_done);
     if (c->d_prog) cudaFree(c->d_prog);
     if (c->h_prog) cudaFreeHost(c->h_prog);
+    for (void *p : c->shared_opened) cudaIpcCloseMemHandle(p);
+    for (void *p : c->shared_owned) cudaFree(p);
     if (c->d_fb) cudaFree(c->d_fb);
     if (c->copy_stream) { cudaStreamSynchronize(c->copy_stream); cudaStreamDestroy(c->copy_stream); }
     if (c->d_ring) cudaFree(c->d_ring);

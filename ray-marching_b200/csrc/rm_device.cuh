@@ -35,6 +35,9 @@ struct FrameParams {
     // row0 + (ry / strip_rows) * strip_pitch + ry % strip_rows; strip_pitch == 0 = contiguous band
     uint32_t strip_rows, strip_pitch;
     uint32_t n_insn;     // decoded instruction count (0 = empty scene)
+    // 0: dst holds the band's rows packed (local row ry -> dst row ry).  1: dst is the WHOLE frame and every row lands
+    // at its frame position (frame_row(ry)) — used to store strips straight into another GPU's frame over NVLink.
+    uint32_t dst_frame_rows;
     // Per-frame constants of ray generation, computed once on the host with the same IEEE float operations the
     // shader's expressions denote (rm_abi.cu make_params), so they are bit-identical to evaluating them per ray:
     float ro4[4];        // inv_view * (0,0,0,1)                        wgsl:39-40
@@ -45,6 +48,11 @@ struct FrameParams {
 __device__ __forceinline__ uint32_t frame_row(const FrameParams &fp, uint32_t ry) {
     if (fp.strip_pitch == 0) return fp.row0 + ry;
     return fp.row0 + (ry / fp.strip_rows) * fp.strip_pitch + ry % fp.strip_rows;
+}
+
+// row of dst that local row ry of the band is stored to
+__device__ __forceinline__ uint32_t dst_row(const FrameParams &fp, uint32_t ry) {
+    return fp.dst_frame_rows ? frame_row(fp, ry) : ry;
 }
 
 template <bool EX>

@@ -152,9 +152,9 @@ k_direct(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ prog
     const uint32_t row_q = (ty * 4u + (uint32_t)warp) * ROWS + (uint32_t)(q4 >> 3);
     if (x0 + TILE_W <= fp.W && (pitch & 15) == 0) {  // warp-uniform
         if (lane < 2 * ROWS && row_q < fp.nrows)
-            *reinterpret_cast<uint4 *>(dst + (size_t)row_q * pitch + (size_t)(x0 + (q4 & 7)) * 4) = v;
+            *reinterpret_cast<uint4 *>(dst + (size_t)dst_row(fp, row_q) * pitch + (size_t)(x0 + (q4 & 7)) * 4) = v;
     } else if (inside && grp == 0) {
-        *reinterpret_cast<uint32_t *>(dst + (size_t)ry * pitch + (size_t)px * 4) = pix;
+        *reinterpret_cast<uint32_t *>(dst + (size_t)dst_row(fp, ry) * pitch + (size_t)px * 4) = pix;
     }
 
     if (COUNT) {

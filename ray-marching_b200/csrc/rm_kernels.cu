@@ -99,7 +99,7 @@ k_resolve(const __grid_constant__ FrameParams fp, const float *__restrict__ code
         c[4 * q] = v.x; c[4 * q + 1] = v.y; c[4 * q + 2] = v.z; c[4 * q + 3] = v.w;
     }
     const uint32_t x = (uint32_t)(pix % fp.W), y = (uint32_t)(pix / fp.W);
-    *reinterpret_cast<uint32_t *>(dst + (size_t)y * pitch + (size_t)x * 4) = resolve_pixel(c);
+    *reinterpret_cast<uint32_t *>(dst + (size_t)dst_row(fp, y) * pitch + (size_t)x * 4) = resolve_pixel(c);
 }
 
 template <bool EX>

@@ -270,10 +270,10 @@ k_wavefront2(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ 
                     v.z = __shfl_sync(FULL, pix, srcl + 2);
                     v.w = __shfl_sync(FULL, pix, srcl + 3);
                     if (lane < 8)
-                        *reinterpret_cast<uint4 *>(dst + (size_t)(y0 + row) * pitch + (size_t)(x0 + half * 4) * 4) = v;
+                        *reinterpret_cast<uint4 *>(dst + (size_t)dst_row(fp, y0 + row) * pitch + (size_t)(x0 + half * 4) * 4) = v;
                 } else {
                     const uint32_t x = x0 + (lane & 7), y = y0 + (lane >> 3);
-                    if (x < fp.W && y < fp.nrows) *reinterpret_cast<uint32_t *>(dst + (size_t)y * pitch + (size_t)x * 4) = pix;
+                    if (x < fp.W && y < fp.nrows) *reinterpret_cast<uint32_t *>(dst + (size_t)dst_row(fp, y) * pitch + (size_t)x * 4) = pix;
                 }
                 __syncwarp();
                 if (lane == 0) ws.tile[k] = -1;
