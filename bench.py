@@ -139,6 +139,9 @@ def main():
     ap.add_argument("--mode", default="fast", choices=["fast", "exact"])
     ap.add_argument("--kernel", default="direct", choices=["wavefront", "simple", "wavefront2", "direct"])
     ap.add_argument("--workload", default="cfg3", choices=list(WORKLOADS))
+    ap.add_argument("--gather", default="p2p", choices=["p2p", "nccl"],
+                    help="cfg4, N>1: p2p = every rank stores its strips straight into rank 0's frame over NVLink "
+                         "(rm_paint_strips_into); nccl = packed bands + NCCL gather + re-order on rank 0")
     ap.add_argument("--poses", type=int, default=0, help="cfg5: override the 1024-pose batch size")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
@@ -220,17 +223,36 @@ def main():
         ctx.prepare(uniforms, cmd, words)
         rays_local = sharding.local_rows(H, strip, rank, world) * W * 16
         rays_step_total = W * H * 16
-        config.update(sharding=f"interleaved strips of {strip} rows, strip s -> rank s % N; NCCL gather + indexed re-order on rank 0")
         frame_out = {}
+        p2p = dist is not None and args.gather == "p2p"
+        if p2p:
+            # rank 0 owns the frame; the others map it (CUDA IPC) and their render kernels store into it over NVLink
+            hbuf = torch.zeros(64, dtype=torch.uint8, device=dev)
+            if rank == 0:
+                frame_ptr, hnd = ctx.shared_frame_create(W * H * 4)
+                hbuf.copy_(torch.frombuffer(bytearray(hnd), dtype=torch.uint8))
+            dist.broadcast(hbuf, src=0)
+            if rank != 0:
+                frame_ptr = ctx.shared_frame_open(bytes(hbuf.cpu().numpy().tobytes()))
+            done = torch.zeros(1, device=dev)
+            config.update(sharding=f"interleaved strips of {strip} rows, strip s -> rank s % N; every rank's render kernel stores its "
+                                   "strips straight into rank 0's frame over NVLink (CUDA IPC mapping), completion = one tiny all-reduce")
 
-        def step():
-            ctx.paint_strips(W, H, strip, rank, world, band.data_ptr(), W * 4, sp)
-            if dist is not None:
-                dist.gather(band, gathered, dst=0)
-                if rank == 0:
-                    frame_out["f"] = sharding.reassemble(torch.stack(gathered), H, strip, world)
-            else:
-                frame_out["f"] = band
+            def step():
+                ctx.paint_strips_into(W, H, strip, rank, world, frame_ptr, W * 4, sp)
+                dist.all_reduce(done)  # enqueued behind the paint on every rank: rank 0 passes it once all strips are stored
+                frame_out["ptr"] = frame_ptr
+        else:
+            config.update(sharding=f"interleaved strips of {strip} rows, strip s -> rank s % N; NCCL gather + indexed re-order on rank 0")
+
+            def step():
+                ctx.paint_strips(W, H, strip, rank, world, band.data_ptr(), W * 4, sp)
+                if dist is not None:
+                    dist.gather(band, gathered, dst=0)
+                    if rank == 0:
+                        frame_out["f"] = sharding.reassemble(torch.stack(gathered), H, strip, world)
+                else:
+                    frame_out["f"] = band
 
         def count_step():
             ctx.paint_strips(W, H, strip, rank, world, band.data_ptr(), W * 4, sp)
@@ -318,11 +340,21 @@ def main():
             ctx.prepare(uniforms, cmd, words)
             step()
             if rank == 0:
-                host_frame.copy_(frame_out["f"][:H], non_blocking=False)
+                if "ptr" in frame_out:
+                    stream.synchronize()
+                    ctx.copy_to_host(frame_out["ptr"], host_frame.numpy(), W * H * 4, sp)
+                else:
+                    host_frame.copy_(frame_out["f"][:H], non_blocking=False)
             barrier()
         e2e_ms_local = (time.perf_counter() - t0) * 1e3 / n_e2e
         # uniforms + limits travel with every launch; the program only when rm_prepare really uploaded it
         h2d, d2h = 144 + 12 + (ctx.program_uploads - up0) * (4 + int(len(words)) * 4) // n_e2e, W * H * 4
+        if rank == 0:  # untimed: the frame the ranks assembled must equal rank 0's own full-frame render, byte for byte
+            alone = np.empty((H, W, 4), np.uint8)
+            ctx.paint(W, H)
+            ctx.download(alone)
+            config["frame_check"] = bool(np.array_equal(alone, host_frame.numpy()))
+        barrier()
     elif args.workload == "cfg5":
         # host uniform blocks in, EVERY frame back in host memory (rm_paint_poses_host: the D2H copy of frame p
         # overlaps the render of frame p+1); the frames land in a pinned 32-frame host ring, as a consumer would drain them
