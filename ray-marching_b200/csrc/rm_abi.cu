@@ -50,6 +50,9 @@ struct rm_ctx {
     // rm_paint_poses_host: device frame ring + copy stream so that frame p's D2H overlaps frame p+1's render
     static constexpr int kRing = 3;
     cudaStream_t copy_stream = nullptr;
+    // rm_paint_poses: odd frames run on a second stream so that one frame's tail overlaps the next frame's start
+    cudaStream_t pose_stream = nullptr;
+    cudaEvent_t pose_fork = nullptr, pose_join = nullptr;
     uint8_t *d_ring = nullptr;
     size_t ring_cap = 0;
     cudaEvent_t ring_rendered[kRing] = {}, ring_copied[kRing] = {};
@@ -198,6 +201,9 @@ void rm_destroy(rm_ctx *c) {
     for (void *p : c->shared_owned) cudaFree(p);
     if (c->d_fb) cudaFree(c->d_fb);
     if (c->copy_stream) { cudaStreamSynchronize(c->copy_stream); cudaStreamDestroy(c->copy_stream); }
+    if (c->pose_stream) { cudaStreamSynchronize(c->pose_stream); cudaStreamDestroy(c->pose_stream); }
+    if (c->pose_fork) cudaEventDestroy(c->pose_fork);
+    if (c->pose_join) cudaEventDestroy(c->pose_join);
     if (c->d_ring) cudaFree(c->d_ring);
     for (auto &e : c->ring_rendered) if (e) cudaEventDestroy(e);
     for (auto &e : c->ring_copied) if (e) cudaEventDestroy(e);
