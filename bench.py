@@ -139,6 +139,9 @@ def main():
     ap.add_argument("--mode", default="fast", choices=["fast", "exact"])
     ap.add_argument("--kernel", default="direct", choices=["wavefront", "simple", "wavefront2", "direct"])
     ap.add_argument("--workload", default="cfg3", choices=list(WORKLOADS))
+    ap.add_argument("--early-out", action="store_true",
+                    help="opt-in exact early-out of the interpreter (bit-identical output, but NOT the shader's literal arithmetic "
+                         "per evaluation: reported separately, never the headline)")
     ap.add_argument("--gather", default="p2p", choices=["p2p", "nccl"],
                     help="cfg4, N>1: p2p = every rank stores its strips straight into rank 0's frame over NVLink "
                          "(rm_paint_strips_into); nccl = packed bands + NCCL gather + re-order on rank 0")
@@ -202,6 +205,9 @@ def main():
     ctx.set_kernel({"wavefront": rm.KERNEL_WAVEFRONT, "simple": rm.KERNEL_SIMPLE, "wavefront2": rm.KERNEL_WAVEFRONT2, "direct": rm.KERNEL_DIRECT}[args.kernel])
     # a dedicated non-default stream: the ABI reads a NULL stream as "the ctx's own stream", and the
     # CUDA events that time the steps must sit on the stream the kernels are launched on
+    if args.early_out:
+        ctx.set_early_out(True)
+        config["early_out"] = "ON: executed work per map_scene evaluation is less than the algorithmic FLOPs the roofline fraction counts"
     stream = torch.cuda.Stream(dev)
     torch.cuda.set_stream(stream)
     sp = stream.cuda_stream

@@ -96,6 +96,10 @@ RM_API int rm_set_limits(rm_ctx *ctx, const void *limits12);
 RM_API int rm_set_mode(rm_ctx *ctx, int mode);
 RM_API int rm_get_mode(rm_ctx *ctx);
 RM_API int rm_set_kernel(rm_ctx *ctx, int kernel);
+/* Opt-in (default 0), RM_KERNEL_DIRECT only: skip the rest of a primitive+operator instruction when a cheap lower bound of
+ * the primitive proves the accumulator unchanged.  Output is bit-identical; the work done per map_scene evaluation is not
+ * the shader's literal arithmetic any more, so numbers measured with it are reported separately. */
+RM_API int rm_set_early_out(rm_ctx *ctx, int on);
 
 /* ---- per frame: replaces RayMarchingCallback::prepare, renderer.rs:196-242 ------------------ */
 /* Validates the program (opcodes, word count, stack discipline), then uploads the 144-byte

@@ -26,7 +26,7 @@ UNIFORMS_BYTES, LIMITS_BYTES = 144, 12
 
 # every symbol include/rm_b200.h declares (checked by tests/test_abi_symbols.py)
 ABI_SYMBOLS = [
-    "rm_create", "rm_create_ex", "rm_destroy", "rm_set_limits", "rm_set_mode", "rm_get_mode", "rm_set_kernel",
+    "rm_create", "rm_create_ex", "rm_destroy", "rm_set_limits", "rm_set_mode", "rm_get_mode", "rm_set_kernel", "rm_set_early_out",
     "rm_prepare", "rm_prepare_uniforms", "rm_program_uploads", "rm_validate_program", "rm_paint", "rm_paint_strips", "rm_paint_strips_into", "rm_shared_frame_create", "rm_shared_frame_open",
     "rm_shared_frame_close", "rm_copy_to_host", "rm_paint_poses", "rm_paint_poses_host", "rm_download",
     "rm_sync", "rm_paint_debug", "rm_map", "rm_set_counters", "rm_get_counters", "rm_mark", "rm_elapsed_ms",
@@ -69,6 +69,7 @@ def lib() -> C.CDLL:
             "rm_create_ex": (i, [i, u32, C.POINTER(vp)]),
             "rm_destroy": (None, [vp]),
             "rm_set_limits": (i, [vp, vp]),
+            "rm_set_early_out": (i, [vp, i]),
             "rm_set_mode": (i, [vp, i]),
             "rm_get_mode": (i, [vp]),
             "rm_set_kernel": (i, [vp, i]),
@@ -181,6 +182,9 @@ class Context:
         self._chk(self._L.rm_set_kernel(self._h, kernel))
 
     # ---- prepare (renderer.rs:196-242)
+    def set_early_out(self, on: bool):
+        self._chk(self._L.rm_set_early_out(self._h, int(bool(on))))
+
     def prepare(self, uniforms: bytes, cmd_count: int, words):
         assert len(uniforms) == UNIFORMS_BYTES
         w = _words_arr(words)

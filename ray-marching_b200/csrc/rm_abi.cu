@@ -32,6 +32,7 @@ struct rm_ctx {
     int kernel = RM_KERNEL_DIRECT;
     bool prepared = false;
     bool counters_on = false;
+    bool early_out = false;  // rm_set_early_out: opt-in, never on by default
     float limits_f[2] = {0.01f, 100.0f};  // renderer.rs:133-137
     uint32_t max_iter = 100;
     float uniforms[36] = {};

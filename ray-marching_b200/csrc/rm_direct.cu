@@ -28,7 +28,7 @@ constexpr int DIRECT_THREADS = 128;
 #ifndef RM_DIRECT_MINB8
 #define RM_DIRECT_MINB8 6
 #endif
-template <bool EX, int R, bool COUNT>
+template <bool EX, int R, bool COUNT, bool EO>
 __global__ void __launch_bounds__(DIRECT_THREADS, (R == 8 ? RM_DIRECT_MINB8 : 0))
 k_direct(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ prog_g, uint8_t *__restrict__ dst, size_t pitch,
          unsigned long long *__restrict__ counters) {
@@ -78,7 +78,7 @@ k_direct(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ prog
             pz_[r] = A::mad(rdz[r], dist[r], ro[2]);
         }
         RM_FOR_R asm volatile("" : "+f"(px_[r]), "+f"(py_[r]), "+f"(pz_[r]));
-        map_evalR<EX, R>(s_prog, fp.n_insn, fp.max_dist, px_, py_, pz_, s, spill);
+        map_evalR<EX, R, EO>(s_prog, fp.n_insn, fp.max_dist, px_, py_, pz_, s, spill);
         const bool last = it + 1 >= fp.max_iter;  // loop bound wgsl:90
         RM_FOR_R {
             const uint32_t bit = 1u << r;
@@ -116,7 +116,7 @@ k_direct(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ prog
             px_[4 * j + 3] = __fadd_rn(hx[j], ep); py_[4 * j + 3] = __fadd_rn(hy[j], ep); pz_[4 * j + 3] = __fadd_rn(hz[j], ep);
         }
         RM_FOR_R asm volatile("" : "+f"(px_[r]), "+f"(py_[r]), "+f"(pz_[r]));
-        map_evalR<EX, R>(s_prog, fp.n_insn, fp.max_dist, px_, py_, pz_, s, spill);
+        map_evalR<EX, R, EO>(s_prog, fp.n_insn, fp.max_dist, px_, py_, pz_, s, spill);
 #pragma unroll
         for (int j = 0; j < R / 4; ++j) {
             if (rr[j] >= 0) {
@@ -169,10 +169,10 @@ k_direct(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ prog
     }
 }
 
-template <bool EX, int R, bool COUNT>
+template <bool EX, int R, bool COUNT, bool EO>
 cudaError_t launch_direct_t(const FrameParams &fp, const RmInsn *prog, uint8_t *dst, size_t pitch,
                             unsigned long long *counters, cudaStream_t st) {
-    auto kern = k_direct<EX, R, COUNT>;
+    auto kern = k_direct<EX, R, COUNT, EO>;
     constexpr uint32_t tile_h = 4u * ((32u / (16u / R)) / 8u);
     const size_t smem = (size_t)fp.n_insn * sizeof(RmInsn);
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -184,7 +184,7 @@ cudaError_t launch_direct_t(const FrameParams &fp, const RmInsn *prog, uint8_t *
 
 }  // namespace
 
-cudaError_t launch_direct(bool exact, const FrameParams &fp, const RmInsn *prog_dev, uint8_t *dst, size_t pitch,
+cudaError_t launch_direct(bool exact, bool early_out, const FrameParams &fp, const RmInsn *prog_dev, uint8_t *dst, size_t pitch,
                           unsigned long long *counters, cudaStream_t st) {
     if (fp.nrows == 0 || fp.W == 0) return cudaSuccess;
     // Rays per thread: 4 for shallow programs (more threads, less lock-step waste), 8 for deep ones (fetch/dispatch
@@ -197,11 +197,13 @@ cudaError_t launch_direct(bool exact, const FrameParams &fp, const RmInsn *prog_
         return (v == 4 || v == 8) ? v : 0;
     }();
     const int kR = kForce ? kForce : (fp.n_insn <= 4 ? 4 : 8);
-#define RM_DIRECT_DISPATCH(EXV, RV)                                                        \
-    (counters ? launch_direct_t<EXV, RV, true>(fp, prog_dev, dst, pitch, counters, st)    \
-              : launch_direct_t<EXV, RV, false>(fp, prog_dev, dst, pitch, counters, st))
+#define RM_DIRECT_DISPATCH2(EXV, RV, EOV)                                                      \
+    (counters ? launch_direct_t<EXV, RV, true, EOV>(fp, prog_dev, dst, pitch, counters, st)     \
+              : launch_direct_t<EXV, RV, false, EOV>(fp, prog_dev, dst, pitch, counters, st))
+#define RM_DIRECT_DISPATCH(EXV, RV) (early_out ? RM_DIRECT_DISPATCH2(EXV, RV, true) : RM_DIRECT_DISPATCH2(EXV, RV, false))
     if (exact) return kR == 8 ? RM_DIRECT_DISPATCH(true, 8) : RM_DIRECT_DISPATCH(true, 4);
     return kR == 8 ? RM_DIRECT_DISPATCH(false, 8) : RM_DIRECT_DISPATCH(false, 4);
+#undef RM_DIRECT_DISPATCH2
 #undef RM_DIRECT_DISPATCH
 }
 

@@ -27,7 +27,8 @@ cudaError_t launch_wavefront2(WavefrontState *ws, bool exact, const FrameParams 
                               uint8_t *dst, size_t pitch, unsigned long long *counters, cudaStream_t st);
 
 // Shallow-program kernel (rm_direct.cu): 4 sample rays per thread, fused in-order resolve, no queues.
-cudaError_t launch_direct(bool exact, const FrameParams &fp, const RmInsn *prog_dev, uint8_t *dst, size_t pitch,
+// early_out: opt-in exact early-out of the interpreter (rm_wavefront_common.cuh), bit-identical output.
+cudaError_t launch_direct(bool exact, bool early_out, const FrameParams &fp, const RmInsn *prog_dev, uint8_t *dst, size_t pitch,
                           unsigned long long *counters, cudaStream_t st);
 
 }  // namespace rm

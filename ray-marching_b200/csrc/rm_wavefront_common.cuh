@@ -57,7 +57,15 @@ __device__ __forceinline__ float prim_eval(float x, float y, float z, const floa
 __device__ __forceinline__ void acc_min(float &acc, float v) { asm("min.f32 %0, %0, %1;" : "+f"(acc) : "f"(v)); }
 __device__ __forceinline__ void acc_max(float &acc, float v) { asm("max.f32 %0, %0, %1;" : "+f"(acc) : "f"(v)); }
 
-template <bool EX, int R>
+// Early-out (EO, opt-in, off in every default path): for acc = op(acc, prim(p)) with op in {union, smooth-union,
+// subtraction} the accumulator is provably unchanged — bit for bit, in both arithmetic modes — when a cheap lower bound
+// of prim(p) already exceeds  acc (+ k for the smooth union), resp. -acc for the subtraction:
+//   sphere: |p-c|^2 >= T*max(T,0) with T = +-acc + r (+ k) + slack;   box: max(qx,qy,qz) >= +-acc (+ k) + slack
+// (max(q) <= box distance).  Then e = max(k - |acc - v|, 0) is exactly 0 and min(acc, v) = acc / max(acc, -v) = acc.
+// If that holds for all R rays of the thread the rest of the instruction is skipped (sqrt, the blend, most of the box).
+// The slack (1e-4) covers the few roundings between the bound and the value for coordinates up to max_dist = 100.
+#define RM_EO_SLACK 1e-4f
+template <bool EX, int R, bool EO = false>
 __device__ __forceinline__ void map_evalR(const float4 *__restrict__ prog, uint32_t n_insn, float max_dist,
                                           const float (&px)[R], const float (&py)[R], const float (&pz)[R],
                                           float (&acc)[R], float (*spill)[R]) {
@@ -75,6 +83,31 @@ __device__ __forceinline__ void map_evalR(const float4 *__restrict__ prog, uint3
         // Dispatch on one-hot flag bits, most frequent fused ops first (primitive kind, then
         // smooth-union / union / subtraction / intersection / push / first).
         if (!(fl & FLAG_POP)) {
+            if (EO && (fl & (FLAG_SMOOTH | FLAG_UNION | FLAG_SUB))) {
+                using A = Arith<EX>;
+                const float sgn = (fl & FLAG_SUB) ? -1.0f : 1.0f;
+                const float thr = ((fl & FLAG_SMOOTH) ? q1.z : 0.0f) + RM_EO_SLACK;
+                // one signed margin per ray, all independent (ILP = R), then ONE minimum and ONE branch: written with
+                // `skip = skip && cond` the compiler short-circuits ray by ray into a serial chain of predicated tests
+                float worst = 3.0e38f;
+                if (fl & FLAG_BOX) {
+                    RM_FOR_R {  // margin = max(q) - T,  T = +-acc (+ k) + slack;  max(q) <= box distance
+                        const float qx = A::sub(fabsf(A::sub(px[r], q0.x)), q0.w);
+                        const float qy = A::sub(fabsf(A::sub(py[r], q0.y)), q1.x);
+                        const float qz = A::sub(fabsf(A::sub(pz[r], q0.z)), q1.y);
+                        worst = fminf(worst, fmaxf(qx, fmaxf(qy, qz)) - fmaf(sgn, acc[r], thr));
+                    }
+                } else {
+                    const float thr_s = thr + q0.w;
+                    RM_FOR_R {  // margin = |p-c|^2 - T*max(T,0),  T = +-acc + r (+ k) + slack.  T < 0 means the accumulator is
+                                // already below -r <= sphere distance, so the margin |p-c|^2 >= 0 is right there too
+                        const float dx = A::sub(px[r], q0.x), dy = A::sub(py[r], q0.y), dz = A::sub(pz[r], q0.z);
+                        const float t = fmaf(sgn, acc[r], thr_s);
+                        worst = fminf(worst, fmaf(-t, fmaxf(t, 0.0f), A::dot3s(dx, dy, dz)));
+                    }
+                }
+                if (worst >= 0.0f) continue;
+            }
             float v[R];
             if (fl & FLAG_BOX) {
                 RM_FOR_R v[r] = sd_box<EX>(px[r], py[r], pz[r], q0.x, q0.y, q0.z, q0.w, q1.x, q1.y);
