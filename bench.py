@@ -101,7 +101,7 @@ def ncu_traffic(workload: str, kernel: str):
     """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture of this exact
     workload + kernel (profiles/*.ncu_summary.csv), or None.  Not measured live: a profiler is never in a timed run."""
     name = {("cfg3", "wavefront2"): "r1_s3_wavefront2_R8_cfg3.ncu_summary.csv",
-            ("cfg3", "direct"): "r1_s7_direct_R8_cfg3.ncu_summary.csv"}.get((workload, kernel))
+            ("cfg3", "direct"): "r1_final_direct_R8_cfg3.ncu_summary.csv"}.get((workload, kernel))
     if not name or not (ROOT / "profiles" / name).exists():
         return None, None
     tot, unit_scale = 0.0, {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}

@@ -22,14 +22,19 @@ namespace {
 constexpr int DIRECT_THREADS = 128;
 // R = sample rays per thread (4 or 8); a pixel's 16 samples are held by TPP = 16/R neighbouring lanes, so a warp covers
 // 32/TPP pixels = ROWS rows of 8, and the 4-warp block an 8 x (4*ROWS) pixel tile.
-// Resident blocks per SM asked of ptxas.  8-ray variant: 6 (80 registers, 148 B of spill) measured 45.19 ms on cfg3 against
-// 45.41 at 5 (96 registers) and 45.99 at 4 (123 registers, no spill) — one more warp per scheduler is worth the spill.
-// 4-ray variant: no hint (69 registers, 7 blocks); an explicit hint of 1 let ptxas take 77 and cost 6 % on cfg2.
+// Resident blocks per SM asked of ptxas (measured on B200, profiles/r1_s12_*):
+//   8-ray variant, cfg3: 4 blocks (123 registers, no spill) 45.99 ms, 5: 45.41, 6: 45.19 -> after the ray-generation change
+//   6: 44.76, 7 (72 registers, 196 B spill): 44.02, 8 (64 registers): 45.13.  One more warp per scheduler beats the spill up to 7.
+//   4-ray variant, cfg2: no hint (70 registers) 1.203 ms, 8 blocks (64 registers, 44 B spill) 1.184, 9: 1.189, 10: 1.232;
+//   an explicit hint of 1 let ptxas take 77 registers and cost 6 %.
 #ifndef RM_DIRECT_MINB8
-#define RM_DIRECT_MINB8 6
+#define RM_DIRECT_MINB8 7
+#endif
+#ifndef RM_DIRECT_MINB4
+#define RM_DIRECT_MINB4 8
 #endif
 template <bool EX, int R, bool COUNT, bool EO>
-__global__ void __launch_bounds__(DIRECT_THREADS, (R == 8 ? RM_DIRECT_MINB8 : 0))
+__global__ void __launch_bounds__(DIRECT_THREADS, (R == 8 ? RM_DIRECT_MINB8 : RM_DIRECT_MINB4))
 k_direct(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ prog_g, uint8_t *__restrict__ dst, size_t pitch,
          unsigned long long *__restrict__ counters) {
     static_assert(R == 4 || R == 8, "4 or 8 rays per thread");
