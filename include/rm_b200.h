@@ -163,6 +163,35 @@ RM_API int rm_paint_poses_host(rm_ctx *ctx, const void *uniforms144_array, uint3
 RM_API int rm_download(rm_ctx *ctx, void *host_rgba8, size_t bytes);
 RM_API int rm_sync(rm_ctx *ctx);
 
+/* ---- one host thread, several GPUs (SURVEY.md 8(b) "Multi-GPU (new surface)", 8(e)) ------------------------------ */
+/* The reference is one process with one render thread (main.rs:44-82, renderer.rs:244-255); this is the surface that
+ * thread would drive when the box has several GPUs.  A group is one rm_ctx per listed device (the <= 1.2 KB of inputs are
+ * replicated) plus a frame on the FIRST device that every member addresses over NVLink (peer access; RM_E_CUDA when a
+ * member cannot reach the first device).  Listing a device more than once is allowed.  The one-process-per-GPU form of the
+ * same thing is rm_paint_strips_into + rm_shared_frame_* and rm_paint_poses_host above. */
+typedef struct rm_group rm_group;
+RM_API int rm_group_create(const int *cuda_devices, int n, rm_group **out);
+RM_API void rm_group_destroy(rm_group *g);
+RM_API int rm_group_size(rm_group *g);
+/* Member i's context, e.g. for rm_set_kernel / rm_last_error / rm_launch_count; owned by the group. */
+RM_API rm_ctx *rm_group_ctx(rm_group *g, int i);
+RM_API int rm_group_set_mode(rm_group *g, int mode);
+RM_API int rm_group_set_limits(rm_group *g, const void *limits12);
+/* rm_prepare on every member. */
+RM_API int rm_group_prepare(rm_group *g, const void *uniforms144, uint32_t cmd_count, const uint32_t *words,
+                            uint32_t n_words);
+/* Config 4: ONE W x H frame; member i shades strips i, i+n, ... of strip_rows rows and stores them straight into the
+ * group frame on the first device.  Returns when the frame is complete there (rm_group_frame); when host_rgba8 is not
+ * NULL the frame is also copied to it (W*4*H bytes, tightly packed). */
+RM_API int rm_group_paint_bands(rm_group *g, uint32_t W, uint32_t H, uint32_t strip_rows, void *host_rgba8);
+/* Device pointer (first device) and pitch of the frame of the last rm_group_paint_bands. */
+RM_API int rm_group_frame(rm_group *g, void **dev_ptr, size_t *pitch_bytes);
+/* Config 5: pose p is rendered by member p % n and returned at host_rgba8 + p*host_frame_stride_bytes (pinned memory
+ * lets the copies overlap the renders); members run concurrently; returns when every frame is in host memory. */
+RM_API int rm_group_paint_poses(rm_group *g, const void *uniforms144_array, uint32_t n_poses, uint32_t W, uint32_t H,
+                                void *host_rgba8, size_t host_frame_stride_bytes);
+RM_API const char *rm_group_last_error(rm_group *g);
+
 /* ---- debug / verification surface (untimed) -------------------------------------------------- */
 /* Straightforward one-thread-per-sample kernels that also emit the AOVs the parity gates need.
  * All pointers are HOST memory and may be NULL.  cls: nrows*W*16 bytes (sample i*4+j);

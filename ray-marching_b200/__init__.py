@@ -24,7 +24,7 @@ MODE_EXACT, MODE_FAST = 0, 1
 KERNEL_WAVEFRONT, KERNEL_SIMPLE, KERNEL_WAVEFRONT2, KERNEL_DIRECT = 0, 1, 2, 3
 UNIFORMS_BYTES, LIMITS_BYTES = 144, 12
 
-# every symbol include/rm_b200.h declares (checked by tests/test_abi_symbols.py)
+# every symbol include/rm_b200.h declares (checked by tests/test_abi_cpu.py)
 ABI_SYMBOLS = [
     "rm_create", "rm_create_ex", "rm_destroy", "rm_set_limits", "rm_set_mode", "rm_get_mode", "rm_set_kernel", "rm_set_early_out",
     "rm_prepare", "rm_prepare_uniforms", "rm_program_uploads", "rm_validate_program", "rm_paint", "rm_paint_strips", "rm_paint_strips_into", "rm_shared_frame_create", "rm_shared_frame_open",
@@ -32,6 +32,8 @@ ABI_SYMBOLS = [
     "rm_sync", "rm_paint_debug", "rm_map", "rm_set_counters", "rm_get_counters", "rm_mark", "rm_elapsed_ms",
     "rm_flush_l2", "rm_fp32_peak", "rm_launch_count", "rm_host_alloc", "rm_host_free", "rm_last_error",
     "rm_strerror", "rm_version",
+    "rm_group_create", "rm_group_destroy", "rm_group_size", "rm_group_ctx", "rm_group_set_mode", "rm_group_set_limits",
+    "rm_group_prepare", "rm_group_paint_bands", "rm_group_frame", "rm_group_paint_poses", "rm_group_last_error",
 ]
 
 
@@ -102,6 +104,17 @@ def lib() -> C.CDLL:
             "rm_last_error": (C.c_char_p, [vp]),
             "rm_strerror": (C.c_char_p, [i]),
             "rm_version": (C.c_char_p, []),
+            "rm_group_create": (i, [C.POINTER(i), i, C.POINTER(vp)]),
+            "rm_group_destroy": (None, [vp]),
+            "rm_group_size": (i, [vp]),
+            "rm_group_ctx": (vp, [vp, i]),
+            "rm_group_set_mode": (i, [vp, i]),
+            "rm_group_set_limits": (i, [vp, vp]),
+            "rm_group_prepare": (i, [vp, vp, u32, vp, u32]),
+            "rm_group_paint_bands": (i, [vp, u32, u32, u32, vp]),
+            "rm_group_frame": (i, [vp, C.POINTER(vp), C.POINTER(sz)]),
+            "rm_group_paint_poses": (i, [vp, vp, u32, u32, u32, vp, sz]),
+            "rm_group_last_error": (C.c_char_p, [vp]),
         }
         for name, (res, args) in sig.items():
             f = getattr(L, name)
@@ -326,3 +339,83 @@ class Context:
     @property
     def launch_count(self) -> int:
         return int(self._L.rm_launch_count(self._h))
+
+
+class Group:
+    """One host thread driving several GPUs (include/rm_b200.h rm_group_*): one Context per device, the frame of
+    paint_bands lives on the first device and the others store into it over NVLink."""
+
+    def __init__(self, devices):
+        self._L = lib()
+        self.devices = [int(d) for d in devices]
+        arr = (C.c_int * len(self.devices))(*self.devices)
+        h = C.c_void_p()
+        rc = self._L.rm_group_create(arr, len(self.devices), C.byref(h))
+        if rc != RM_OK:
+            raise RmError(rc, f"rm_group_create({self.devices}): {self._L.rm_strerror(rc).decode()} "
+                              "(every device must be sm_100 and able to address the first one)")
+        self._h = h
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.rm_group_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        self.close()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __len__(self):
+        return int(self._L.rm_group_size(self._h))
+
+    def _chk(self, rc: int):
+        if rc != RM_OK:
+            raise RmError(rc, self._L.rm_group_last_error(self._h).decode() or self._L.rm_strerror(rc).decode())
+
+    def member_launch_count(self, i: int) -> int:
+        return int(self._L.rm_launch_count(self._L.rm_group_ctx(self._h, i)))
+
+    def set_kernel(self, kernel: int):
+        for i in range(len(self)):
+            rc = self._L.rm_set_kernel(self._L.rm_group_ctx(self._h, i), kernel)
+            if rc != RM_OK:
+                raise RmError(rc, self._L.rm_strerror(rc).decode())
+
+    def set_mode(self, mode: int):
+        self._chk(self._L.rm_group_set_mode(self._h, mode))
+
+    def set_limits(self, min_dist=0.01, max_dist=100.0, max_iter=100):
+        b = np.array([min_dist, max_dist], np.float32).tobytes() + np.array([max_iter], np.uint32).tobytes()
+        self._chk(self._L.rm_group_set_limits(self._h, b))
+
+    def prepare(self, uniforms: bytes, cmd_count: int, words):
+        assert len(uniforms) == UNIFORMS_BYTES
+        w = _words_arr(words)
+        self._chk(self._L.rm_group_prepare(self._h, uniforms, cmd_count, w.ctypes.data if w.size else None, w.size))
+
+    def paint_bands(self, W: int, H: int, strip_rows: int = 16, out=None):
+        """ONE frame across the members; `out` (PinnedBuffer or C-contiguous array of W*H*4 bytes) receives it."""
+        ptr = None
+        if isinstance(out, PinnedBuffer):
+            ptr = out.ptr
+        elif out is not None:
+            assert out.flags["C_CONTIGUOUS"] and out.nbytes >= W * H * 4
+            ptr = out.ctypes.data
+        self._chk(self._L.rm_group_paint_bands(self._h, W, H, strip_rows, ptr))
+        return out.array if isinstance(out, PinnedBuffer) else out
+
+    def frame(self) -> tuple[int, int]:
+        p, pitch = C.c_void_p(), C.c_size_t()
+        self._chk(self._L.rm_group_frame(self._h, C.byref(p), C.byref(pitch)))
+        return int(p.value), int(pitch.value)
+
+    def paint_poses(self, uniforms_array: bytes, n_poses: int, W: int, H: int, host_ptr: int,
+                    host_frame_stride: int | None = None):
+        assert len(uniforms_array) >= n_poses * UNIFORMS_BYTES
+        self._chk(self._L.rm_group_paint_poses(self._h, uniforms_array, n_poses, W, H, host_ptr,
+                                               host_frame_stride or W * H * 4))

@@ -79,3 +79,16 @@ def test_scene_definitions():
     assert c == 5 and len(w) == 19
     c, w = h.scene_s2()
     assert c == 63 and len(w) == 251 and rm_import.load().validate_program(c, w) == 0
+
+
+def test_group_entry_points_reject_null_arguments_without_a_device(rm):
+    L = rm.lib()
+    hnd = C.c_void_p()
+    assert L.rm_group_create(None, 2, C.byref(hnd)) == -1
+    assert L.rm_group_create((C.c_int * 1)(0), 0, C.byref(hnd)) == -1
+    assert L.rm_group_size(None) == 0 and not L.rm_group_ctx(None, 0)
+    assert L.rm_group_prepare(None, None, 0, None, 0) == -1
+    assert L.rm_group_paint_bands(None, 8, 8, 4, None) == -1
+    assert L.rm_group_paint_poses(None, None, 0, 8, 8, None, 0) == -1
+    assert L.rm_group_last_error(None) == b"null group"
+    L.rm_group_destroy(None)
