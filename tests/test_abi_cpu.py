@@ -92,3 +92,22 @@ def test_group_entry_points_reject_null_arguments_without_a_device(rm):
     assert L.rm_group_paint_poses(None, None, 0, 8, 8, None, 0) == -1
     assert L.rm_group_last_error(None) == b"null group"
     L.rm_group_destroy(None)
+
+
+def _arg_count(arglist: str) -> int:
+    arglist = arglist.strip()
+    return 0 if arglist in ("", "void") else arglist.count(",") + 1
+
+
+def test_rust_binding_declares_the_same_functions_with_the_same_arity(rm):
+    """bindings/rust/rm_sys.rs cannot be compiled here (no Rust toolchain): keep it in step with the header by name
+    and by number of arguments."""
+    header = (ROOT / "include" / "rm_b200.h").read_text()
+    header = re.sub(r"/\*.*?\*/", "", header, flags=re.S)
+    c_decl = {m.group(1): _arg_count(m.group(2))
+              for m in re.finditer(r"RM_API\s+[\w \*]+?\b(rm_\w+)\s*\(([^)]*)\)\s*;", header)}
+    rust = (ROOT / "bindings" / "rust" / "rm_sys.rs").read_text()
+    rust = re.sub(r"//.*", "", rust)
+    r_decl = {m.group(1): _arg_count(m.group(2)) for m in re.finditer(r"pub fn (rm_\w+)\s*\(([^)]*)\)", rust)}
+    assert set(c_decl) == set(rm.ABI_SYMBOLS)
+    assert r_decl == c_decl, {k: (c_decl.get(k), r_decl.get(k)) for k in set(c_decl) | set(r_decl) if c_decl.get(k) != r_decl.get(k)}
