@@ -14,6 +14,7 @@ use core::ffi::{c_char, c_void};
 
 pub const RM_OK: i32 = 0;
 pub const RM_E_INVALID_ARG: i32 = -1;
+pub const RM_E_JIT: i32 = -9;
 pub const RM_MODE_EXACT: i32 = 0;
 pub const RM_MODE_FAST: i32 = 1;
 pub const RM_KERNEL_WAVEFRONT: i32 = 0;
@@ -41,6 +42,17 @@ extern "C" {
     pub fn rm_prepare_uniforms(ctx: *mut RmCtx, uniforms144: *const u8) -> i32;
     pub fn rm_program_uploads(ctx: *mut RmCtx) -> u64;
     pub fn rm_validate_program(cmd_count: u32, words: *const u32, n_words: u32, max_words: u32) -> i32;
+
+    // program specialisation: compile the scene into the kernel (optional)
+    pub fn rm_specialize(ctx: *mut RmCtx) -> i32;
+    pub fn rm_set_specialize(ctx: *mut RmCtx, on: i32) -> i32;
+    pub fn rm_spec_info(ctx: *mut RmCtx, active: *mut i32, rays_per_thread: *mut i32, min_blocks: *mut i32,
+                        compile_ms: *mut f64, cubin_bytes: *mut u64, compiles: *mut u64, launches: *mut u64) -> i32;
+    pub fn rm_spec_status(ctx: *mut RmCtx) -> *const c_char;
+    pub fn rm_spec_source(cmd_count: u32, words: *const u32, n_words: u32, mode: i32, rays_per_thread: i32,
+                          buf: *mut c_char, cap: usize, needed: *mut usize) -> i32;
+    pub fn rm_spec_compile_check(cmd_count: u32, words: *const u32, n_words: u32, mode: i32, rays_per_thread: i32,
+                                 cubin_bytes: *mut u64, compile_ms: *mut f64, log: *mut c_char, log_cap: usize) -> i32;
 
     // per frame — RayMarchingCallback::paint (renderer.rs:244-255)
     pub fn rm_paint(ctx: *mut RmCtx, w: u32, h: u32, row0: u32, nrows: u32, dst_rgba8_dev: *mut c_void,
@@ -71,6 +83,7 @@ extern "C" {
     pub fn rm_group_ctx(g: *mut RmGroup, i: i32) -> *mut RmCtx;
     pub fn rm_group_set_mode(g: *mut RmGroup, mode: i32) -> i32;
     pub fn rm_group_set_limits(g: *mut RmGroup, limits12: *const u8) -> i32;
+    pub fn rm_group_specialize(g: *mut RmGroup) -> i32;
     pub fn rm_group_prepare(g: *mut RmGroup, uniforms144: *const u8, cmd_count: u32, words: *const u32, n_words: u32) -> i32;
     pub fn rm_group_paint_bands(g: *mut RmGroup, w: u32, h: u32, strip_rows: u32, host_rgba8: *mut c_void) -> i32;
     pub fn rm_group_frame(g: *mut RmGroup, dev_ptr: *mut *mut c_void, pitch_bytes: *mut usize) -> i32;

@@ -45,7 +45,8 @@ enum {
     RM_E_STACK_UNBALANCED = -5,  /* pop from empty stack / truncated params / empty result */
     RM_E_CUDA = -6,
     RM_E_NOT_PREPARED = -7,
-    RM_E_BAD_PARAM = -8          /* SmoothUnion k <= 0 or non-finite */
+    RM_E_BAD_PARAM = -8,         /* SmoothUnion k <= 0 or non-finite */
+    RM_E_JIT = -9                /* program specialisation failed; the interpreter kernel keeps working */
 };
 
 /* ---- byte sizes of the reference's GPU buffers --------------------------------------------- */
@@ -115,6 +116,38 @@ RM_API uint64_t rm_program_uploads(rm_ctx *ctx);
 RM_API int rm_validate_program(uint32_t cmd_count, const uint32_t *words, uint32_t n_words,
                                uint32_t max_words);
 
+/* ---- program specialisation (optional; the reference compiles its shader once, RayMarchingResources::new
+ *      renderer.rs:55-62 — here the SCENE can be compiled too) --------------------------------------------------- */
+/* By default the kernels interpret the decoded command stream: any program, no set-up cost.  A program that is painted
+ * many times (a static scene, a turntable) can instead be compiled: map_scene is emitted as straight-line CUDA — every
+ * constant an immediate, no fetch or dispatch — and built at run time (NVRTC, sm_100a) around the same kernel body.
+ * Arithmetic per ray is operation for operation the interpreter's: exact mode stays bit-identical, fast mode may round
+ * differently where the compiler contracts multiply-adds (within the parity gates).  Compiling takes of the order of a
+ * second per (program, mode) and is cached process-wide, so the contexts of a group share it.  Only RM_KERNEL_DIRECT
+ * paints are affected; with rm_set_early_out on, the interpreter is used.
+ * rm_specialize: compile the currently prepared program for the current mode now; paints use it until rm_prepare
+ *   receives different words.  RM_E_JIT (reason in rm_last_error) when NVRTC cannot be loaded (libnvrtc.so.12; the
+ *   environment variable RM_NVRTC_PATH names an exact file), the compile fails or the program is too long for the
+ *   instruction cache — painting then simply continues through the interpreter.
+ * rm_set_specialize(1): do that automatically for every program at its first paint (a stall of one compile per new
+ *   program: meant for batch rendering, not for interactive editing); failures are silent, see rm_spec_status.
+ *   rm_set_specialize(0) returns to the interpreter from the next paint on (also after rm_specialize). */
+RM_API int rm_specialize(rm_ctx *ctx);
+RM_API int rm_set_specialize(rm_ctx *ctx, int on);
+/* Whether the next RM_KERNEL_DIRECT paint (current mode, counters setting) runs specialised code, and what it is:
+ * sample rays per thread (2, 4, 8: chosen from the code size), resident blocks asked of the compiler, compile + load
+ * time, cubin size; number of compiles this context triggered and of specialised launches.  Any pointer may be NULL. */
+RM_API int rm_spec_info(rm_ctx *ctx, int *active, int *rays_per_thread, int *min_blocks, double *compile_ms,
+                        uint64_t *cubin_bytes, uint64_t *compiles, uint64_t *launches);
+RM_API const char *rm_spec_status(rm_ctx *ctx);
+/* No device needed: the generated CUDA source of a command stream (rays_per_thread 0 = automatic), and a trial
+ * compile of it (NVRTC cross-compiles for sm_100a without a GPU). */
+RM_API int rm_spec_source(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, int mode, int rays_per_thread,
+                          char *buf, size_t cap, size_t *needed);
+RM_API int rm_spec_compile_check(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, int mode,
+                                 int rays_per_thread, uint64_t *cubin_bytes, double *compile_ms, char *log,
+                                 size_t log_cap);
+
 /* ---- per frame: replaces RayMarchingCallback::paint, renderer.rs:244-255 -------------------- */
 /* Shades rows [row0,row0+nrows) of a W×H frame (row 0 = top) as RGBA8 (R,G,B,A bytes; A=255).
  * dst_rgba8_dev: device pointer receiving the band, row `row0` at offset 0, `pitch_bytes`
@@ -177,6 +210,8 @@ RM_API int rm_group_size(rm_group *g);
 RM_API rm_ctx *rm_group_ctx(rm_group *g, int i);
 RM_API int rm_group_set_mode(rm_group *g, int mode);
 RM_API int rm_group_set_limits(rm_group *g, const void *limits12);
+/* rm_specialize on every member (one compile: the cache is process-wide). */
+RM_API int rm_group_specialize(rm_group *g);
 /* rm_prepare on every member. */
 RM_API int rm_group_prepare(rm_group *g, const void *uniforms144, uint32_t cmd_count, const uint32_t *words,
                             uint32_t n_words);

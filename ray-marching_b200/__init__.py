@@ -33,7 +33,8 @@ ABI_SYMBOLS = [
     "rm_flush_l2", "rm_fp32_peak", "rm_launch_count", "rm_host_alloc", "rm_host_free", "rm_last_error",
     "rm_strerror", "rm_version",
     "rm_group_create", "rm_group_destroy", "rm_group_size", "rm_group_ctx", "rm_group_set_mode", "rm_group_set_limits",
-    "rm_group_prepare", "rm_group_paint_bands", "rm_group_frame", "rm_group_paint_poses", "rm_group_last_error",
+    "rm_specialize", "rm_set_specialize", "rm_spec_info", "rm_spec_status", "rm_spec_source", "rm_spec_compile_check",
+    "rm_group_specialize", "rm_group_prepare", "rm_group_paint_bands", "rm_group_frame", "rm_group_paint_poses", "rm_group_last_error",
 ]
 
 
@@ -104,6 +105,14 @@ def lib() -> C.CDLL:
             "rm_last_error": (C.c_char_p, [vp]),
             "rm_strerror": (C.c_char_p, [i]),
             "rm_version": (C.c_char_p, []),
+            "rm_specialize": (i, [vp]),
+            "rm_set_specialize": (i, [vp, i]),
+            "rm_spec_info": (i, [vp, C.POINTER(i), C.POINTER(i), C.POINTER(i), C.POINTER(C.c_double), C.POINTER(u64),
+                                 C.POINTER(u64), C.POINTER(u64)]),
+            "rm_spec_status": (C.c_char_p, [vp]),
+            "rm_spec_source": (i, [u32, vp, u32, i, i, C.c_char_p, sz, C.POINTER(sz)]),
+            "rm_spec_compile_check": (i, [u32, vp, u32, i, i, C.POINTER(u64), C.POINTER(C.c_double), C.c_char_p, sz]),
+            "rm_group_specialize": (i, [vp]),
             "rm_group_create": (i, [C.POINTER(i), i, C.POINTER(vp)]),
             "rm_group_destroy": (None, [vp]),
             "rm_group_size": (i, [vp]),
@@ -131,6 +140,27 @@ def validate_program(cmd_count: int, words, max_words: int = 255) -> int:
     """Static validation only — no device needed.  Returns an RM_* code."""
     w = _words_arr(words)
     return lib().rm_validate_program(cmd_count, w.ctypes.data if w.size else None, w.size, max_words)
+
+
+def spec_source(cmd_count: int, words, mode: int = MODE_FAST, rays_per_thread: int = 0) -> str:
+    """CUDA source of the specialised kernel for a command stream (no device needed).  Raises RmError."""
+    w = _words_arr(words)
+    need = C.c_size_t()
+    rc = lib().rm_spec_source(cmd_count, w.ctypes.data if w.size else None, w.size, mode, rays_per_thread, None, 0, C.byref(need))
+    if rc != RM_OK:
+        raise RmError(rc, lib().rm_strerror(rc).decode())
+    buf = C.create_string_buffer(need.value)
+    lib().rm_spec_source(cmd_count, w.ctypes.data if w.size else None, w.size, mode, rays_per_thread, buf, need.value, None)
+    return buf.value.decode()
+
+
+def spec_compile_check(cmd_count: int, words, mode: int = MODE_FAST, rays_per_thread: int = 0) -> dict:
+    """Trial NVRTC compile for sm_100a (no device needed) -> {rc, cubin_bytes, compile_ms, log}."""
+    w = _words_arr(words)
+    cb, ms, log = C.c_uint64(), C.c_double(), C.create_string_buffer(16384)
+    rc = lib().rm_spec_compile_check(cmd_count, w.ctypes.data if w.size else None, w.size, mode, rays_per_thread,
+                                     C.byref(cb), C.byref(ms), log, 16384)
+    return {"rc": rc, "cubin_bytes": int(cb.value), "compile_ms": ms.value, "log": log.value.decode(errors="replace")}
 
 
 class PinnedBuffer:
@@ -197,6 +227,22 @@ class Context:
     # ---- prepare (renderer.rs:196-242)
     def set_early_out(self, on: bool):
         self._chk(self._L.rm_set_early_out(self._h, int(bool(on))))
+
+    # ---- program specialisation (run-time compiled straight-line map_scene)
+    def specialize(self):
+        """Compile the prepared program for the current mode now; raises RmError(-9) if that is not possible."""
+        self._chk(self._L.rm_specialize(self._h))
+
+    def set_specialize(self, on: bool):
+        self._chk(self._L.rm_set_specialize(self._h, int(bool(on))))
+
+    def spec_info(self) -> dict:
+        a, r, mb, ms = C.c_int(), C.c_int(), C.c_int(), C.c_double()
+        cb, nc, nl = C.c_uint64(), C.c_uint64(), C.c_uint64()
+        self._chk(self._L.rm_spec_info(self._h, C.byref(a), C.byref(r), C.byref(mb), C.byref(ms), C.byref(cb), C.byref(nc), C.byref(nl)))
+        return {"active": bool(a.value), "rays_per_thread": r.value, "min_blocks": mb.value, "compile_ms": ms.value,
+                "cubin_bytes": int(cb.value), "compiles": int(nc.value), "launches": int(nl.value),
+                "status": self._L.rm_spec_status(self._h).decode(errors="replace")}
 
     def prepare(self, uniforms: bytes, cmd_count: int, words):
         assert len(uniforms) == UNIFORMS_BYTES
@@ -397,6 +443,9 @@ class Group:
         assert len(uniforms) == UNIFORMS_BYTES
         w = _words_arr(words)
         self._chk(self._L.rm_group_prepare(self._h, uniforms, cmd_count, w.ctypes.data if w.size else None, w.size))
+
+    def specialize(self):
+        self._chk(self._L.rm_group_specialize(self._h))
 
     def paint_bands(self, W: int, H: int, strip_rows: int = 16, out=None):
         """ONE frame across the members; `out` (PinnedBuffer or C-contiguous array of W*H*4 bytes) receives it."""

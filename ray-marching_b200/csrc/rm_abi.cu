@@ -3,12 +3,14 @@
 // all wgpu plumbing — limits, command buffer (decoded), uniforms — plus a framebuffer.
 #include <cuda_runtime.h>
 
+#include <chrono>
 #include <cstdio>
 #include <cstring>
 #include <new>
 #include <string>
 
 #include "../../include/rm_b200.h"
+#include "rm_jit.h"
 #include "rm_kernels.h"
 #include "rm_program.h"
 #include "rm_wavefront.h"
@@ -33,6 +35,13 @@ struct rm_ctx {
     bool prepared = false;
     bool counters_on = false;
     bool early_out = false;  // rm_set_early_out: opt-in, never on by default
+    // program specialisation (rm_jit.cu): paint the DIRECT kernel through run-time compiled straight-line code
+    int spec_policy = 0;          // rm_set_specialize: 1 = every program, compiled on first use
+    bool spec_requested = false;  // rm_specialize: the current program only
+    const SpecKernel *spec_cur[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};  // [exact][counters] for the current words
+    bool spec_failed[2][2] = {{false, false}, {false, false}};
+    std::string spec_status;      // why the last specialisation failed
+    uint64_t spec_compiles = 0, spec_launches = 0;
     float limits_f[2] = {0.01f, 100.0f};  // renderer.rs:133-137
     uint32_t max_iter = 100;
     float uniforms[36] = {};
@@ -150,6 +159,7 @@ const char *rm_strerror(int code) {
         case RM_E_CUDA: return "CUDA error";
         case RM_E_NOT_PREPARED: return "no program/uniforms prepared";
         case RM_E_BAD_PARAM: return "bad command parameter";
+        case RM_E_JIT: return "program specialisation failed (NVRTC unavailable, compile error or program too long)";
         default: return "unknown error";
     }
 }
@@ -268,6 +278,10 @@ int rm_prepare(rm_ctx *c, const void *uniforms144, uint32_t cmd_count, const uin
     std::memcpy(c->uniforms, uniforms144, RM_UNIFORMS_BYTES);
     c->last_words.assign(words, words + n_words);
     c->last_cmd_count = cmd_count;
+    // a specialised kernel belongs to one command stream: back to the interpreter (or, with the policy on, the new
+    // program is compiled at its first paint)
+    c->spec_requested = false;
+    for (int a = 0; a < 2; ++a) for (int b = 0; b < 2; ++b) { c->spec_cur[a][b] = nullptr; c->spec_failed[a][b] = false; }
     ++c->prog_uploads;
     c->prepared = true;
     return RM_OK;

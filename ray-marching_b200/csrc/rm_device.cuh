@@ -5,10 +5,14 @@
 //                sqrt.rn/div.rn) in the shader's evaluation order -> bit-identical to the oracle.
 //   Arith<false> (RM_MODE_FAST):  FMA contraction, MUFU sqrt/rsqrt/rcp.
 #pragma once
+#ifndef __CUDACC_RTC__
 #include <cuda_runtime.h>
 #include <stdint.h>
+#endif
 
 #include "rm_program.h"
+
+#define RM_FOR_R _Pragma("unroll") for (int r = 0; r < R; ++r)
 
 namespace rm {
 
@@ -248,6 +252,17 @@ __device__ __forceinline__ float shade_diffuse(float nx, float ny, float nz, flo
     A::normalize3(lx, ly, lz);
     float d = A::add(A::add(A::mul(nx, lx), A::mul(ny, ly)), A::mul(nz, lz));
     return fmaxf(RM_AMBIENT, d);
+}
+
+// normal from the four tetrahedron taps + diffuse term (wgsl:98-105, 138-143) -> sample code.  A rare per-ray event,
+// kept OUT OF LINE (one copy) so that the marching loops keep a small instruction footprint.
+template <bool EX>
+__device__ __noinline__ float wf_shade(float a0, float a1, float a2, float a3, float hx, float hy, float hz) {
+    using A = Arith<EX>;
+    const float nx = A::add(A::add(A::add(a0, -a1), -a2), a3);
+    const float ny = A::add(A::add(A::add(-a0, -a1), a2), a3);
+    const float nz = A::add(A::add(A::add(-a0, a1), -a2), a3);
+    return shade_diffuse<EX>(nx, ny, nz, hx, hy, hz);
 }
 
 // ---- floor / sky wgsl:117-130.  Returns class; colour via c[3]; t = floor_dist. ---------------

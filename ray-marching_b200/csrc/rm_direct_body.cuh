@@ -1,0 +1,184 @@
+// rm_direct_body.cuh — the body of the production kernel, shared by
+//   * rm_direct.cu: compiled ahead of time around the decoded-program INTERPRETER (any program, no set-up cost), and
+//   * rm_jit.cu:    compiled at run time (NVRTC) around map_scene emitted as STRAIGHT-LINE code for one program.
+// It is everything of fs_main / ray_march (wgsl:33-115) except map_scene itself, which is the MAP argument: a functor
+// `void operator()(const float (&px)[R], const float (&py)[R], const float (&pz)[R], float (&s)[R])` evaluating the scene
+// at R points.  Must stay free of host headers (NVRTC has none).
+//
+// A thread owns R sample rays of one pixel (R = 2, 4 or 8) and marches them in lock-step (wgsl:87-115): the rays are a
+// fraction of a pixel apart, so they leave the loop within a step or two of each other, and the warp's neighbouring
+// pixels are coherent.  Rays that hit get their normal from the 4 tetrahedron taps (wgsl:138-142), which fill the same
+// R slots of MAP, and the 16 samples of a pixel are summed in the shader's order by a shuffle chain over the pixel's
+// 16/R threads (wgsl:68-75).  Per-ray arithmetic is operation for operation that of the other kernels.
+#pragma once
+#include "rm_device.cuh"
+
+namespace rm {
+
+#define RM_DIRECT_THREADS 128
+#define RM_DIRECT_TILE_W 8
+#define RM_FULL_MASK 0xffffffffu
+
+// rows of the 8-wide pixel tile one 128-thread block covers
+__host__ __device__ constexpr uint32_t direct_tile_rows(int R) { return 4u * (32u / (16u / (uint32_t)R)) / 8u; }
+
+template <bool EX, int R, bool COUNT, class MAP>
+__device__ __forceinline__ void direct_body(const FrameParams &fp, uint8_t *__restrict__ dst, size_t pitch,
+                                            unsigned long long *__restrict__ counters, MAP &map) {
+    static_assert(R == 2 || R == 4 || R == 8, "2, 4 or 8 rays per thread");
+    constexpr int TPP = 16 / R;           // threads per pixel
+    constexpr int PPW = 32 / TPP;         // pixels per warp: 4, 8 or 16 consecutive pixels of the block's 8-wide tile
+    constexpr uint32_t TILE_ROWS = direct_tile_rows(R);  // 2, 4 or 8
+    using A = Arith<EX>;
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t tiles_x = (fp.W + RM_DIRECT_TILE_W - 1) / RM_DIRECT_TILE_W;
+    const uint32_t tx = blockIdx.x % tiles_x, ty = blockIdx.x / tiles_x;
+    const uint32_t pb = (uint32_t)warp * PPW + (uint32_t)lane / TPP;  // pixel of the block, row-major over its 8-wide tile
+    const uint32_t px = tx * RM_DIRECT_TILE_W + (pb & 7u), ry = ty * TILE_ROWS + (pb >> 3);
+    const uint32_t grp = (uint32_t)lane % TPP;  // this thread holds samples grp*R .. grp*R+R-1 (sample = 4*i + j)
+    const bool inside = px < fp.W && ry < fp.nrows;
+
+    float ro[3] = {0.f, 0.f, 0.f};
+    float rdx[R], rdy[R], rdz[R], dist[R], code[R];
+    uint32_t live = 0, hit = 0;  // bit r: ray r still marching / ray r hit the scene
+    uint32_t c_step = 0, c_hit = 0, c_floor = 0, c_sample = 0;
+    RM_FOR_R { rdx[r] = rdy[r] = rdz[r] = 0.f; dist[r] = 0.f; code[r] = RM_CODE_SKY; }
+    if (inside) {
+        const uint32_t fy = frame_row(fp, ry);
+        RM_FOR_R {
+            float o[3], d[3], c[3], t;
+            gen_ray<EX>(fp, px, fy, grp * R + (uint32_t)r, o, d);  // wgsl:39-62
+            ro[0] = o[0]; ro[1] = o[1]; ro[2] = o[2];
+            rdx[r] = d[0]; rdy[r] = d[1]; rdz[r] = d[2];
+            const int cls = shade_miss(o, d, c, t);  // wgsl:117-130: what the ray gets if it never hits
+            code[r] = cls == 0 ? RM_CODE_SKY : (c[0] > 0.2f ? RM_CODE_FLOOR_LIGHT : RM_CODE_FLOOR_DARK);
+        }
+        if (COUNT) c_sample = R;
+        if (fp.max_iter > 0) live = (1u << R) - 1u;
+    }
+
+    float px_[R], py_[R], pz_[R], s[R];
+    // ---------------- march: all live rays of the thread take one step per trip (wgsl:88-115) ----------------
+    for (uint32_t it = 0; live != 0; ++it) {
+        RM_FOR_R {  // pos = origin + direction * dist   wgsl:91
+            px_[r] = A::mad(rdx[r], dist[r], ro[0]);
+            py_[r] = A::mad(rdy[r], dist[r], ro[1]);
+            pz_[r] = A::mad(rdz[r], dist[r], ro[2]);
+        }
+        RM_FOR_R asm volatile("" : "+f"(px_[r]), "+f"(py_[r]), "+f"(pz_[r]));
+        map(px_, py_, pz_, s);
+        const bool last = it + 1 >= fp.max_iter;  // loop bound wgsl:90
+        RM_FOR_R {
+            const uint32_t bit = 1u << r;
+            if (live & bit) {
+                if (COUNT) ++c_step;
+                if (s[r] < fp.min_dist) {  // wgsl:97: hit, dist stays at the hit distance
+                    hit |= bit;
+                    live &= ~bit;
+                } else if (s[r] > fp.max_dist) {  // wgsl:109-111
+                    live &= ~bit;
+                } else {
+                    dist[r] = A::add(dist[r], s[r]);  // wgsl:114
+                    if (last) live &= ~bit;
+                }
+            }
+        }
+    }
+    // ---------------- normals + diffuse term of the rays that hit (wgsl:98-105,138-143) ----------------
+    const uint32_t hit0 = hit;
+    const float ep = RM_NORMAL_EPS, en = -RM_NORMAL_EPS;
+    if constexpr (R == 2) {  // a hit ray's 4 taps take two passes of the 2-wide map: taps 0,1 then taps 2,3
+        while (hit != 0) {
+            const int rr = __ffs((int)hit) - 1;
+            hit &= hit - 1u;
+            const float dx = rr ? rdx[1] : rdx[0], dy = rr ? rdy[1] : rdy[0], dz = rr ? rdz[1] : rdz[0];
+            const float dd = rr ? dist[1] : dist[0];
+            const float hx = A::mad(dx, dd, ro[0]), hy = A::mad(dy, dd, ro[1]), hz = A::mad(dz, dd, ro[2]);
+            float a[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll 1
+            for (int pass = 0; pass < 2; ++pass) {  // taps wgsl:138-142: (+,-,-) (-,-,+) | (-,+,-) (+,+,+)
+                px_[0] = __fadd_rn(hx, pass ? en : ep); py_[0] = __fadd_rn(hy, pass ? ep : en); pz_[0] = __fadd_rn(hz, en);
+                px_[1] = __fadd_rn(hx, pass ? ep : en); py_[1] = __fadd_rn(hy, pass ? ep : en); pz_[1] = __fadd_rn(hz, ep);
+                map(px_, py_, pz_, s);
+                if (pass == 0) { a[0] = s[0]; a[1] = s[1]; } else { a[2] = s[0]; a[3] = s[1]; }
+            }
+            const float c = wf_shade<EX>(a[0], a[1], a[2], a[3], hx, hy, hz);
+            if (rr) code[1] = c; else code[0] = c;
+            if (COUNT) ++c_hit;
+        }
+    } else {
+        while (hit != 0) {
+            int rr[(R + 3) / 4];
+            float hx[(R + 3) / 4], hy[(R + 3) / 4], hz[(R + 3) / 4];
+#pragma unroll
+            for (int j = 0; j < R / 4; ++j) {  // R/4 hit rays per trip: ray j's 4 taps fill slots 4j..4j+3
+                rr[j] = hit ? __ffs((int)hit) - 1 : -1;
+                hit &= hit - 1u;  // 0 stays 0
+                float dx = 0.f, dy = 0.f, dz = 0.f, dd = 0.f;
+                RM_FOR_R if (r == rr[j]) { dx = rdx[r]; dy = rdy[r]; dz = rdz[r]; dd = dist[r]; }
+                hx[j] = A::mad(dx, dd, ro[0]); hy[j] = A::mad(dy, dd, ro[1]); hz[j] = A::mad(dz, dd, ro[2]);
+                // tetrahedron taps wgsl:138-142: (+,-,-) (-,-,+) (-,+,-) (+,+,+), eps = 1e-4
+                px_[4 * j + 0] = __fadd_rn(hx[j], ep); py_[4 * j + 0] = __fadd_rn(hy[j], en); pz_[4 * j + 0] = __fadd_rn(hz[j], en);
+                px_[4 * j + 1] = __fadd_rn(hx[j], en); py_[4 * j + 1] = __fadd_rn(hy[j], en); pz_[4 * j + 1] = __fadd_rn(hz[j], ep);
+                px_[4 * j + 2] = __fadd_rn(hx[j], en); py_[4 * j + 2] = __fadd_rn(hy[j], ep); pz_[4 * j + 2] = __fadd_rn(hz[j], en);
+                px_[4 * j + 3] = __fadd_rn(hx[j], ep); py_[4 * j + 3] = __fadd_rn(hy[j], ep); pz_[4 * j + 3] = __fadd_rn(hz[j], ep);
+            }
+            RM_FOR_R asm volatile("" : "+f"(px_[r]), "+f"(py_[r]), "+f"(pz_[r]));
+            map(px_, py_, pz_, s);
+#pragma unroll
+            for (int j = 0; j < R / 4; ++j) {
+                if (rr[j] >= 0) {
+                    const float c = wf_shade<EX>(s[4 * j], s[4 * j + 1], s[4 * j + 2], s[4 * j + 3], hx[j], hy[j], hz[j]);
+                    RM_FOR_R if (r == rr[j]) code[r] = c;
+                    if (COUNT) ++c_hit;
+                }
+            }
+        }
+    }
+    if (COUNT && inside) RM_FOR_R if (!(hit0 & (1u << r)) && code[r] != RM_CODE_SKY) ++c_floor;
+
+    // ---------------- resolve: 16-sample mean in shader order (wgsl:44-45,68-75) ----------------
+    // a pixel's threads hold consecutive sample ranges, so the running sum visits them in lane order
+    float gm[R][3];
+    RM_FOR_R code_to_gamma(code[r], gm[r]);
+    float sr = 0.0f, sg = 0.0f, sb = 0.0f;
+#pragma unroll
+    for (int g = 0; g < TPP; ++g) {
+        if ((int)grp == g) RM_FOR_R { sr = __fadd_rn(sr, gm[r][0]); sg = __fadd_rn(sg, gm[r][1]); sb = __fadd_rn(sb, gm[r][2]); }
+        const int src = (lane / TPP) * TPP + g;
+        sr = __shfl_sync(RM_FULL_MASK, sr, src); sg = __shfl_sync(RM_FULL_MASK, sg, src); sb = __shfl_sync(RM_FULL_MASK, sb, src);
+    }
+    const uint32_t pix = unorm8(__fdiv_rn(sr, 16.0f)) | (unorm8(__fdiv_rn(sg, 16.0f)) << 8) |
+                         (unorm8(__fdiv_rn(sb, 16.0f)) << 16) | 0xff000000u;
+    // ---------------- store: every 4 consecutive pixels of a row go out as one 128-bit store ----------------
+    const uint32_t x0 = tx * RM_DIRECT_TILE_W;
+    constexpr int QUADS = PPW / 4;               // 4-pixel groups per warp
+    const int q4 = (lane & (QUADS - 1)) * 4;     // first of the 4 pixels this lane gathers (used by lanes < QUADS)
+    uint4 v;
+    v.x = __shfl_sync(RM_FULL_MASK, pix, (q4 + 0) * TPP);
+    v.y = __shfl_sync(RM_FULL_MASK, pix, (q4 + 1) * TPP);
+    v.z = __shfl_sync(RM_FULL_MASK, pix, (q4 + 2) * TPP);
+    v.w = __shfl_sync(RM_FULL_MASK, pix, (q4 + 3) * TPP);
+    const uint32_t pb_q = (uint32_t)warp * PPW + (uint32_t)q4;
+    const uint32_t row_q = ty * TILE_ROWS + (pb_q >> 3);
+    if (x0 + RM_DIRECT_TILE_W <= fp.W && (pitch & 15) == 0) {  // warp-uniform
+        if (lane < QUADS && row_q < fp.nrows)
+            *reinterpret_cast<uint4 *>(dst + (size_t)dst_row(fp, row_q) * pitch + (size_t)(x0 + (pb_q & 7u)) * 4) = v;
+    } else if (inside && grp == 0) {
+        *reinterpret_cast<uint32_t *>(dst + (size_t)dst_row(fp, ry) * pitch + (size_t)px * 4) = pix;
+    }
+
+    if (COUNT) {
+        const uint32_t a = __reduce_add_sync(RM_FULL_MASK, c_step), b = __reduce_add_sync(RM_FULL_MASK, c_hit),
+                       c = __reduce_add_sync(RM_FULL_MASK, c_floor), d = __reduce_add_sync(RM_FULL_MASK, c_sample);
+        if (lane == 0) {
+            atomicAdd(&counters[0], (unsigned long long)a);
+            atomicAdd(&counters[1], (unsigned long long)b);
+            atomicAdd(&counters[2], (unsigned long long)c);
+            atomicAdd(&counters[3], (unsigned long long)d);
+        }
+    }
+}
+
+}  // namespace rm

@@ -96,6 +96,12 @@ int rm_group_set_limits(rm_group *g, const void *limits12) {
     return RM_OK;
 }
 
+int rm_group_specialize(rm_group *g) {
+    if (!g) return RM_E_INVALID_ARG;
+    for (size_t i = 0; i < g->ctx.size(); ++i) { const int rc = rm_specialize(g->ctx[i]); if (rc != RM_OK) return member_fail(g, (int)i, rc); }
+    return RM_OK;
+}
+
 // The <= 1.2 KB of inputs are replicated to every member; unchanged words are not re-uploaded.
 int rm_group_prepare(rm_group *g, const void *uniforms144, uint32_t cmd_count, const uint32_t *words, uint32_t n_words) {
     if (!g) return RM_E_INVALID_ARG;

@@ -1,0 +1,49 @@
+// rm_jit.h — program specialisation: map_scene of ONE command stream emitted as straight-line CUDA, compiled at run
+// time (NVRTC, sm_100a) around the production kernel body (rm_direct_body.cuh), cached process-wide.
+//
+// Why (measured on B200, profiles/r1_s14_NOTES.md): the decoded-program interpreter issues 168 warp instructions per
+// fused instruction for 8 rays, 23 of them fetch/dispatch/copies, and holds the instruction's constants in registers.
+// Straight-line code has none of that — constants are immediates, there is no dispatch — and needs fewer registers, so
+// more warps are resident.  What bounds it instead is the instruction cache: a 63-command scene is 9 KB of code per ray,
+// so the rays per thread drop from 8 to 2 to keep the march loop inside the 32-KB L1.5 instruction cache
+// (8 rays: 80 KB loop, 61 ms; 4 rays: 40 KB, 42.4 ms; 2 rays: 18 KB, 34.5 ms; interpreter 44.0 ms).
+// Arithmetic per ray is operation for operation the interpreter's: exact mode stays bit-identical to the oracle.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+
+#include "rm_device.cuh"
+
+namespace rm {
+
+struct SpecKernel {
+    cudaKernel_t fn = nullptr;
+    cudaLibrary_t lib = nullptr;
+    int rays_per_thread = 0;   // 2, 4 or 8
+    int min_blocks = 0;        // __launch_bounds__ second argument
+    bool exact = false, count = false;
+    double compile_ms = 0.0;   // NVRTC compile + module load
+    size_t cubin_bytes = 0;
+    uint32_t est_insn_per_ray = 0;
+};
+
+// CUDA source of the specialised kernel for this (already validated) command stream.  rays_per_thread 0 = choose from
+// the code-size estimate.  Returns RM_OK, or RM_E_JIT when the program is too long to specialise usefully.
+int spec_generate_source(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, bool exact, bool count,
+                         int rays_per_thread, std::string *src, int *r_out, int *minb_out, uint32_t *est_out, std::string *err);
+
+// NVRTC-compiles `src` for sm_100a to a cubin (no GPU needed).  RM_E_JIT + message when libnvrtc cannot be loaded or
+// the compile fails.
+int spec_compile(const std::string &src, std::string *cubin, std::string *err);
+
+// Cached: generate + compile + load for (program, mode, counters).  The returned pointer stays valid for the life of
+// the process.  `cached` reports whether this call had to compile.
+int spec_get(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, bool exact, bool count, const SpecKernel **out,
+             bool *compiled_now, std::string *err);
+
+cudaError_t launch_spec(const SpecKernel &k, const FrameParams &fp, uint8_t *dst, size_t pitch, unsigned long long *counters,
+                        cudaStream_t st);
+
+}  // namespace rm

@@ -31,15 +31,20 @@ inline uint32_t combine_of(uint32_t t) {
 }
 inline void set_k(RmInsn &in, float k) {
     in.k = k;
-    in.inv_k = 1.0f / k;
-    in.c4k = 0.25f / k;  // fast mode folds h*h*k*0.25 = e*e/(4k) into one constant
-    int e = 0;
-    float m = std::frexp(k, &e);
-    // 1/k and x*(1/k) == x/k bit for bit when k is a normal power of two with a normal reciprocal
-    if (m == 0.5f && std::fpclassify(k) == FP_NORMAL && std::fpclassify(in.inv_k) == FP_NORMAL)
-        in.flags |= FLAG_K_POW2;
+    bool pow2 = false;
+    smooth_constants(k, &in.inv_k, &in.c4k, &pow2);
+    if (pow2) in.flags |= FLAG_K_POW2;
 }
 }  // namespace
+
+void smooth_constants(float k, float *inv_k, float *c4k, bool *k_pow2) {
+    *inv_k = 1.0f / k;
+    *c4k = 0.25f / k;  // fast mode folds h*h*k*0.25 = e*e/(4k) into one constant
+    int e = 0;
+    const float m = std::frexp(k, &e);
+    // 1/k and x*(1/k) == x/k bit for bit when k is a normal power of two with a normal reciprocal
+    *k_pow2 = m == 0.5f && std::fpclassify(k) == FP_NORMAL && std::fpclassify(*inv_k) == FP_NORMAL;
+}
 
 int decode_program(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, uint32_t max_words,
                    Program *out) {

@@ -12,9 +12,15 @@
 //   * per-instruction constants that are exact (k*0.25, 1/k when k is a power of two) are
 //     precomputed.  Nothing here changes evaluation order or rounding.
 #pragma once
+#ifdef __CUDACC_RTC__  // runtime compilation of specialised kernels (rm_jit.cu): no host headers there
+typedef unsigned char uint8_t;
+typedef unsigned int uint32_t;
+typedef unsigned long long uint64_t;
+#else
 #include <stdint.h>
 
 #include <vector>
+#endif
 
 #ifndef RM_STACK_MAX
 #define RM_STACK_MAX 32u  // value_stack_max_size, ray_marching.wgsl:173 (same value as rm_b200.h)
@@ -76,6 +82,7 @@ struct alignas(16) RmInsn {
 };
 static_assert(sizeof(RmInsn) == 48, "RmInsn must be 48 bytes");
 
+#ifndef __CUDACC_RTC__
 struct Program {
     std::vector<RmInsn> insns;
     uint32_t cmd_count = 0;
@@ -88,8 +95,13 @@ struct Program {
     }
 };
 
+// Per-instruction constants of the smooth union (X2) — one definition for the interpreter's decoder and the
+// specialised-kernel generator (rm_jit.cu), so that both evaluate the blend with the same numbers.
+void smooth_constants(float k, float *inv_k, float *c4k, bool *k_pow2);
+
 // Returns an RM_* code (rm_b200.h).  `out` may be null for validation only.
 int decode_program(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, uint32_t max_words,
                    Program *out);
+#endif  // !__CUDACC_RTC__
 
 }  // namespace rm

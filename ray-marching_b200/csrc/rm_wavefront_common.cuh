@@ -31,7 +31,6 @@ __device__ __forceinline__ float prim_eval(float x, float y, float z, const floa
 }
 
 #define RM_OPC(SRC, CB) opcode(SRC, CB)
-#define RM_FOR_R _Pragma("unroll") for (int r = 0; r < R; ++r)
 #define RM_PRIM_CASES(SRC)                                                                                  \
     case RM_OPC(SRC, CB_FIRST):                                                                             \
         RM_FOR_R acc[r] = prim_eval<EX, SRC>(px[r], py[r], pz[r], q0, q1);                                  \
@@ -148,15 +147,7 @@ __device__ __forceinline__ void map_evalR(const float4 *__restrict__ prog, uint3
 // ---- rare per-ray events, kept OUT OF LINE (one copy each) so that the per-iteration instruction
 // footprint of the persistent loop stays inside the instruction cache (profiles/r1_v1_*: the fully
 // inlined R=4 kernel stalled 4.7 cycles per issue on no_instruction) ------------------------------
-// normal from the four tetrahedron taps + diffuse term (wgsl:98-105, 138-143) -> sample code
-template <bool EX>
-__device__ __noinline__ float wf_shade(float a0, float a1, float a2, float a3, float hx, float hy, float hz) {
-    using A = Arith<EX>;
-    const float nx = A::add(A::add(A::add(a0, -a1), -a2), a3);
-    const float ny = A::add(A::add(A::add(-a0, -a1), a2), a3);
-    const float nz = A::add(A::add(A::add(-a0, a1), -a2), a3);
-    return shade_diffuse<EX>(nx, ny, nz, hx, hy, hz);
-}
+// (wf_shade, the normal + diffuse term of a hit, lives in rm_device.cuh: the direct kernel shares it)
 
 // in-order 16-sample resolve of one pixel of a finished tile (codes[sample*32 + pixel])
 __device__ __noinline__ uint32_t wf_resolve(const float *codes, int lane) {

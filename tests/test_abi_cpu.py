@@ -33,7 +33,7 @@ def test_library_exports_every_declared_symbol(rm):
 
 def test_strerror_covers_codes(rm):
     L = rm.lib()
-    for code in range(0, -9, -1):
+    for code in range(0, -10, -1):
         assert L.rm_strerror(code) != b"unknown error"
 
 

@@ -1,0 +1,226 @@
+"""Program specialisation on the GPU (rm_specialize / rm_set_specialize): map_scene of the prepared command stream is
+compiled at run time into straight-line code around the production kernel body.
+Bars: exact mode bit-identical to the CPU oracle (image and work counters) — the arithmetic per ray is the
+interpreter's, operation for operation; fast mode inside the north-star gates against the oracle and within 1 LSB of the
+interpreter; every band / strip / pose-batch path unchanged; falls back to the interpreter when the words change, when
+NVRTC is missing, and for programs too long for the instruction cache."""
+import os
+import subprocess
+import sys
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+import helpers as h
+import rm_import
+from test_gpu_parity import GATE_HITMASK, GATE_RGBA_FRAC, GATE_RGBA_LSB, cases, gates, random_program
+
+pytestmark = pytest.mark.gpu
+ROOT = Path(__file__).resolve().parent.parent
+
+
+@pytest.fixture(scope="module")
+def rm():
+    return rm_import.load()
+
+
+@pytest.fixture()
+def ctx(rm):
+    c = rm.Context(0)
+    yield c
+    c.close()
+
+
+@pytest.mark.parametrize("name,W,H,yaw,pitch", cases())
+def test_specialised_exact_mode_is_bit_identical_to_the_oracle(rm, ctx, name, W, H, yaw, pitch):
+    cmd, words = h.SCENES[name]()
+    u = h.orbit_uniforms(W, H, yaw=yaw, pitch=pitch)
+    ref = h.oracle_render(u, cmd, words, W, H, aov=True)
+    ctx.set_mode(rm.MODE_EXACT)
+    ctx.set_counters(True)
+    ctx.prepare(u, cmd, words)
+    ctx.specialize()
+    info = ctx.spec_info()
+    assert info["active"] and info["rays_per_thread"] == (2 if name == "S2" else 4) and info["compile_ms"] > 0
+    n0 = info["launches"]
+    img = ctx.render(u, cmd, words, W, H)
+    cnt = ctx.get_counters()
+    assert ctx.spec_info()["launches"] == n0 + 1  # the specialised kernel is what ran
+    assert np.array_equal(img, ref["rgba"]), gates(img, ref["rgba"])
+    assert np.array_equal(cnt, ref["counters"]), (cnt, ref["counters"])
+
+
+@pytest.mark.parametrize("name,W,H,yaw,pitch", cases())
+def test_specialised_fast_mode_meets_the_gates_and_tracks_the_interpreter(rm, ctx, name, W, H, yaw, pitch):
+    cmd, words = h.SCENES[name]()
+    u = h.orbit_uniforms(W, H, yaw=yaw, pitch=pitch)
+    ref = h.oracle_render(u, cmd, words, W, H)
+    ctx.set_mode(rm.MODE_FAST)
+    interp = ctx.render(u, cmd, words, W, H)
+    ctx.specialize()
+    img = ctx.render(u, cmd, words, W, H)
+    assert ctx.spec_info()["active"] and ctx.spec_info()["launches"] == 1
+    g = gates(img, ref["rgba"])
+    assert g["rgba_frac"] <= GATE_RGBA_FRAC, g
+    d = np.abs(img.astype(int) - interp.astype(int)).max(-1)
+    assert d.max() <= 1 and (d > 0).mean() <= 1e-3, (int(d.max()), float((d > 0).mean()))
+    # hit mask: the class of every sample comes out of the same comparisons; count disagreeing PIXELS through the image
+    # (a sample that flips between hit and miss changes its pixel by far more than 2 LSB only at silhouettes)
+    assert (d > GATE_RGBA_LSB).mean() <= GATE_HITMASK
+
+
+@pytest.mark.parametrize("seed", range(4))
+def test_specialised_random_trees_exact(rm, ctx, seed):
+    """All opcodes, mixed tree shapes (operands that are subtrees, stack depth > 2), several k values."""
+    rng = np.random.default_rng(4321 + seed)
+    W, H = 96, 64
+    u = h.orbit_uniforms(W, H, yaw=0.3 + seed, pitch=0.35)
+    ctx.set_mode(rm.MODE_EXACT)
+    ctx.set_counters(True)
+    for n_leaves in (1, 2, 5, 12, 24):
+        words, cmd = random_program(rng, n_leaves, right_bias=0.5)
+        if len(words) > 255:
+            continue
+        ref = h.oracle_render(u, cmd, words, W, H)
+        ctx.prepare(u, cmd, words)
+        ctx.specialize()
+        assert ctx.spec_info()["active"]
+        ctx.paint(W, H)
+        img = np.empty((H, W, 4), np.uint8)
+        ctx.download(img)
+        assert np.array_equal(img, ref["rgba"]), (n_leaves, gates(img, ref["rgba"]))
+        assert np.array_equal(ctx.get_counters(), ref["counters"])
+
+
+def test_empty_program_specialises_to_max_dist(rm, ctx):
+    u = h.orbit_uniforms(64, 48, pitch=0.3)
+    ctx.set_mode(rm.MODE_EXACT)
+    ctx.prepare(u, 0, [])
+    ctx.specialize()
+    img = ctx.render(u, 0, [], 64, 48)
+    assert ctx.spec_info()["launches"] == 1
+    assert np.array_equal(img, h.oracle_render(u, 0, [], 64, 48)["rgba"])
+
+
+def test_bands_strips_and_pose_batches_run_specialised(rm, ctx):
+    W, H = 200, 77  # ragged: not a multiple of any tile
+    cmd, words = h.scene_s2()
+    u = h.orbit_uniforms(W, H, yaw=0.6, pitch=0.4)
+    ctx.set_mode(rm.MODE_FAST)
+    ctx.prepare(u, cmd, words)
+    ctx.specialize()
+    full = ctx.render(u, cmd, words, W, H)
+    assert ctx.spec_info()["rays_per_thread"] == 2
+    # row bands
+    for row0, n in ((0, 1), (5, 31), (70, 7), (0, 77)):
+        band = ctx.render(u, cmd, words, W, H, row0, n)
+        assert np.array_equal(band, full[row0:row0 + n])
+    # interleaved strips stored at their frame rows
+    import torch
+    frame = torch.zeros((H, W, 4), dtype=torch.uint8, device="cuda:0")
+    for first in range(3):
+        ctx.paint_strips_into(W, H, 4, first, 3, frame.data_ptr())
+    ctx.sync()
+    assert np.array_equal(frame.cpu().numpy(), full)
+    # pose batch returned to host
+    us = [h.orbit_uniforms(W, H, yaw=0.9 * k, pitch=0.4) for k in range(5)]
+    singles = [ctx.render(p, cmd, words, W, H) for p in us]
+    buf = rm.PinnedBuffer(5 * W * H * 4)
+    n0 = ctx.spec_info()["launches"]
+    ctx.paint_poses_host(b"".join(us), 5, W, H, buf.ptr)
+    assert ctx.spec_info()["launches"] == n0 + 5
+    for k in range(5):
+        assert np.array_equal(buf.array.reshape(5, H, W, 4)[k], singles[k])
+    buf.free()
+
+
+def test_new_words_go_back_to_the_interpreter_and_the_policy_recompiles(rm, ctx):
+    W, H = 96, 64
+    u = h.orbit_uniforms(W, H, yaw=0.3, pitch=0.2)
+    ctx.set_mode(rm.MODE_EXACT)
+    cmd, words = h.scene_s1()
+    ctx.prepare(u, cmd, words)
+    ctx.specialize()
+    ctx.render(u, cmd, words, W, H)
+    assert ctx.spec_info()["launches"] == 1
+    cmd2, words2 = h.scene_s0()
+    img = ctx.render(u, cmd2, words2, W, H)       # different words: interpreter, no compile
+    info = ctx.spec_info()
+    assert not info["active"] and info["launches"] == 1
+    assert np.array_equal(img, h.oracle_render(u, cmd2, words2, W, H)["rgba"])
+    ctx.set_specialize(True)                       # policy: every program, compiled at first paint
+    img = ctx.render(u, cmd2, words2, W, H)
+    info = ctx.spec_info()
+    assert info["active"] and info["launches"] == 2
+    assert np.array_equal(img, h.oracle_render(u, cmd2, words2, W, H)["rgba"])
+    compiles = info["compiles"]
+    ctx.render(u, cmd, words, W, H)                # S1 again: already in the process-wide cache
+    assert ctx.spec_info()["compiles"] == compiles and ctx.spec_info()["launches"] == 3
+    # a second context shares the cache
+    with rm.Context(0) as other:
+        other.set_mode(rm.MODE_EXACT)
+        other.prepare(u, cmd, words)
+        other.specialize()
+        assert other.spec_info()["compiles"] == 0 and other.spec_info()["active"]
+
+
+def test_too_long_a_program_stays_on_the_interpreter(rm):
+    n = 120
+    words = h.box((0, 0, 0), (1, 1, 1))
+    for i in range(n - 1):
+        words = words + h.box((0.02 * i, 0, 0), (0.5, 0.5, 0.5)) + [103, h.fbits(0.25)]
+    cmd = 2 * n - 1
+    W, H = 48, 32
+    u = h.orbit_uniforms(W, H, yaw=0.3, pitch=0.2)
+    with rm.Context(0, max_words=2048) as ctx:
+        ctx.set_mode(rm.MODE_EXACT)
+        ctx.prepare(u, cmd, words)
+        with pytest.raises(rm.RmError) as e:
+            ctx.specialize()
+        assert e.value.code == -9 and "too long" in str(e.value)
+        img = ctx.render(u, cmd, words, W, H)
+        assert ctx.spec_info()["launches"] == 0
+        ctx.set_specialize(True)  # the policy fails silently and says why
+        img2 = ctx.render(u, cmd, words, W, H)
+        assert np.array_equal(img, img2) and "too long" in ctx.spec_info()["status"]
+
+
+def test_without_nvrtc_specialize_reports_and_painting_continues():
+    """RM_NVRTC_PATH names an exact file; a missing one must give RM_E_JIT, not a crash and not a silent CPU path."""
+    code = (
+        "import sys; sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
+        "import numpy as np, helpers as h, rm_import\n"
+        "rm = rm_import.load()\n"
+        "ctx = rm.Context(0); ctx.set_mode(rm.MODE_EXACT)\n"
+        "cmd, words = h.scene_s1(); u = h.orbit_uniforms(64, 48)\n"
+        "ctx.prepare(u, cmd, words)\n"
+        "try:\n"
+        "    ctx.specialize(); print('NOERROR')\n"
+        "except rm.RmError as e:\n"
+        "    print('CODE', e.code, 'NVRTC is not available' in str(e))\n"
+        "img = ctx.render(u, cmd, words, 64, 48)\n"
+        "print('SAME', bool(np.array_equal(img, h.oracle_render(u, cmd, words, 64, 48)['rgba'])), ctx.spec_info()['launches'])\n"
+    ) % (str(ROOT), str(ROOT / "tests"))
+    env = dict(os.environ, RM_NVRTC_PATH="/nonexistent/libnvrtc.so")
+    r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=300)
+    assert "CODE -9 True" in r.stdout, r.stdout + r.stderr
+    assert "SAME True 0" in r.stdout, r.stdout + r.stderr
+
+
+def test_group_specialises_once_for_all_members(rm):
+    import torch
+    have = max(1, torch.cuda.device_count())
+    W, H = 256, 150
+    cmd, words = h.scene_s2()
+    u = h.orbit_uniforms(W, H, yaw=1.1, pitch=0.4)
+    with rm.Context(0) as ctx:
+        ctx.set_mode(rm.MODE_EXACT)
+        full = ctx.render(u, cmd, words, W, H)
+    with rm.Group([k % have for k in range(3)]) as g:
+        g.set_mode(rm.MODE_EXACT)
+        g.prepare(u, cmd, words)
+        g.specialize()
+        got = np.zeros((H, W, 4), np.uint8)
+        g.paint_bands(W, H, 16, got)
+    assert np.array_equal(got, full)

@@ -1,0 +1,96 @@
+"""Program specialisation, the parts that need no GPU: the source generator (straight-line map_scene from the postfix
+command stream) and a trial NVRTC compile for sm_100a (NVRTC cross-compiles without a device, like nvcc)."""
+import re
+
+import numpy as np
+import pytest
+
+import helpers as h
+import rm_import
+
+
+@pytest.fixture(scope="module")
+def rm():
+    m = rm_import.load()
+    if not m.LIB_PATH.exists():
+        m.build()
+    return m
+
+
+def _defs(src):
+    return re.findall(r"RM_FOR_R (v\d+)\[r\] = (\w+)", src)
+
+
+def test_source_is_one_ssa_value_per_command_in_stream_order(rm):
+    cmd, words = h.scene_s1()  # box, sphere, union, sphere, subtraction  (main.rs:112-126)
+    src = rm.spec_source(cmd, words, rm.MODE_FAST)
+    assert [f for _, f in _defs(src)] == ["sd_box", "sd_sphere", "fminf", "sd_sphere", "fmaxf"]
+    assert "v2[r] = fminf(v0[r], v1[r])" in src              # a = deeper entry, b = top (wgsl:243-244)
+    assert "v4[r] = fmaxf(v2[r], -v3[r])" in src             # A \ B = max(a, -b)     (wgsl:248-252)
+    assert "RM_FOR_R out[r] = v4[r];" in src
+    assert 'extern "C" __global__' in src and "rm::direct_body<false, 4, false>" in src
+    assert "direct_body<true, 4, false>" in rm.spec_source(cmd, words, rm.MODE_EXACT)
+
+
+def test_constants_are_emitted_by_their_bits(rm):
+    words = h.sphere((0.1, -2.5, 3.0e-7), 1.25)
+    src = rm.spec_source(1, words, rm.MODE_FAST)
+    for w in words[1:]:
+        assert "__uint_as_float(0x%08xu)" % w in src
+    k = 0.3
+    words = h.sphere((0, 0, 0), 1) + h.sphere((1, 0, 0), 1) + [103, h.fbits(k)]
+    src = rm.spec_source(3, words, rm.MODE_FAST)
+    inv = np.float32(1.0) / np.float32(k)
+    c4k = np.float32(0.25) / np.float32(k)
+    m = re.search(r"op_smooth<EX>\(v0\[r\], v1\[r\], (\S+), (\S+), (\S+), (true|false)\)", src)
+    assert m and m.group(1) == "__uint_as_float(0x%08xu)" % h.fbits(k)
+    assert m.group(2) == "__uint_as_float(0x%08xu)" % int(inv.view(np.uint32))
+    assert m.group(3) == "__uint_as_float(0x%08xu)" % int(c4k.view(np.uint32))
+    assert m.group(4) == "false"
+    words[-1] = h.fbits(0.25)  # power of two: the exact-mode divide becomes a multiply by the exact reciprocal
+    assert ", true)" in rm.spec_source(3, words, rm.MODE_FAST)
+
+
+def test_rays_per_thread_follow_the_code_size(rm):
+    cmd, words = h.scene_s0()
+    assert "direct_body<false, 4," in rm.spec_source(cmd, words)
+    cmd, words = h.scene_s2()  # 63 commands: ~9 KB of code per ray -> 2 rays keep the march loop in the instruction cache
+    src = rm.spec_source(cmd, words)
+    assert "direct_body<false, 2," in src and "__launch_bounds__(RM_DIRECT_THREADS, 12)" in src
+    assert "direct_body<false, 8," in rm.spec_source(cmd, words, rm.MODE_FAST, 8)  # explicit request is honoured
+    # a chain far beyond the instruction-cache budget is refused (the interpreter is the better kernel there)
+    n = 120
+    long_words = h.box((0, 0, 0), (1, 1, 1))
+    for _ in range(n - 1):
+        long_words += h.box((0.5, 0, 0), (1, 1, 1)) + [103, h.fbits(0.25)]
+    with pytest.raises(rm.RmError) as e:
+        rm.spec_source(2 * n - 1, long_words)
+    assert e.value.code == -9
+
+
+def test_deep_stacks_and_empty_program(rm):
+    # ((s0 u s1) n (s2 \ s3)): right operand is a subtree -> the interpreter needs a spill slot, SSA does not care
+    s = [h.sphere((i, 0, 0), 1) for i in range(4)]
+    words = s[0] + s[1] + [100] + s[2] + s[3] + [101] + [102]
+    src = rm.spec_source(7, words)
+    assert "v6[r] = fmaxf(v2[r], v5[r])" in src and "v5[r] = fmaxf(v3[r], -v4[r])" in src
+    src = rm.spec_source(0, [])
+    assert "out[r] = max_dist" in src
+
+
+@pytest.mark.parametrize("bad,code", [([5], -3), ([100], -5), (h.sphere((0, 0, 0), 1) * 2, -5)])
+def test_invalid_streams_are_rejected_with_the_validation_codes(rm, bad, code):
+    with pytest.raises(rm.RmError) as e:
+        rm.spec_source(len(bad) if bad[0] != 0 else 2, bad)
+    assert e.value.code == code
+
+
+@pytest.mark.parametrize("scene", ["s0", "s1", "s2"])
+@pytest.mark.parametrize("mode", [0, 1])
+def test_generated_source_compiles_for_sm_100a(rm, scene, mode):
+    cmd, words = getattr(h, "scene_" + scene)()
+    r = rm.spec_compile_check(cmd, words, mode)
+    if r["rc"] == -9 and "NVRTC is not available" in r["log"]:
+        pytest.skip("no libnvrtc in this environment: " + r["log"][:200])
+    assert r["rc"] == 0, r["log"]
+    assert r["cubin_bytes"] > 10000 and r["compile_ms"] > 0
