@@ -123,7 +123,8 @@ RM_API int rm_validate_program(uint32_t cmd_count, const uint32_t *words, uint32
  * constant an immediate, no fetch or dispatch — and built at run time (NVRTC, sm_100a) around the same kernel body.
  * Arithmetic per ray is operation for operation the interpreter's: exact mode stays bit-identical, fast mode may round
  * differently where the compiler contracts multiply-adds (within the parity gates).  Compiling takes of the order of a
- * second per (program, mode) and is cached process-wide, so the contexts of a group share it.  Only RM_KERNEL_DIRECT
+ * second per (program, mode) and is cached process-wide (up to 512 programs; beyond that new programs stay on the
+ * interpreter), so the contexts of a group share it.  Only RM_KERNEL_DIRECT
  * paints are affected; with rm_set_early_out on, the interpreter is used.
  * rm_specialize: compile the currently prepared program for the current mode now; paints use it until rm_prepare
  *   receives different words.  RM_E_JIT (reason in rm_last_error) when NVRTC cannot be loaded (libnvrtc.so.12; the

@@ -130,6 +130,7 @@ struct Entry {
     std::string err;
     SpecKernel k;
 };
+constexpr size_t kMaxCacheEntries = 512;
 std::mutex g_mu;
 std::map<Key, std::unique_ptr<Entry>> g_cache;
 
@@ -261,6 +262,12 @@ int spec_get(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, bool e
     std::lock_guard<std::mutex> lock(g_mu);  // one compile at a time; the other members of a group then hit the cache
     if (compiled_now) *compiled_now = false;
     auto it = g_cache.find(key);
+    if (it == g_cache.end() && g_cache.size() >= kMaxCacheEntries) {
+        // kernels are never unloaded (contexts hold pointers into the cache), so the cache is bounded instead: a host that
+        // streams thousands of distinct programs with the policy on falls back to the interpreter for the new ones
+        if (err) *err = "specialisation cache is full (" + std::to_string(kMaxCacheEntries) + " programs): the interpreter is used";
+        return RM_E_JIT;
+    }
     if (it == g_cache.end()) {
         if (compiled_now) *compiled_now = true;
         auto e = std::make_unique<Entry>();
