@@ -94,6 +94,8 @@ extern "C" {
     // verification surface (untimed)
     pub fn rm_paint_debug(ctx: *mut RmCtx, w: u32, h: u32, row0: u32, nrows: u32, cls_host: *mut u8, t_host: *mut f32,
                           counters4: *mut u64, rgba_host: *mut u8) -> i32;
+    pub fn rm_paint_aov(ctx: *mut RmCtx, w: u32, h: u32, row0: u32, nrows: u32, cls_host: *mut u8, t_host: *mut f32,
+                        rgba_host: *mut u8, specialised: *mut i32) -> i32;
     pub fn rm_map(ctx: *mut RmCtx, pts_host: *const f32, n: u64, out_host: *mut f32) -> i32;
     pub fn rm_set_counters(ctx: *mut RmCtx, enable: i32) -> i32;
     pub fn rm_get_counters(ctx: *mut RmCtx, counters4: *mut u64, reset: i32) -> i32;

@@ -235,6 +235,11 @@ RM_API const char *rm_group_last_error(rm_group *g);
  * counters: {N_step, N_hit, N_floor, N_sample}; rgba: nrows*W*4 bytes. */
 RM_API int rm_paint_debug(rm_ctx *ctx, uint32_t W, uint32_t H, uint32_t row0, uint32_t nrows,
                           uint8_t *cls_host, float *t_host, uint64_t *counters4, uint8_t *rgba_host);
+/* The same AOVs (and, optionally, the image) from the PRODUCTION kernel's own march — RM_KERNEL_DIRECT's body, run
+ * specialised when rm_specialize / rm_set_specialize apply to the prepared program (*specialised = 1), else around the
+ * interpreter: lets the parity gates be checked on the kernel that is benchmarked, not on a stand-in. */
+RM_API int rm_paint_aov(rm_ctx *ctx, uint32_t W, uint32_t H, uint32_t row0, uint32_t nrows, uint8_t *cls_host,
+                        float *t_host, uint8_t *rgba_host, int *specialised);
 /* Evaluates the prepared program's map_scene at n host points (xyz interleaved). */
 RM_API int rm_map(rm_ctx *ctx, const float *pts_host, uint64_t n, float *out_host);
 /* Work counters {N_step, N_hit, N_floor, N_sample} accumulated by rm_paint when enabled with

@@ -29,7 +29,7 @@ ABI_SYMBOLS = [
     "rm_create", "rm_create_ex", "rm_destroy", "rm_set_limits", "rm_set_mode", "rm_get_mode", "rm_set_kernel", "rm_set_early_out",
     "rm_prepare", "rm_prepare_uniforms", "rm_program_uploads", "rm_validate_program", "rm_paint", "rm_paint_strips", "rm_paint_strips_into", "rm_shared_frame_create", "rm_shared_frame_open",
     "rm_shared_frame_close", "rm_copy_to_host", "rm_paint_poses", "rm_paint_poses_host", "rm_download",
-    "rm_sync", "rm_paint_debug", "rm_map", "rm_set_counters", "rm_get_counters", "rm_mark", "rm_elapsed_ms",
+    "rm_sync", "rm_paint_debug", "rm_paint_aov", "rm_map", "rm_set_counters", "rm_get_counters", "rm_mark", "rm_elapsed_ms",
     "rm_flush_l2", "rm_fp32_peak", "rm_launch_count", "rm_host_alloc", "rm_host_free", "rm_last_error",
     "rm_strerror", "rm_version",
     "rm_group_create", "rm_group_destroy", "rm_group_size", "rm_group_ctx", "rm_group_set_mode", "rm_group_set_limits",
@@ -92,6 +92,7 @@ def lib() -> C.CDLL:
             "rm_download": (i, [vp, vp, sz]),
             "rm_sync": (i, [vp]),
             "rm_paint_debug": (i, [vp, u32, u32, u32, u32, vp, vp, vp, vp]),
+            "rm_paint_aov": (i, [vp, u32, u32, u32, u32, vp, vp, vp, C.POINTER(i)]),
             "rm_map": (i, [vp, vp, u64, vp]),
             "rm_set_counters": (i, [vp, i]),
             "rm_get_counters": (i, [vp, vp, i]),
@@ -350,6 +351,16 @@ class Context:
         if aov:
             out["cls"], out["t"] = cls, t
         return out
+
+    def paint_aov(self, W: int, H: int, row0: int = 0, nrows: int | None = None) -> dict:
+        """Image + per-sample class / distance from the production kernel itself (specialised if that is on)."""
+        nrows = H - row0 if nrows is None else nrows
+        cls = np.zeros((nrows, W, 16), np.uint8)
+        t = np.zeros((nrows, W, 16), np.float32)
+        rgba = np.zeros((nrows, W, 4), np.uint8)
+        sp = C.c_int()
+        self._chk(self._L.rm_paint_aov(self._h, W, H, row0, nrows, cls.ctypes.data, t.ctypes.data, rgba.ctypes.data, C.byref(sp)))
+        return {"rgba": rgba, "cls": cls, "t": t, "specialised": bool(sp.value)}
 
     def map(self, pts: np.ndarray) -> np.ndarray:
         pts = np.ascontiguousarray(pts, np.float32).reshape(-1, 3)

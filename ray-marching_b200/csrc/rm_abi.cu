@@ -38,8 +38,8 @@ struct rm_ctx {
     // program specialisation (rm_jit.cu): paint the DIRECT kernel through run-time compiled straight-line code
     int spec_policy = 0;          // rm_set_specialize: 1 = every program, compiled on first use
     bool spec_requested = false;  // rm_specialize: the current program only
-    const SpecKernel *spec_cur[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};  // [exact][counters] for the current words
-    bool spec_failed[2][2] = {{false, false}, {false, false}};
+    const SpecKernel *spec_cur[2][3] = {};  // [exact][SPEC_PLAIN / SPEC_COUNT / SPEC_AOV] for the current words
+    bool spec_failed[2][3] = {};
     std::string spec_status;      // why the last specialisation failed
     uint64_t spec_compiles = 0, spec_launches = 0;
     float limits_f[2] = {0.01f, 100.0f};  // renderer.rs:133-137
@@ -281,7 +281,7 @@ int rm_prepare(rm_ctx *c, const void *uniforms144, uint32_t cmd_count, const uin
     // a specialised kernel belongs to one command stream: back to the interpreter (or, with the policy on, the new
     // program is compiled at its first paint)
     c->spec_requested = false;
-    for (int a = 0; a < 2; ++a) for (int b = 0; b < 2; ++b) { c->spec_cur[a][b] = nullptr; c->spec_failed[a][b] = false; }
+    for (int a = 0; a < 2; ++a) for (int b = 0; b < 3; ++b) { c->spec_cur[a][b] = nullptr; c->spec_failed[a][b] = false; }
     ++c->prog_uploads;
     c->prepared = true;
     return RM_OK;

@@ -57,7 +57,34 @@ k_direct(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ prog
     __syncthreads();
     InterpMap<EX, R, EO> map;
     map.prog = s_prog; map.n_insn = fp.n_insn; map.max_dist = fp.max_dist;
-    direct_body<EX, R, COUNT>(fp, dst, pitch, counters, map);
+    direct_body<EX, R, COUNT, false>(fp, dst, pitch, counters, nullptr, nullptr, map);
+}
+
+// the same kernel with the per-sample AOVs written out (verification: rm_paint_aov)
+template <bool EX, int R>
+__global__ void __launch_bounds__(DIRECT_THREADS, (R == 8 ? RM_DIRECT_MINB8 : RM_DIRECT_MINB4))
+k_direct_aov(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ prog_g, uint8_t *__restrict__ dst, size_t pitch,
+             uint8_t *__restrict__ aov_cls, float *__restrict__ aov_t) {
+    extern __shared__ float4 s_prog[];
+    const uint32_t nq = fp.n_insn * 3;
+    for (uint32_t i = threadIdx.x; i < nq; i += blockDim.x) s_prog[i] = reinterpret_cast<const float4 *>(prog_g)[i];
+    __syncthreads();
+    InterpMap<EX, R, false> map;
+    map.prog = s_prog; map.n_insn = fp.n_insn; map.max_dist = fp.max_dist;
+    direct_body<EX, R, false, true>(fp, dst, pitch, nullptr, aov_cls, aov_t, map);
+}
+
+template <bool EX, int R>
+cudaError_t launch_direct_aov_t(const FrameParams &fp, const RmInsn *prog, uint8_t *dst, size_t pitch, uint8_t *cls, float *t,
+                                cudaStream_t st) {
+    auto kern = k_direct_aov<EX, R>;
+    const size_t smem = (size_t)fp.n_insn * sizeof(RmInsn);
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    const uint32_t tile_h = direct_tile_rows(R);
+    const unsigned grid = ((fp.W + TILE_W_D - 1) / TILE_W_D) * ((fp.nrows + tile_h - 1) / tile_h);
+    kern<<<grid, DIRECT_THREADS, smem, st>>>(fp, prog, dst, pitch, cls, t);
+    return cudaGetLastError();
 }
 
 template <bool EX, int R, bool COUNT, bool EO>
@@ -75,19 +102,20 @@ cudaError_t launch_direct_t(const FrameParams &fp, const RmInsn *prog, uint8_t *
 
 }  // namespace
 
+static int direct_rays_per_thread(const FrameParams &fp);
+
+cudaError_t launch_direct_aov(bool exact, const FrameParams &fp, const RmInsn *prog_dev, uint8_t *dst, size_t pitch, uint8_t *cls,
+                              float *t, cudaStream_t st) {
+    if (fp.nrows == 0 || fp.W == 0) return cudaSuccess;
+    const int kR = direct_rays_per_thread(fp);
+    if (exact) return kR == 8 ? launch_direct_aov_t<true, 8>(fp, prog_dev, dst, pitch, cls, t, st) : launch_direct_aov_t<true, 4>(fp, prog_dev, dst, pitch, cls, t, st);
+    return kR == 8 ? launch_direct_aov_t<false, 8>(fp, prog_dev, dst, pitch, cls, t, st) : launch_direct_aov_t<false, 4>(fp, prog_dev, dst, pitch, cls, t, st);
+}
+
 cudaError_t launch_direct(bool exact, bool early_out, const FrameParams &fp, const RmInsn *prog_dev, uint8_t *dst, size_t pitch,
                           unsigned long long *counters, cudaStream_t st) {
     if (fp.nrows == 0 || fp.W == 0) return cudaSuccess;
-    // Rays per thread: 4 for shallow programs (more threads, less lock-step waste), 8 for deep ones (fetch/dispatch
-    // amortised over more rays).  Measured on B200 on truncated S2 chains at 1080p (tools/crossover.py, ms per frame,
-    // R=4 / R=8): 1 instruction 0.72/0.85, 3: 1.38/1.47, 4: 1.80/1.82, 5: 2.10/2.09, 8: 3.21/3.14, 32: 12.39/11.87.
-    // RM_DIRECT_R overrides.
-    static const int kForce = [] {
-        const char *s = std::getenv("RM_DIRECT_R");
-        const int v = s ? std::atoi(s) : 0;
-        return (v == 4 || v == 8) ? v : 0;
-    }();
-    const int kR = kForce ? kForce : (fp.n_insn <= 4 ? 4 : 8);
+    const int kR = direct_rays_per_thread(fp);
 #define RM_DIRECT_DISPATCH2(EXV, RV, EOV)                                                      \
     (counters ? launch_direct_t<EXV, RV, true, EOV>(fp, prog_dev, dst, pitch, counters, st)     \
               : launch_direct_t<EXV, RV, false, EOV>(fp, prog_dev, dst, pitch, counters, st))
@@ -96,6 +124,19 @@ cudaError_t launch_direct(bool exact, bool early_out, const FrameParams &fp, con
     return kR == 8 ? RM_DIRECT_DISPATCH(false, 8) : RM_DIRECT_DISPATCH(false, 4);
 #undef RM_DIRECT_DISPATCH2
 #undef RM_DIRECT_DISPATCH
+}
+
+// Rays per thread: 4 for shallow programs (more threads, less lock-step waste), 8 for deep ones (fetch/dispatch
+// amortised over more rays).  Measured on B200 on truncated S2 chains at 1080p (tools/crossover.py, ms per frame,
+// R=4 / R=8): 1 instruction 0.72/0.85, 3: 1.38/1.47, 4: 1.80/1.82, 5: 2.10/2.09, 8: 3.21/3.14, 32: 12.39/11.87.
+// RM_DIRECT_R overrides.
+static int direct_rays_per_thread(const FrameParams &fp) {
+    static const int kForce = [] {
+        const char *s = std::getenv("RM_DIRECT_R");
+        const int v = s ? std::atoi(s) : 0;
+        return (v == 4 || v == 8) ? v : 0;
+    }();
+    return kForce ? kForce : (fp.n_insn <= 4 ? 4 : 8);
 }
 
 }  // namespace rm

@@ -22,9 +22,13 @@ namespace rm {
 // rows of the 8-wide pixel tile one 128-thread block covers
 __host__ __device__ constexpr uint32_t direct_tile_rows(int R) { return 4u * (32u / (16u / (uint32_t)R)) / 8u; }
 
-template <bool EX, int R, bool COUNT, class MAP>
+// AOV (verification only): also writes every sample's class (0 sky, 1 floor, 2 object) and distance (hit distance, else
+// the floor distance of wgsl:120) to aov_cls / aov_t[(row * W + x) * 16 + sample] — the same outputs, in the same
+// layout, as the one-thread-per-sample verification kernel (rm_kernels.cu), but from THIS kernel's own march.
+template <bool EX, int R, bool COUNT, bool AOV, class MAP>
 __device__ __forceinline__ void direct_body(const FrameParams &fp, uint8_t *__restrict__ dst, size_t pitch,
-                                            unsigned long long *__restrict__ counters, MAP &map) {
+                                            unsigned long long *__restrict__ counters, uint8_t *__restrict__ aov_cls,
+                                            float *__restrict__ aov_t, MAP &map) {
     static_assert(R == 2 || R == 4 || R == 8, "2, 4 or 8 rays per thread");
     constexpr int TPP = 16 / R;           // threads per pixel
     constexpr int PPW = 32 / TPP;         // pixels per warp: 4, 8 or 16 consecutive pixels of the block's 8-wide tile
@@ -43,6 +47,8 @@ __device__ __forceinline__ void direct_body(const FrameParams &fp, uint8_t *__re
     float rdx[R], rdy[R], rdz[R], dist[R], code[R];
     uint32_t live = 0, hit = 0;  // bit r: ray r still marching / ray r hit the scene
     uint32_t c_step = 0, c_hit = 0, c_floor = 0, c_sample = 0;
+    float t_miss[AOV ? R : 1];
+    int cls_miss[AOV ? R : 1];
     RM_FOR_R { rdx[r] = rdy[r] = rdz[r] = 0.f; dist[r] = 0.f; code[r] = RM_CODE_SKY; }
     if (inside) {
         const uint32_t fy = frame_row(fp, ry);
@@ -53,6 +59,7 @@ __device__ __forceinline__ void direct_body(const FrameParams &fp, uint8_t *__re
             rdx[r] = d[0]; rdy[r] = d[1]; rdz[r] = d[2];
             const int cls = shade_miss(o, d, c, t);  // wgsl:117-130: what the ray gets if it never hits
             code[r] = cls == 0 ? RM_CODE_SKY : (c[0] > 0.2f ? RM_CODE_FLOOR_LIGHT : RM_CODE_FLOOR_DARK);
+            if constexpr (AOV) { t_miss[r] = t; cls_miss[r] = cls; }
         }
         if (COUNT) c_sample = R;
         if (fp.max_iter > 0) live = (1u << R) - 1u;
@@ -137,6 +144,14 @@ __device__ __forceinline__ void direct_body(const FrameParams &fp, uint8_t *__re
         }
     }
     if (COUNT && inside) RM_FOR_R if (!(hit0 & (1u << r)) && code[r] != RM_CODE_SKY) ++c_floor;
+    if constexpr (AOV) if (inside) {
+        const size_t base = ((size_t)ry * fp.W + px) * 16 + grp * R;
+        RM_FOR_R {
+            const bool h = (hit0 >> r) & 1u;
+            aov_cls[base + r] = (uint8_t)(h ? 2 : cls_miss[r]);
+            aov_t[base + r] = h ? dist[r] : t_miss[r];
+        }
+    }
 
     // ---------------- resolve: 16-sample mean in shader order (wgsl:44-45,68-75) ----------------
     // a pixel's threads hold consecutive sample ranges, so the running sum visits them in lane order

@@ -117,11 +117,12 @@ const Nvrtc &nvrtc() {
 struct Key {
     std::vector<uint32_t> words;
     uint32_t cmd_count;
-    bool exact, count;
+    bool exact;
+    int variant;
     bool operator<(const Key &o) const {
         if (cmd_count != o.cmd_count) return cmd_count < o.cmd_count;
         if (exact != o.exact) return exact < o.exact;
-        if (count != o.count) return count < o.count;
+        if (variant != o.variant) return variant < o.variant;
         return words < o.words;
     }
 };
@@ -136,7 +137,7 @@ std::map<Key, std::unique_ptr<Entry>> g_cache;
 
 }  // namespace
 
-int spec_generate_source(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, bool exact, bool count, int R,
+int spec_generate_source(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, bool exact, int variant, int R,
                          std::string *src, int *r_out, int *minb_out, uint32_t *est_out, std::string *err) {
     // walk the postfix stream (builder.rs:26-62) with a stack of SSA value numbers: command i defines v<i>
     std::string body;
@@ -217,10 +218,10 @@ int spec_generate_source(uint32_t cmd_count, const uint32_t *words, uint32_t n_w
     else s += body + "        RM_FOR_R out[r] = " + var(stack.back()) + "[r];\n";
     s += "    }\n};\n}  // namespace rm\n";
     s += "extern \"C\" __global__ void __launch_bounds__(RM_DIRECT_THREADS, " + std::to_string(minb) + ")\n";
-    s += "rm_spec(const __grid_constant__ rm::FrameParams fp, uint8_t *__restrict__ dst, size_t pitch, unsigned long long *__restrict__ counters) {\n";
+    s += "rm_spec(const __grid_constant__ rm::FrameParams fp, uint8_t *__restrict__ dst, size_t pitch, unsigned long long *__restrict__ counters,\n        uint8_t *__restrict__ aov_cls, float *__restrict__ aov_t) {\n";
     s += "    rm::SpecMap<" + std::string(exact ? "true" : "false") + ", " + std::to_string(R) + "> map;\n    map.max_dist = fp.max_dist;\n";
-    s += "    rm::direct_body<" + std::string(exact ? "true" : "false") + ", " + std::to_string(R) + ", " + (count ? "true" : "false") +
-         ">(fp, dst, pitch, counters, map);\n}\n";
+    s += "    rm::direct_body<" + std::string(exact ? "true" : "false") + ", " + std::to_string(R) + ", " + (variant == SPEC_COUNT ? "true" : "false") + ", " +
+         (variant == SPEC_AOV ? "true" : "false") + ">(fp, dst, pitch, counters, aov_cls, aov_t, map);\n}\n";
     *src = std::move(s);
     return RM_OK;
 }
@@ -256,9 +257,9 @@ int spec_compile(const std::string &src, std::string *cubin, std::string *err) {
     return RM_OK;
 }
 
-int spec_get(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, bool exact, bool count, const SpecKernel **out,
+int spec_get(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, bool exact, int variant, const SpecKernel **out,
              bool *compiled_now, std::string *err) {
-    Key key{std::vector<uint32_t>(words, words + n_words), cmd_count, exact, count};
+    Key key{std::vector<uint32_t>(words, words + n_words), cmd_count, exact, variant};
     std::lock_guard<std::mutex> lock(g_mu);  // one compile at a time; the other members of a group then hit the cache
     if (compiled_now) *compiled_now = false;
     auto it = g_cache.find(key);
@@ -273,8 +274,8 @@ int spec_get(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, bool e
         auto e = std::make_unique<Entry>();
         const auto t0 = std::chrono::steady_clock::now();
         std::string src, cubin;
-        e->k.exact = exact; e->k.count = count;
-        e->rc = spec_generate_source(cmd_count, words, n_words, exact, count, 0, &src, &e->k.rays_per_thread, &e->k.min_blocks,
+        e->k.exact = exact; e->k.variant = variant;
+        e->rc = spec_generate_source(cmd_count, words, n_words, exact, variant, 0, &src, &e->k.rays_per_thread, &e->k.min_blocks,
                                      &e->k.est_insn_per_ray, &e->err);
         if (e->rc == RM_OK) e->rc = spec_compile(src, &cubin, &e->err);
         if (e->rc == RM_OK) {
@@ -300,12 +301,12 @@ int spec_get(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, bool e
 }
 
 cudaError_t launch_spec(const SpecKernel &k, const FrameParams &fp, uint8_t *dst, size_t pitch, unsigned long long *counters,
-                        cudaStream_t st) {
+                        uint8_t *aov_cls, float *aov_t, cudaStream_t st) {
     if (fp.nrows == 0 || fp.W == 0) return cudaSuccess;
     const uint32_t tile_h = direct_tile_rows(k.rays_per_thread);
     const unsigned grid = ((fp.W + RM_DIRECT_TILE_W - 1) / RM_DIRECT_TILE_W) * ((fp.nrows + tile_h - 1) / tile_h);
     FrameParams p = fp;
-    void *args[] = {&p, &dst, &pitch, &counters};
+    void *args[] = {&p, &dst, &pitch, &counters, &aov_cls, &aov_t};
     return cudaLaunchKernel((const void *)k.fn, dim3(grid), dim3(RM_DIRECT_THREADS), args, 0, st);
 }
 

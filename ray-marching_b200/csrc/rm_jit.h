@@ -18,12 +18,16 @@
 
 namespace rm {
 
+// what the kernel does besides painting: nothing, the work counters (rm_set_counters), or the per-sample AOVs (rm_paint_aov)
+enum { SPEC_PLAIN = 0, SPEC_COUNT = 1, SPEC_AOV = 2 };
+
 struct SpecKernel {
     cudaKernel_t fn = nullptr;
     cudaLibrary_t lib = nullptr;
     int rays_per_thread = 0;   // 2, 4 or 8
     int min_blocks = 0;        // __launch_bounds__ second argument
-    bool exact = false, count = false;
+    bool exact = false;
+    int variant = 0;           // SPEC_PLAIN / SPEC_COUNT / SPEC_AOV
     double compile_ms = 0.0;   // NVRTC compile + module load
     size_t cubin_bytes = 0;
     uint32_t est_insn_per_ray = 0;
@@ -31,19 +35,19 @@ struct SpecKernel {
 
 // CUDA source of the specialised kernel for this (already validated) command stream.  rays_per_thread 0 = choose from
 // the code-size estimate.  Returns RM_OK, or RM_E_JIT when the program is too long to specialise usefully.
-int spec_generate_source(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, bool exact, bool count,
+int spec_generate_source(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, bool exact, int variant,
                          int rays_per_thread, std::string *src, int *r_out, int *minb_out, uint32_t *est_out, std::string *err);
 
 // NVRTC-compiles `src` for sm_100a to a cubin (no GPU needed).  RM_E_JIT + message when libnvrtc cannot be loaded or
 // the compile fails.
 int spec_compile(const std::string &src, std::string *cubin, std::string *err);
 
-// Cached: generate + compile + load for (program, mode, counters).  The returned pointer stays valid for the life of
+// Cached: generate + compile + load for (program, mode, variant).  The returned pointer stays valid for the life of
 // the process.  `cached` reports whether this call had to compile.
-int spec_get(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, bool exact, bool count, const SpecKernel **out,
+int spec_get(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, bool exact, int variant, const SpecKernel **out,
              bool *compiled_now, std::string *err);
 
 cudaError_t launch_spec(const SpecKernel &k, const FrameParams &fp, uint8_t *dst, size_t pitch, unsigned long long *counters,
-                        cudaStream_t st);
+                        uint8_t *aov_cls, float *aov_t, cudaStream_t st);
 
 }  // namespace rm

@@ -31,4 +31,8 @@ cudaError_t launch_wavefront2(WavefrontState *ws, bool exact, const FrameParams 
 cudaError_t launch_direct(bool exact, bool early_out, const FrameParams &fp, const RmInsn *prog_dev, uint8_t *dst, size_t pitch,
                           unsigned long long *counters, cudaStream_t st);
 
+// The same kernel with the per-sample classes / distances of its own march written out (verification, rm_paint_aov).
+cudaError_t launch_direct_aov(bool exact, const FrameParams &fp, const RmInsn *prog_dev, uint8_t *dst, size_t pitch, uint8_t *cls,
+                              float *t, cudaStream_t st);
+
 }  // namespace rm

@@ -224,3 +224,51 @@ def test_group_specialises_once_for_all_members(rm):
         got = np.zeros((H, W, 4), np.uint8)
         g.paint_bands(W, H, 16, got)
     assert np.array_equal(got, full)
+
+
+@pytest.mark.parametrize("name,W,H,yaw,pitch", cases())
+@pytest.mark.parametrize("specialised", [False, True])
+def test_production_kernel_own_aovs_meet_all_three_gates(rm, ctx, name, W, H, yaw, pitch, specialised):
+    """rm_paint_aov: classes and hit distances written by the production kernel's OWN march (interpreter build and
+    run-time specialised build), not by the verification kernel.  Exact mode: bit-identical to the oracle.  Fast mode:
+    hit-mask, RGBA8 and hit-distance gates of the north star."""
+    from test_gpu_parity import GATE_T_FRAC
+    cmd, words = h.SCENES[name]()
+    u = h.orbit_uniforms(W, H, yaw=yaw, pitch=pitch)
+    ref = h.oracle_render(u, cmd, words, W, H, aov=True)
+    for mode in (rm.MODE_EXACT, rm.MODE_FAST):
+        ctx.set_mode(mode)
+        ctx.prepare(u, cmd, words)
+        if specialised:
+            ctx.specialize()
+        else:
+            ctx.set_specialize(False)
+        out = ctx.paint_aov(W, H)
+        assert out["specialised"] == specialised
+        assert np.array_equal(out["rgba"], ctx.render(u, cmd, words, W, H))  # the AOV build paints the same image
+        if mode == rm.MODE_EXACT:
+            assert np.array_equal(out["cls"], ref["cls"])
+            assert np.array_equal(out["t"].view(np.uint32), ref["t"].view(np.uint32))
+            assert np.array_equal(out["rgba"], ref["rgba"])
+        else:
+            g = gates(out["rgba"], ref["rgba"], out["cls"], ref["cls"], out["t"], ref["t"])
+            print(name, "specialised" if specialised else "interpreter", g)
+            assert g["hitmask_pix"] <= GATE_HITMASK, g
+            assert g["rgba_frac"] <= GATE_RGBA_FRAC, g
+            assert g["t_frac"] <= GATE_T_FRAC, g
+
+
+def test_aov_bands_and_ragged_sizes(rm, ctx):
+    W, H = 77, 45
+    cmd, words = h.scene_s2()
+    u = h.orbit_uniforms(W, H, yaw=0.6, pitch=0.4)
+    ref = h.oracle_render(u, cmd, words, W, H, aov=True)
+    ctx.set_mode(rm.MODE_EXACT)
+    ctx.prepare(u, cmd, words)
+    ctx.specialize()
+    for row0, n in ((0, 45), (7, 13), (44, 1)):
+        out = ctx.paint_aov(W, H, row0, n)
+        assert out["specialised"]
+        assert np.array_equal(out["cls"], ref["cls"][row0:row0 + n])
+        assert np.array_equal(out["t"].view(np.uint32), ref["t"][row0:row0 + n].view(np.uint32))
+        assert np.array_equal(out["rgba"], ref["rgba"][row0:row0 + n])

@@ -28,8 +28,8 @@ def test_source_is_one_ssa_value_per_command_in_stream_order(rm):
     assert "v2[r] = fminf(v0[r], v1[r])" in src              # a = deeper entry, b = top (wgsl:243-244)
     assert "v4[r] = fmaxf(v2[r], -v3[r])" in src             # A \ B = max(a, -b)     (wgsl:248-252)
     assert "RM_FOR_R out[r] = v4[r];" in src
-    assert 'extern "C" __global__' in src and "rm::direct_body<false, 4, false>" in src
-    assert "direct_body<true, 4, false>" in rm.spec_source(cmd, words, rm.MODE_EXACT)
+    assert 'extern "C" __global__' in src and "rm::direct_body<false, 4, false, false>" in src
+    assert "direct_body<true, 4, false, false>" in rm.spec_source(cmd, words, rm.MODE_EXACT)
 
 
 def test_constants_are_emitted_by_their_bits(rm):
