@@ -90,3 +90,34 @@ def test_cfg5_pose_batch_to_host_equals_single_frames_at_1080p(rm, ctx):
     got = buf.array.reshape(n, H, W, 4)
     assert [digest(got[k]) for k in range(n)] == singles
     buf.free()
+
+
+def test_cfg3_specialised_kernel_at_3840x2160(rm, ctx):
+    """The run-time specialised kernel (what `python bench.py` times) at the full config-3 size: exact mode must give
+    the interpreter's bytes and work counters; fast mode may differ from the interpreter by one LSB on a few pixels (the
+    compiler contracts multiply-adds differently), never by more."""
+    W, H = 3840, 2160
+    cmd, words = h.scene_s2()
+    u = h.orbit_uniforms(W, H, yaw=0.6, pitch=0.4)
+    for mode in (rm.MODE_EXACT, rm.MODE_FAST):
+        ctx.set_mode(mode)
+        ctx.set_specialize(False)
+        ctx.set_counters(True)
+        interp = ctx.render(u, cmd, words, W, H)
+        cnt_i = ctx.get_counters()
+        ctx.specialize()
+        n0 = ctx.spec_info()["launches"]
+        spec = ctx.render(u, cmd, words, W, H)
+        cnt_s = ctx.get_counters()
+        info = ctx.spec_info()  # of the counters build, the one that just ran
+        ctx.set_counters(False)
+        assert info["launches"] == n0 + 1 and info["rays_per_thread"] == 2
+        if mode == rm.MODE_EXACT:
+            assert digest(spec) == digest(interp) and np.array_equal(cnt_i, cnt_s)
+        else:
+            d = np.abs(spec.astype(np.int16) - interp.astype(np.int16)).max(-1)
+            assert d.max() <= 1 and (d > 0).mean() <= 1e-3, (int(d.max()), float((d > 0).mean()))
+            assert abs(int(cnt_i[1]) - int(cnt_s[1])) <= 1e-4 * W * H  # hit samples: far fewer flips than 0.01 % of the pixels
+        # a band of the specialised kernel equals the same rows of its full frame
+        band = ctx.render(u, cmd, words, W, H, row0=1003, nrows=517)
+        assert np.array_equal(band, spec[1003:1520])
