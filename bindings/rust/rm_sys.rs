@@ -45,7 +45,7 @@ extern "C" {
 
     // program specialisation: compile the scene into the kernel (optional)
     pub fn rm_specialize(ctx: *mut RmCtx) -> i32;
-    pub fn rm_set_specialize(ctx: *mut RmCtx, on: i32) -> i32;
+    pub fn rm_set_specialize(ctx: *mut RmCtx, on: i32) -> i32;   // 0 interpreter, 1 at first paint, 2 in the background
     pub fn rm_spec_info(ctx: *mut RmCtx, active: *mut i32, rays_per_thread: *mut i32, min_blocks: *mut i32,
                         compile_ms: *mut f64, cubin_bytes: *mut u64, compiles: *mut u64, launches: *mut u64) -> i32;
     pub fn rm_spec_status(ctx: *mut RmCtx) -> *const c_char;

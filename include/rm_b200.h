@@ -132,6 +132,9 @@ RM_API int rm_validate_program(uint32_t cmd_count, const uint32_t *words, uint32
  *   instruction cache — painting then simply continues through the interpreter.
  * rm_set_specialize(1): do that automatically for every program at its first paint (a stall of one compile per new
  *   program: meant for batch rendering, not for interactive editing); failures are silent, see rm_spec_status.
+ *   rm_set_specialize(2): the same without the stall — the program is compiled by a background thread of the context
+ *   while paints keep going through the interpreter, and the first paint after the compile has finished switches over
+ *   (a compile for words that have changed meanwhile is dropped): the setting for an interactive editor.
  *   rm_set_specialize(0) returns to the interpreter from the next paint on (also after rm_specialize). */
 RM_API int rm_specialize(rm_ctx *ctx);
 RM_API int rm_set_specialize(rm_ctx *ctx, int on);

@@ -234,8 +234,9 @@ class Context:
         """Compile the prepared program for the current mode now; raises RmError(-9) if that is not possible."""
         self._chk(self._L.rm_specialize(self._h))
 
-    def set_specialize(self, on: bool):
-        self._chk(self._L.rm_set_specialize(self._h, int(bool(on))))
+    def set_specialize(self, on):
+        """0 / False: interpreter; 1 / True: compile every program at its first paint; 2: compile in the background."""
+        self._chk(self._L.rm_set_specialize(self._h, int(on)))
 
     def spec_info(self) -> dict:
         a, r, mb, ms = C.c_int(), C.c_int(), C.c_int(), C.c_double()

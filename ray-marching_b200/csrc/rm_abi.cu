@@ -3,11 +3,13 @@
 // all wgpu plumbing — limits, command buffer (decoded), uniforms — plus a framebuffer.
 #include <cuda_runtime.h>
 
+#include <atomic>
 #include <chrono>
 #include <cstdio>
 #include <cstring>
 #include <new>
 #include <string>
+#include <thread>
 
 #include "../../include/rm_b200.h"
 #include "rm_jit.h"
@@ -36,7 +38,14 @@ struct rm_ctx {
     bool counters_on = false;
     bool early_out = false;  // rm_set_early_out: opt-in, never on by default
     // program specialisation (rm_jit.cu): paint the DIRECT kernel through run-time compiled straight-line code
-    int spec_policy = 0;          // rm_set_specialize: 1 = every program, compiled on first use
+    int spec_policy = 0;          // rm_set_specialize: 1 = every program, compiled at its first paint; 2 = compiled in the background
+    // policy 2: one worker thread per context compiles while the interpreter keeps painting
+    std::thread spec_worker;
+    std::atomic<int> spec_bg_state{0};  // 0 idle, 1 compiling, 2 result ready
+    uint64_t spec_bg_generation = 0;    // prog_uploads of the words being compiled: a result for older words is dropped
+    int spec_bg_ex = 0, spec_bg_variant = 0, spec_bg_rc = 0;
+    const SpecKernel *spec_bg_kernel = nullptr;
+    std::string spec_bg_err;
     bool spec_requested = false;  // rm_specialize: the current program only
     const SpecKernel *spec_cur[2][3] = {};  // [exact][SPEC_PLAIN / SPEC_COUNT / SPEC_AOV] for the current words
     bool spec_failed[2][3] = {};
@@ -201,6 +210,7 @@ int rm_create(int cuda_device, rm_ctx **out) { return rm_create_ex(cuda_device, 
 
 void rm_destroy(rm_ctx *c) {
     if (!c) return;
+    if (c->spec_worker.joinable()) c->spec_worker.join();
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     wavefront_destroy(&c->wf);

@@ -272,3 +272,34 @@ def test_aov_bands_and_ragged_sizes(rm, ctx):
         assert np.array_equal(out["cls"], ref["cls"][row0:row0 + n])
         assert np.array_equal(out["t"].view(np.uint32), ref["t"][row0:row0 + n].view(np.uint32))
         assert np.array_equal(out["rgba"], ref["rgba"][row0:row0 + n])
+
+
+def test_background_policy_never_stalls_and_switches_over(rm, ctx):
+    """rm_set_specialize(2): the first paints of a new program go through the interpreter while a worker thread compiles;
+    a later paint adopts the kernel.  Exact mode, so every frame on either path must equal the oracle."""
+    import time
+    W, H = 96, 64
+    u = h.orbit_uniforms(W, H, yaw=0.3, pitch=0.2)
+    # a program nobody has compiled in this process yet (the cache is process-wide)
+    words = h.sphere((0.123, 0.2, -0.1), 0.9) + h.box((0.4, 0.1, 0.0), (0.5, 0.6, 0.7)) + [103, h.fbits(0.37)]
+    ref = h.oracle_render(u, 3, words, W, H)["rgba"]
+    ctx.set_mode(rm.MODE_EXACT)
+    ctx.set_specialize(2)
+    t0 = time.perf_counter()
+    img = ctx.render(u, 3, words, W, H)
+    first_ms = (time.perf_counter() - t0) * 1e3
+    assert np.array_equal(img, ref)
+    assert ctx.spec_info()["launches"] == 0           # painted by the interpreter, the compile had only just started
+    assert first_ms < 100, first_ms                   # no compile in the paint path (a compile is 150-600 ms)
+    deadline = time.time() + 30
+    while ctx.spec_info()["launches"] == 0 and time.time() < deadline:
+        assert np.array_equal(ctx.render(u, 3, words, W, H), ref)
+        time.sleep(0.02)
+    info = ctx.spec_info()
+    assert info["active"] and info["launches"] >= 1 and info["compiles"] == 1
+    # words that change while a compile is in flight: its result is dropped, nothing crashes, frames stay right
+    for i in range(4):
+        w2 = h.sphere((0.01 * i, 0.2, -0.1), 0.8 + 0.01 * i)
+        assert np.array_equal(ctx.render(u, 1, w2, W, H), h.oracle_render(u, 1, w2, W, H)["rgba"])
+    with pytest.raises(rm.RmError):
+        ctx.set_specialize(3)
