@@ -45,8 +45,9 @@ enum {
     RM_E_STACK_UNBALANCED = -5,  /* pop from empty stack / truncated params / empty result */
     RM_E_CUDA = -6,
     RM_E_NOT_PREPARED = -7,
-    RM_E_BAD_PARAM = -8,         /* SmoothUnion k <= 0 or non-finite */
-    RM_E_JIT = -9                /* program specialisation failed; the interpreter kernel keeps working */
+    RM_E_BAD_PARAM = -8,         /* SmoothUnion k / Scale s <= 0 or non-finite; ScalePop s differs from its push */
+    RM_E_JIT = -9,               /* program specialisation failed; the interpreter kernel keeps working */
+    RM_E_UNSUPPORTED = -10       /* the selected kernel does not run this program (N4 commands need RM_KERNEL_DIRECT / _SIMPLE) */
 };
 
 /* ---- byte sizes of the reference's GPU buffers --------------------------------------------- */
@@ -54,6 +55,7 @@ enum {
 #define RM_LIMITS_BYTES 12u    /* RayMarchLimits {f32 min_dist, f32 max_dist, u32 max_iter} :36-41 */
 #define RM_DEFAULT_MAX_WORDS 255u /* 1024-B command buffer minus cmd_count       renderer.rs:144 */
 #define RM_STACK_MAX 32u          /* value_stack_max_size                         wgsl:173 */
+#define RM_POS_STACK_MAX 8u       /* nesting depth of space-transform groups (N4 extension) */
 #define RM_SAMPLES_PER_PIXEL 16u  /* aa_samples^2                                 wgsl:34 */
 
 /* ---- command opcodes: CSGCommandType, csg/builder.rs:1-24 ---------------------------------- */
@@ -63,7 +65,20 @@ enum {
     RM_OP_UNION = 100,        /* [100]   min(a,b)          wgsl:242-246 */
     RM_OP_SUBTRACTION = 101,  /* [101]   max(a,-b)         wgsl:248-252 */
     RM_OP_INTERSECTION = 102, /* [102]   max(a,b)   extension: slot reserved at builder.rs:14 */
-    RM_OP_SMOOTH_UNION = 103  /* [103,k] polynomial smooth-min, extension */
+    RM_OP_SMOOTH_UNION = 103, /* [103,k] polynomial smooth-min, extension */
+    /* N4 extension: the commands the reference's enum reserves in comments, at the values the
+     * #[repr(u32)] enum would give them (builder.rs:8 Plane after Box; builder.rs:16-23 TranslationPush = 200 ...).
+     * A Push saves the evaluation point and replaces it, the child's commands follow ("1 child, transforms space"),
+     * the matching Pop restores it; Push/Pop push no value.  Groups nest up to RM_POS_STACK_MAX deep and must
+     * enclose exactly one value.  Arithmetic, one rounding per operation in exact mode (oracle/rm_oracle.c): */
+    RM_OP_PLANE = 2,              /* [2, nx,ny,nz, h]    ((x*nx + y*ny) + z*nz) + h; n is expected to be unit length */
+    RM_OP_TRANSLATION_PUSH = 200, /* [200, tx,ty,tz]     pos = pos - t */
+    RM_OP_TRANSLATION_POP = 201,  /* [201] */
+    RM_OP_ROTATION_PUSH = 202,    /* [202, m00,m01,m02, m10,m11,m12, m20,m21,m22]  row-major rotation R (object -> world):
+                                   * pos = transpose(R) * pos, x' = (m00*x + m10*y) + m20*z ... */
+    RM_OP_ROTATION_POP = 203,     /* [203] */
+    RM_OP_SCALE_PUSH = 204,       /* [204, s]            pos = pos / s   (uniform, s finite and > 0) */
+    RM_OP_SCALE_POP = 205         /* [205, s]            same s as the push; the child's distance is multiplied by s */
 };
 
 /* ---- arithmetic mode ------------------------------------------------------------------------ */

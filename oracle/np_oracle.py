@@ -5,7 +5,9 @@ every add/mul/div/sqrt once and never fuses, i.e. the same IEEE semantics the C 
 with (-ffp-contract=off).  PARITY UNPINNED by the reference itself (no tests/goldens upstream).
 
 Follows /root/reference/src/ray_marching/ray_marching.wgsl: fs_main :36-76, ray_march :87-131,
-calculate_normal :135-144, map_scene/eval_cmd_* :187-252 (+ extension opcodes 102/103).
+calculate_normal :135-144, map_scene/eval_cmd_* :187-252 (+ extension opcodes 102/103, and the N4
+extension: Plane = 2, Translation/Rotation/Scale Push/Pop = 200..205 on a position stack, at the opcode
+values the reference's enum reserves in comments, builder.rs:8,16-23).
 """
 from __future__ import annotations
 
@@ -33,11 +35,41 @@ def map_scene(cmd_count, words, px, py, pz, max_dist=F(100.0)):
     w = np.asarray(words, np.uint32)
     fb = w.view(F)
     stack = []
+    pos_stack = []  # N4: saved evaluation points
     ptr = 0
     zero = F(0.0)
     for _ in range(cmd_count):
         t = int(w[ptr]); ptr += 1
-        if t == 0:  # sphere :229-233
+        if t == 200:  # TranslationPush: pos = pos - t
+            tx, ty, tz = fb[ptr:ptr + 3]; ptr += 3
+            pos_stack.append((px, py, pz))
+            px, py, pz = (px - tx).astype(F), (py - ty).astype(F), (pz - tz).astype(F)
+            continue
+        if t == 202:  # RotationPush (row-major R, object -> world): pos = R^T pos
+            m = fb[ptr:ptr + 9]; ptr += 9
+            pos_stack.append((px, py, pz))
+            x = ((m[0] * px + m[3] * py) + m[6] * pz).astype(F)
+            y = ((m[1] * px + m[4] * py) + m[7] * pz).astype(F)
+            z = ((m[2] * px + m[5] * py) + m[8] * pz).astype(F)
+            px, py, pz = x, y, z
+            continue
+        if t == 204:  # ScalePush: pos = pos / s
+            sc = fb[ptr]; ptr += 1
+            pos_stack.append((px, py, pz))
+            px, py, pz = (px / sc).astype(F), (py / sc).astype(F), (pz / sc).astype(F)
+            continue
+        if t in (201, 203):  # Translation / Rotation Pop
+            px, py, pz = pos_stack.pop()
+            continue
+        if t == 205:  # ScalePop: the child's distance was measured in scaled units
+            sc = fb[ptr]; ptr += 1
+            px, py, pz = pos_stack.pop()
+            stack[-1] = (stack[-1] * sc).astype(F)
+            continue
+        if t == 2:  # plane: dot(pos, n) + h
+            nx, ny, nz, h = fb[ptr:ptr + 4]; ptr += 4
+            v = ((px * nx + py * ny) + pz * nz) + h
+        elif t == 0:  # sphere :229-233
             cx, cy, cz, r = fb[ptr:ptr + 4]; ptr += 4
             dx, dy, dz = px - cx, py - cy, pz - cz
             v = np.sqrt((dx * dx + dy * dy) + dz * dz) - r

@@ -20,7 +20,11 @@
  *   src/ray_marching/renderer.rs:29-41          Uniforms (144 B) / RayMarchLimits (12 B) layouts
  *   src/ray_marching/csg/builder.rs:1-62        wire format of the u32 word buffer
  * plus the two build-defined extension opcodes of SURVEY.md §8(a) X1/X2 (Intersection = 102,
- * SmoothUnion = 103 [k]) which have no counterpart in the reference.
+ * SmoothUnion = 103 [k]) which have no counterpart in the reference, and the N4 extension
+ *  at the opcode values the reference's enum reserves in comments
+ * (builder.rs:8,16-23): Plane = 2 and the space-transform pairs TranslationPush/Pop = 200/201,
+ * RotationPush/Pop = 202/203, ScalePush/Pop = 204/205, evaluated on a position stack the way
+ * the reserved names describe ("1 child, transforms space").  Normative semantics: map_scene().
  *
  * Numerics: float32 throughout, IEEE add/mul/div/sqrt, NO fused multiply-add (build with
  * -ffp-contract=off), evaluation order exactly as SURVEY.md §8(c).1 rules 1–11.
@@ -43,6 +47,7 @@
 #define RMO_E_BAD_PROGRAM (-2)
 
 #define RMO_STACK_MAX 32 /* ray_marching.wgsl:173 */
+#define RMO_POS_STACK_MAX 8 /* N4: nesting depth of space transforms (build-defined) */
 
 /* sample classes written to the per-sample AOV */
 #define RMO_CLS_SKY 0
@@ -92,10 +97,60 @@ static float map_scene(const rmo_scene *sc, float px, float py, float pz) {
     uint32_t sp = 0;   /* wgsl:194 */
     uint32_t ptr = 0;  /* wgsl:195 */
     const uint32_t *w = sc->words;
+    float pos_stack[RMO_POS_STACK_MAX][3]; /* N4: saved evaluation points */
+    uint32_t psp = 0;
     for (uint32_t idx = 0; idx < sc->cmd_count; ++idx) { /* wgsl:197 */
         uint32_t type = w[ptr++];                          /* wgsl:198 */
         float v;
         switch (type) {
+        /* ---- N4 space transforms: no value is pushed; Push saves the evaluation point and
+         * replaces it, Pop restores it (builder.rs:16-23 "1 child, transforms space") ---- */
+        case 200u: { /* TranslationPush [200, tx,ty,tz]: pos = pos - t */
+            float tx = f_bits(w[ptr]), ty = f_bits(w[ptr + 1]), tz = f_bits(w[ptr + 2]);
+            ptr += 3;
+            pos_stack[psp][0] = px; pos_stack[psp][1] = py; pos_stack[psp][2] = pz; ++psp;
+            px = px - tx; py = py - ty; pz = pz - tz;
+            continue;
+        }
+        case 202u: { /* RotationPush [202, m00,m01,m02, m10,m11,m12, m20,m21,m22] (row-major R,
+                      * object -> world): pos = transpose(R) * pos, each row summed left to right */
+            const float *m = (const float *)(const void *)(w + ptr);
+            float M[9];
+            memcpy(M, m, sizeof M);
+            ptr += 9;
+            pos_stack[psp][0] = px; pos_stack[psp][1] = py; pos_stack[psp][2] = pz; ++psp;
+            float x = (M[0] * px + M[3] * py) + M[6] * pz;
+            float y = (M[1] * px + M[4] * py) + M[7] * pz;
+            float z = (M[2] * px + M[5] * py) + M[8] * pz;
+            px = x; py = y; pz = z;
+            continue;
+        }
+        case 204u: { /* ScalePush [204, s]: pos = pos / s (uniform scale, s > 0) */
+            float s = f_bits(w[ptr]);
+            ptr += 1;
+            pos_stack[psp][0] = px; pos_stack[psp][1] = py; pos_stack[psp][2] = pz; ++psp;
+            px = px / s; py = py / s; pz = pz / s;
+            continue;
+        }
+        case 201u: case 203u: /* TranslationPop [201], RotationPop [203]: restore pos */
+            --psp;
+            px = pos_stack[psp][0]; py = pos_stack[psp][1]; pz = pos_stack[psp][2];
+            continue;
+        case 205u: { /* ScalePop [205, s]: restore pos; the child's distance is in scaled units */
+            float s = f_bits(w[ptr]);
+            ptr += 1;
+            --psp;
+            px = pos_stack[psp][0]; py = pos_stack[psp][1]; pz = pos_stack[psp][2];
+            stack[sp - 1] = stack[sp - 1] * s;
+            continue;
+        }
+        case 2u: { /* N4 plane [2, nx,ny,nz, h]: dot(pos, n) + h  (n expected unit length) */
+            float nx = f_bits(w[ptr]), ny = f_bits(w[ptr + 1]), nz = f_bits(w[ptr + 2]);
+            float h = f_bits(w[ptr + 3]);
+            ptr += 4;
+            v = ((px * nx + py * ny) + pz * nz) + h;
+            break;
+        }
         case 0u: { /* sphere — wgsl:229-233 */
             float cx = f_bits(w[ptr]), cy = f_bits(w[ptr + 1]), cz = f_bits(w[ptr + 2]);
             float r = f_bits(w[ptr + 3]);
@@ -155,6 +210,10 @@ static float map_scene(const rmo_scene *sc, float px, float py, float pz) {
 static int validate_program(uint32_t cmd_count, const uint32_t *w, uint32_t n_words) {
     uint32_t ptr = 0;
     int sp = 0;
+    /* N4: open transform groups — opcode of the push, value-stack depth at the push, scale bits */
+    uint32_t g_op[RMO_POS_STACK_MAX], g_s[RMO_POS_STACK_MAX];
+    int g_sp[RMO_POS_STACK_MAX];
+    int psp = 0;
     if (cmd_count == 0) return RMO_OK;
     if (!w) return RMO_E_INVALID_ARG;
     for (uint32_t i = 0; i < cmd_count; ++i) {
@@ -165,18 +224,43 @@ static int validate_program(uint32_t cmd_count, const uint32_t *w, uint32_t n_wo
         switch (t) {
         case 0u: np = 4; pops = 0; break;
         case 1u: np = 6; pops = 0; break;
+        case 2u: np = 4; pops = 0; break;
         case 100u: case 101u: case 102u: np = 0; pops = 2; break;
         case 103u: np = 1; pops = 2; break;
+        case 200u: np = 3; pops = -1; break;
+        case 202u: np = 9; pops = -1; break;
+        case 204u: np = 1; pops = -1; break;
+        case 201u: case 203u: np = 0; pops = -2; break;
+        case 205u: np = 1; pops = -2; break;
         default: return RMO_E_BAD_PROGRAM;
         }
         if (ptr + np > n_words) return RMO_E_BAD_PROGRAM;
+        if (pops == -1) { /* push: opens a group that must produce exactly one value */
+            if (psp >= RMO_POS_STACK_MAX) return RMO_E_BAD_PROGRAM;
+            if (t == 204u) {
+                float s = f_bits(w[ptr]);
+                if (!(s > 0.0f) || s > 3.0e38f) return RMO_E_BAD_PROGRAM;
+            }
+            g_op[psp] = t; g_sp[psp] = sp; g_s[psp] = (t == 204u) ? w[ptr] : 0u;
+            ++psp;
+            ptr += np;
+            continue;
+        }
+        if (pops == -2) { /* pop: closes the innermost group, which must be of the same kind */
+            if (psp == 0 || g_op[psp - 1] + 1u != t || sp != g_sp[psp - 1] + 1) return RMO_E_BAD_PROGRAM;
+            if (t == 205u && w[ptr] != g_s[psp - 1]) return RMO_E_BAD_PROGRAM;
+            --psp;
+            ptr += np;
+            continue;
+        }
         ptr += np;
-        if (sp < pops) return RMO_E_BAD_PROGRAM;
+        /* an operator inside a group may only consume values produced inside it */
+        if (sp - (psp ? g_sp[psp - 1] : 0) < pops) return RMO_E_BAD_PROGRAM;
         sp -= pops;
         sp += 1;
         if (sp > RMO_STACK_MAX) return RMO_E_BAD_PROGRAM;
     }
-    if (sp < 1) return RMO_E_BAD_PROGRAM;
+    if (sp < 1 || psp != 0) return RMO_E_BAD_PROGRAM;
     return RMO_OK;
 }
 

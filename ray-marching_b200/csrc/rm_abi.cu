@@ -163,12 +163,13 @@ const char *rm_strerror(int code) {
         case RM_E_INVALID_ARG: return "invalid argument";
         case RM_E_PROGRAM_TOO_LARGE: return "command buffer larger than capacity";
         case RM_E_BAD_OPCODE: return "unknown command opcode";
-        case RM_E_STACK_OVERFLOW: return "value stack deeper than 32";
-        case RM_E_STACK_UNBALANCED: return "value stack underflow or truncated command stream";
+        case RM_E_STACK_OVERFLOW: return "value stack deeper than 32 (or transform groups nested deeper than 8)";
+        case RM_E_STACK_UNBALANCED: return "value stack underflow, truncated command stream or unbalanced transform group";
         case RM_E_CUDA: return "CUDA error";
         case RM_E_NOT_PREPARED: return "no program/uniforms prepared";
         case RM_E_BAD_PARAM: return "bad command parameter";
         case RM_E_JIT: return "program specialisation failed (NVRTC unavailable, compile error or program too long)";
+        case RM_E_UNSUPPORTED: return "the selected kernel does not run this program";
         default: return "unknown error";
     }
 }
@@ -275,6 +276,9 @@ int rm_prepare(rm_ctx *c, const void *uniforms144, uint32_t cmd_count, const uin
     Program p;
     int rc = decode_program(cmd_count, words, n_words, c->max_words, &p);
     if (rc != RM_OK) return fail(c, rc, rm_strerror(rc));
+    // an extended program (N4) re-establishes the evaluation point whenever the chain of transforms in force changes, so
+    // its instruction stream can be longer than its word stream; the device buffer holds max_words instructions
+    if (p.insns.size() > c->prog_cap) return fail(c, RM_E_PROGRAM_TOO_LARGE, "decoded program is longer than the instruction capacity (rm_create_ex max_words)");
     RM_CUDA(c, cudaSetDevice(c->device));
     // the staging buffer may still be in flight from the previous prepare
     RM_CUDA(c, cudaEventSynchronize(c->upload_done));

@@ -14,6 +14,23 @@
 
 #define RM_FOR_R _Pragma("unroll") for (int r = 0; r < R; ++r)
 
+// The few places that pin an instruction with inline PTX go through these macros.  RM_HOST_CHECK is defined only by
+// tests/hostcheck (a host compile of the interpreters and of generated map_scene code, checked against the oracle
+// without a GPU); the library itself is never built with it.
+#ifndef RM_HOST_CHECK
+#define RM_PTX_SQRT_APPROX(r, a) asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a))
+#define RM_PTX_MIN_ACC(acc, v) asm("min.f32 %0, %0, %1;" : "+f"(acc) : "f"(v))
+#define RM_PTX_MAX_ACC(acc, v) asm("max.f32 %0, %0, %1;" : "+f"(acc) : "f"(v))
+#define RM_PTX_SUB_ACC(acc, v) asm("sub.rn.f32 %0, %0, %1;" : "+f"(acc) : "f"(v))
+#define RM_PTX_FMA_ACC(acc, a, b) asm("fma.rn.f32 %0, %1, %2, %0;" : "+f"(acc) : "f"(a), "f"(b))
+#else
+#define RM_PTX_SQRT_APPROX(r, a) ((r) = sqrtf(a))
+#define RM_PTX_MIN_ACC(acc, v) ((acc) = fminf((acc), (v)))
+#define RM_PTX_MAX_ACC(acc, v) ((acc) = fmaxf((acc), (v)))
+#define RM_PTX_SUB_ACC(acc, v) ((acc) = (acc) - (v))
+#define RM_PTX_FMA_ACC(acc, a, b) ((acc) = fmaf((a), (b), (acc)))
+#endif
+
 namespace rm {
 
 // constants of the shader (SURVEY.md §5 "Config / flags")
@@ -90,7 +107,7 @@ struct Arith<false> {
     static __device__ __forceinline__ float div(float a, float b) { return __fdividef(a, b); }
     static __device__ __forceinline__ float sqrt(float a) {
         float r;
-        asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a));
+        RM_PTX_SQRT_APPROX(r, a);
         return r;
     }
     static __device__ __forceinline__ float mad(float a, float b, float c) { return fmaf(a, b, c); }
@@ -122,6 +139,45 @@ __device__ __forceinline__ float sd_box(float px, float py, float pz, float cx, 
     return A::add(len, fminf(fmaxf(qx, fmaxf(qy, qz)), 0.0f));
 }
 
+// ---- N4 extension (include/rm_b200.h RM_OP_PLANE, RM_OP_*_PUSH; normative order: oracle/rm_oracle.c map_scene) ----
+// plane: ((x*nx + y*ny) + z*nz) + h
+template <bool EX>
+__device__ __forceinline__ float sd_plane(float px, float py, float pz, float nx, float ny, float nz, float h) {
+    using A = Arith<EX>;
+    if (EX) return A::add(A::add(A::add(A::mul(px, nx), A::mul(py, ny)), A::mul(pz, nz)), h);
+    return fmaf(pz, nz, fmaf(py, ny, fmaf(px, nx, h)));
+}
+// TranslationPush: q = b - t
+template <bool EX>
+__device__ __forceinline__ void xf_translate(float bx, float by, float bz, float tx, float ty, float tz, float &qx, float &qy,
+                                             float &qz) {
+    using A = Arith<EX>;
+    qx = A::sub(bx, tx); qy = A::sub(by, ty); qz = A::sub(bz, tz);
+}
+// RotationPush: q = transpose(M) * b, M row-major: qx = (m00*bx + m10*by) + m20*bz ...
+template <bool EX>
+__device__ __forceinline__ void xf_rotate(float bx, float by, float bz, float m00, float m01, float m02, float m10, float m11,
+                                          float m12, float m20, float m21, float m22, float &qx, float &qy, float &qz) {
+    using A = Arith<EX>;
+    if (EX) {
+        const float x = A::add(A::add(A::mul(m00, bx), A::mul(m10, by)), A::mul(m20, bz));
+        const float y = A::add(A::add(A::mul(m01, bx), A::mul(m11, by)), A::mul(m21, bz));
+        const float z = A::add(A::add(A::mul(m02, bx), A::mul(m12, by)), A::mul(m22, bz));
+        qx = x; qy = y; qz = z;
+    } else {
+        const float x = fmaf(m20, bz, fmaf(m10, by, m00 * bx));
+        const float y = fmaf(m21, bz, fmaf(m11, by, m01 * bx));
+        const float z = fmaf(m22, bz, fmaf(m12, by, m02 * bx));
+        qx = x; qy = y; qz = z;
+    }
+}
+// ScalePush: q = b / s (fast mode: b * (1/s), the reciprocal computed once per program on the host)
+template <bool EX>
+__device__ __forceinline__ void xf_scale(float bx, float by, float bz, float s, float inv_s, float &qx, float &qy, float &qz) {
+    if (EX) { qx = __fdiv_rn(bx, s); qy = __fdiv_rn(by, s); qz = __fdiv_rn(bz, s); }
+    else { qx = bx * inv_s; qy = by * inv_s; qz = bz * inv_s; }
+}
+
 // ---- binary operators: a = left operand (deeper stack entry), b = right (top) ----------------
 // X2: h = max(k-|a-b|,0)/k ; min(a,b) - h*h*k*0.25
 // Fast mode uses the algebraically equal h*h*k*0.25 = e*e/(4k) with c4k = 1/(4k) precomputed per
@@ -144,14 +200,14 @@ template <bool EX>
 __device__ __forceinline__ void op_smooth_acc(float &acc, float b, float k, float inv_k, float c4k, bool k_pow2) {
     using A = Arith<EX>;
     const float e = fmaxf(A::sub(k, fabsf(A::sub(acc, b))), 0.0f);
-    asm("min.f32 %0, %0, %1;" : "+f"(acc) : "f"(b));
+    RM_PTX_MIN_ACC(acc, b);
     if (EX) {
         const float h = k_pow2 ? __fmul_rn(e, inv_k) : __fdiv_rn(e, k);
         const float t = __fmul_rn(__fmul_rn(__fmul_rn(h, h), k), 0.25f);
-        asm("sub.rn.f32 %0, %0, %1;" : "+f"(acc) : "f"(t));
+        RM_PTX_SUB_ACC(acc, t);
     } else {
         const float t = -(e * e);
-        asm("fma.rn.f32 %0, %1, %2, %0;" : "+f"(acc) : "f"(t), "f"(c4k));
+        RM_PTX_FMA_ACC(acc, t, c4k);
     }
 }
 template <bool EX>
@@ -166,23 +222,46 @@ __device__ __forceinline__ float combine(uint32_t cb, float a, float b, const fl
 
 // ---- map_scene for one point: the decoded-program interpreter (wgsl:187-203) -----------------
 // prog: decoded instructions (shared or global memory), viewed as float4[3*n].
-template <bool EX>
+// EXT: the program may hold N4 instructions (rm_program.h): the primitives then read the evaluation point q that the
+// XOP_* instructions maintain.  EXT = false compiles to the reference-set interpreter, unchanged.
+template <bool EX, bool EXT = false>
 __device__ __forceinline__ float map_eval1(const float4 *__restrict__ prog, uint32_t n_insn, float max_dist,
                                            float px, float py, float pz) {
     if (n_insn == 0) return max_dist;  // wgsl:189-191
     float acc = 0.0f;
     float spill[RM_STACK_MAX - 1];
+    float qx = px, qy = py, qz = pz;
     for (uint32_t i = 0; i < n_insn; ++i) {
         const float4 q0 = prog[3 * i], q1 = prog[3 * i + 1], q2 = prog[3 * i + 2];
         const uint32_t op = __float_as_uint(q2.y), slot = __float_as_uint(q2.z);
+        if (EXT) {
+            const uint32_t fl = __float_as_uint(q2.w);
+            if (fl & FLAG_ACCMUL) {  // ScalePop
+                acc = Arith<EX>::mul(acc, q0.x);
+                continue;
+            }
+            if (fl & FLAG_XF) {
+                const bool world = (slot & 1u) != 0;  // first step of a chain starts from the ray position
+                const float bx = world ? px : qx, by = world ? py : qy, bz = world ? pz : qz;
+                if (op == XOP_TRANSLATE) xf_translate<EX>(bx, by, bz, q0.x, q0.y, q0.z, qx, qy, qz);
+                else if (op == XOP_ROTATE) xf_rotate<EX>(bx, by, bz, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w, q2.x, qx, qy, qz);
+                else if (op == XOP_SCALE) xf_scale<EX>(bx, by, bz, q0.x, q0.y, qx, qy, qz);
+                else { qx = px; qy = py; qz = pz; }  // XOP_RESET
+                continue;
+            }
+        }
+        const float ex = EXT ? qx : px, ey = EXT ? qy : py, ez = EXT ? qz : pz;
         const bool k_pow2 = (__float_as_uint(q2.w) & FLAG_K_POW2) != 0;
-        const uint32_t src = opcode_src(op), cb = opcode_cb(op);
+        const uint32_t src = EXT ? opcode_src_ext(op) : opcode_src(op), cb = EXT ? opcode_cb_ext(op) : opcode_cb(op);
         float a, b;
         if (src == SRC_SPHERE) {
-            b = sd_sphere<EX>(px, py, pz, q0.x, q0.y, q0.z, q0.w);
+            b = sd_sphere<EX>(ex, ey, ez, q0.x, q0.y, q0.z, q0.w);
             a = acc;
         } else if (src == SRC_BOX) {
-            b = sd_box<EX>(px, py, pz, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y);
+            b = sd_box<EX>(ex, ey, ez, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y);
+            a = acc;
+        } else if (EXT && src == SRC_PLANE) {
+            b = sd_plane<EX>(ex, ey, ez, q0.x, q0.y, q0.z, q0.w);
             a = acc;
         } else {
             b = acc;

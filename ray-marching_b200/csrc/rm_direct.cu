@@ -34,50 +34,61 @@ constexpr int TILE_W_D = RM_DIRECT_TILE_W;
 #ifndef RM_DIRECT_MINB4
 #define RM_DIRECT_MINB4 8
 #endif
+// Extended programs (N4: plane, space transforms) also carry the evaluation point q of every ray (3 R registers) through
+// the interpreter loop; fewer resident blocks keep that out of local memory (ptxas -v: see build.log).  Not yet measured.
+#ifndef RM_DIRECT_MINB8_EXT
+#define RM_DIRECT_MINB8_EXT 5
+#endif
+#ifndef RM_DIRECT_MINB4_EXT
+#define RM_DIRECT_MINB4_EXT 6
+#endif
+constexpr int direct_min_blocks(int R, bool EXT) {
+    return EXT ? (R == 8 ? RM_DIRECT_MINB8_EXT : RM_DIRECT_MINB4_EXT) : (R == 8 ? RM_DIRECT_MINB8 : RM_DIRECT_MINB4);
+}
 
 // map_scene through the decoded-program interpreter (program in shared memory, spill slots in the thread's frame)
-template <bool EX, int R, bool EO>
+template <bool EX, int R, bool EO, bool EXT>
 struct InterpMap {
     const float4 *prog;
     uint32_t n_insn;
     float max_dist;
     float spill[RM_STACK_MAX - 1][R];
     __device__ __forceinline__ void operator()(const float (&px)[R], const float (&py)[R], const float (&pz)[R], float (&s)[R]) {
-        map_evalR<EX, R, EO>(prog, n_insn, max_dist, px, py, pz, s, spill);
+        map_evalR<EX, R, EO, EXT>(prog, n_insn, max_dist, px, py, pz, s, spill);
     }
 };
 
-template <bool EX, int R, bool COUNT, bool EO>
-__global__ void __launch_bounds__(DIRECT_THREADS, (R == 8 ? RM_DIRECT_MINB8 : RM_DIRECT_MINB4))
+template <bool EX, int R, bool COUNT, bool EO, bool EXT>
+__global__ void __launch_bounds__(DIRECT_THREADS, direct_min_blocks(R, EXT))
 k_direct(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ prog_g, uint8_t *__restrict__ dst, size_t pitch,
          unsigned long long *__restrict__ counters) {
     extern __shared__ float4 s_prog[];
     const uint32_t nq = fp.n_insn * 3;
     for (uint32_t i = threadIdx.x; i < nq; i += blockDim.x) s_prog[i] = reinterpret_cast<const float4 *>(prog_g)[i];
     __syncthreads();
-    InterpMap<EX, R, EO> map;
+    InterpMap<EX, R, EO, EXT> map;
     map.prog = s_prog; map.n_insn = fp.n_insn; map.max_dist = fp.max_dist;
     direct_body<EX, R, COUNT, false>(fp, dst, pitch, counters, nullptr, nullptr, map);
 }
 
 // the same kernel with the per-sample AOVs written out (verification: rm_paint_aov)
-template <bool EX, int R>
-__global__ void __launch_bounds__(DIRECT_THREADS, (R == 8 ? RM_DIRECT_MINB8 : RM_DIRECT_MINB4))
+template <bool EX, int R, bool EXT>
+__global__ void __launch_bounds__(DIRECT_THREADS, direct_min_blocks(R, EXT))
 k_direct_aov(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ prog_g, uint8_t *__restrict__ dst, size_t pitch,
              uint8_t *__restrict__ aov_cls, float *__restrict__ aov_t) {
     extern __shared__ float4 s_prog[];
     const uint32_t nq = fp.n_insn * 3;
     for (uint32_t i = threadIdx.x; i < nq; i += blockDim.x) s_prog[i] = reinterpret_cast<const float4 *>(prog_g)[i];
     __syncthreads();
-    InterpMap<EX, R, false> map;
+    InterpMap<EX, R, false, EXT> map;
     map.prog = s_prog; map.n_insn = fp.n_insn; map.max_dist = fp.max_dist;
     direct_body<EX, R, false, true>(fp, dst, pitch, nullptr, aov_cls, aov_t, map);
 }
 
-template <bool EX, int R>
+template <bool EX, int R, bool EXT>
 cudaError_t launch_direct_aov_t(const FrameParams &fp, const RmInsn *prog, uint8_t *dst, size_t pitch, uint8_t *cls, float *t,
                                 cudaStream_t st) {
-    auto kern = k_direct_aov<EX, R>;
+    auto kern = k_direct_aov<EX, R, EXT>;
     const size_t smem = (size_t)fp.n_insn * sizeof(RmInsn);
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
@@ -87,10 +98,10 @@ cudaError_t launch_direct_aov_t(const FrameParams &fp, const RmInsn *prog, uint8
     return cudaGetLastError();
 }
 
-template <bool EX, int R, bool COUNT, bool EO>
+template <bool EX, int R, bool COUNT, bool EO, bool EXT>
 cudaError_t launch_direct_t(const FrameParams &fp, const RmInsn *prog, uint8_t *dst, size_t pitch,
                             unsigned long long *counters, cudaStream_t st) {
-    auto kern = k_direct<EX, R, COUNT, EO>;
+    auto kern = k_direct<EX, R, COUNT, EO, EXT>;
     constexpr uint32_t tile_h = direct_tile_rows(R);
     const size_t smem = (size_t)fp.n_insn * sizeof(RmInsn);
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -104,22 +115,27 @@ cudaError_t launch_direct_t(const FrameParams &fp, const RmInsn *prog, uint8_t *
 
 static int direct_rays_per_thread(const FrameParams &fp);
 
-cudaError_t launch_direct_aov(bool exact, const FrameParams &fp, const RmInsn *prog_dev, uint8_t *dst, size_t pitch, uint8_t *cls,
-                              float *t, cudaStream_t st) {
+cudaError_t launch_direct_aov(bool exact, bool extended, const FrameParams &fp, const RmInsn *prog_dev, uint8_t *dst, size_t pitch,
+                              uint8_t *cls, float *t, cudaStream_t st) {
     if (fp.nrows == 0 || fp.W == 0) return cudaSuccess;
     const int kR = direct_rays_per_thread(fp);
-    if (exact) return kR == 8 ? launch_direct_aov_t<true, 8>(fp, prog_dev, dst, pitch, cls, t, st) : launch_direct_aov_t<true, 4>(fp, prog_dev, dst, pitch, cls, t, st);
-    return kR == 8 ? launch_direct_aov_t<false, 8>(fp, prog_dev, dst, pitch, cls, t, st) : launch_direct_aov_t<false, 4>(fp, prog_dev, dst, pitch, cls, t, st);
+#define RM_AOV_DISPATCH(EXV, RV) \
+    (extended ? launch_direct_aov_t<EXV, RV, true>(fp, prog_dev, dst, pitch, cls, t, st) : launch_direct_aov_t<EXV, RV, false>(fp, prog_dev, dst, pitch, cls, t, st))
+    if (exact) return kR == 8 ? RM_AOV_DISPATCH(true, 8) : RM_AOV_DISPATCH(true, 4);
+    return kR == 8 ? RM_AOV_DISPATCH(false, 8) : RM_AOV_DISPATCH(false, 4);
+#undef RM_AOV_DISPATCH
 }
 
-cudaError_t launch_direct(bool exact, bool early_out, const FrameParams &fp, const RmInsn *prog_dev, uint8_t *dst, size_t pitch,
-                          unsigned long long *counters, cudaStream_t st) {
+cudaError_t launch_direct(bool exact, bool early_out, bool extended, const FrameParams &fp, const RmInsn *prog_dev, uint8_t *dst,
+                          size_t pitch, unsigned long long *counters, cudaStream_t st) {
     if (fp.nrows == 0 || fp.W == 0) return cudaSuccess;
     const int kR = direct_rays_per_thread(fp);
-#define RM_DIRECT_DISPATCH2(EXV, RV, EOV)                                                      \
-    (counters ? launch_direct_t<EXV, RV, true, EOV>(fp, prog_dev, dst, pitch, counters, st)     \
-              : launch_direct_t<EXV, RV, false, EOV>(fp, prog_dev, dst, pitch, counters, st))
-#define RM_DIRECT_DISPATCH(EXV, RV) (early_out ? RM_DIRECT_DISPATCH2(EXV, RV, true) : RM_DIRECT_DISPATCH2(EXV, RV, false))
+#define RM_DIRECT_DISPATCH2(EXV, RV, EOV, EXTV)                                                      \
+    (counters ? launch_direct_t<EXV, RV, true, EOV, EXTV>(fp, prog_dev, dst, pitch, counters, st)     \
+              : launch_direct_t<EXV, RV, false, EOV, EXTV>(fp, prog_dev, dst, pitch, counters, st))
+    // extended programs (N4) run the EXT interpreter; the early-out is written for the reference instruction set only
+#define RM_DIRECT_DISPATCH(EXV, RV) \
+    (extended ? RM_DIRECT_DISPATCH2(EXV, RV, false, true) : (early_out ? RM_DIRECT_DISPATCH2(EXV, RV, true, false) : RM_DIRECT_DISPATCH2(EXV, RV, false, false)))
     if (exact) return kR == 8 ? RM_DIRECT_DISPATCH(true, 8) : RM_DIRECT_DISPATCH(true, 4);
     return kR == 8 ? RM_DIRECT_DISPATCH(false, 8) : RM_DIRECT_DISPATCH(false, 4);
 #undef RM_DIRECT_DISPATCH2

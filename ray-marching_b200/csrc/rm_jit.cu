@@ -36,6 +36,9 @@ constexpr int kNumHeaders = (int)(sizeof(kHeaders) / sizeof(kHeaders[0]));
 // code of the S0/S1/S2 scenes: sphere 3 FADD + FMUL + 2 FFMA + MUFU + FADD, box 6 FADD + 5 FMNMX + FMUL + 2 FFMA + MUFU
 // + FADD, smooth union 2 FADD + 2 FMNMX + FMUL + FFMA) and the instruction-cache budget it is checked against ----
 constexpr uint32_t kInsnSphere = 8, kInsnBox = 17, kInsnMinMax = 1, kInsnSmooth = 6;
+// N4 commands, counted from their device functions (not yet measured): plane 3 FFMA + FMUL-free, translation 3 FADD,
+// rotation 3 FMUL + 6 FFMA, scale 3 FMUL (push) + 1 FMUL (pop)
+constexpr uint32_t kInsnPlane = 3, kInsnTranslate = 3, kInsnRotate = 9, kInsnScalePush = 3, kInsnScalePop = 1;
 constexpr uint32_t kBytesPerInsn = 16;
 constexpr uint32_t kLoopBudget4 = 24u << 10;  // 4 rays per thread while the march loop's map code stays under this
 constexpr uint32_t kLoopBudget2 = 40u << 10;  // 2 rays per thread up to here; beyond it the interpreter is the better kernel
@@ -142,27 +145,75 @@ int spec_generate_source(uint32_t cmd_count, const uint32_t *words, uint32_t n_w
     // walk the postfix stream (builder.rs:26-62) with a stack of SSA value numbers: command i defines v<i>
     std::string body;
     std::vector<uint32_t> stack;
+    // N4: the evaluation point is an SSA value too — a Push defines q<i>x/y/z from the point in force, the Pop goes back
+    // to the previous names.  The root point is the functor's argument (px, py, pz).
+    struct Pos { std::string x, y, z; uint32_t push_op, s_bits; size_t depth; };
+    std::vector<Pos> pos = {Pos{"px", "py", "pz", 0, 0, 0}};
     uint32_t ptr = 0, est = 0;
     auto need = [&](uint32_t n) { return ptr + n <= n_words; };
+    auto at = [&]() { return pos.back().x + "[r], " + pos.back().y + "[r], " + pos.back().z + "[r]"; };
     for (uint32_t i = 0; i < cmd_count; ++i) {
         if (!need(1)) { if (err) *err = "truncated command stream"; return RM_E_STACK_UNBALANCED; }
         const uint32_t op = words[ptr++];
         std::string e;
         if (op == RM_OP_SPHERE) {
             if (!need(4)) { if (err) *err = "truncated sphere"; return RM_E_STACK_UNBALANCED; }
-            e = "sd_sphere<EX>(px[r], py[r], pz[r], " + lit(words[ptr]) + ", " + lit(words[ptr + 1]) + ", " + lit(words[ptr + 2]) +
+            e = "sd_sphere<EX>(" + at() + ", " + lit(words[ptr]) + ", " + lit(words[ptr + 1]) + ", " + lit(words[ptr + 2]) +
                 ", " + lit(words[ptr + 3]) + ")";
             ptr += 4; est += kInsnSphere;
             stack.push_back(i);
         } else if (op == RM_OP_BOX) {
             if (!need(6)) { if (err) *err = "truncated box"; return RM_E_STACK_UNBALANCED; }
-            e = "sd_box<EX>(px[r], py[r], pz[r]";
+            e = "sd_box<EX>(" + at();
             for (int j = 0; j < 6; ++j) e += ", " + lit(words[ptr + j]);
             e += ")";
             ptr += 6; est += kInsnBox;
             stack.push_back(i);
+        } else if (op == RM_OP_PLANE) {
+            if (!need(4)) { if (err) *err = "truncated plane"; return RM_E_STACK_UNBALANCED; }
+            e = "sd_plane<EX>(" + at();
+            for (int j = 0; j < 4; ++j) e += ", " + lit(words[ptr + j]);
+            e += ")";
+            ptr += 4; est += kInsnPlane;
+            stack.push_back(i);
+        } else if (op == RM_OP_TRANSLATION_PUSH || op == RM_OP_ROTATION_PUSH || op == RM_OP_SCALE_PUSH) {
+            const uint32_t np = op == RM_OP_TRANSLATION_PUSH ? 3u : (op == RM_OP_ROTATION_PUSH ? 9u : 1u);
+            if (!need(np)) { if (err) *err = "truncated transform"; return RM_E_STACK_UNBALANCED; }
+            if (pos.size() > RM_POS_STACK_MAX) { if (err) *err = "transform groups nested deeper than 8"; return RM_E_STACK_OVERFLOW; }
+            const std::string q = "q" + std::to_string(i);
+            std::string call;
+            if (op == RM_OP_TRANSLATION_PUSH) { call = "xf_translate<EX>(" + at(); est += kInsnTranslate; }
+            else if (op == RM_OP_ROTATION_PUSH) { call = "xf_rotate<EX>(" + at(); est += kInsnRotate; }
+            else {
+                const float sc = as_f32(words[ptr]);
+                if (!(sc > 0.0f) || sc > 3.0e38f) { if (err) *err = "scale must be finite and > 0"; return RM_E_BAD_PARAM; }
+                call = "xf_scale<EX>(" + at() + ", " + lit(words[ptr]) + ", " + lit(as_u32(1.0f / sc));
+                est += kInsnScalePush;
+            }
+            if (op != RM_OP_SCALE_PUSH) for (uint32_t j = 0; j < np; ++j) call += ", " + lit(words[ptr + j]);
+            call += ", " + q + "x[r], " + q + "y[r], " + q + "z[r])";
+            body += "        float " + q + "x[R], " + q + "y[R], " + q + "z[R];\n        RM_FOR_R " + call + ";\n";
+            pos.push_back(Pos{q + "x", q + "y", q + "z", op, words[ptr], stack.size()});
+            ptr += np;
+            continue;
+        } else if (op == RM_OP_TRANSLATION_POP || op == RM_OP_ROTATION_POP || op == RM_OP_SCALE_POP) {
+            if (pos.size() < 2 || pos.back().push_op + 1u != op || stack.size() != pos.back().depth + 1) {
+                if (err) *err = "unbalanced transform group";
+                return RM_E_STACK_UNBALANCED;
+            }
+            if (op == RM_OP_SCALE_POP) {
+                if (!need(1)) { if (err) *err = "truncated scale pop"; return RM_E_STACK_UNBALANCED; }
+                if (words[ptr] != pos.back().s_bits) { if (err) *err = "ScalePop factor differs from its push"; return RM_E_BAD_PARAM; }
+                // the child's distance back in the parent's units: a new SSA value replaces the top of the stack
+                const std::string top = var(stack.back()) + "[r]";
+                body += "        float " + var(i) + "[R];\n        RM_FOR_R " + var(i) + "[r] = Arith<EX>::mul(" + top + ", " + lit(words[ptr]) + ");\n";
+                stack.back() = i;
+                ptr += 1; est += kInsnScalePop;
+            }
+            pos.pop_back();
+            continue;
         } else if (op == RM_OP_UNION || op == RM_OP_SUBTRACTION || op == RM_OP_INTERSECTION || op == RM_OP_SMOOTH_UNION) {
-            if (stack.size() < 2) { if (err) *err = "value stack underflow"; return RM_E_STACK_UNBALANCED; }
+            if (stack.size() < 2 + pos.back().depth) { if (err) *err = "value stack underflow"; return RM_E_STACK_UNBALANCED; }
             const std::string b = var(stack.back()) + "[r]";  // b = pop, a = pop  (wgsl:243-244)
             stack.pop_back();
             const std::string a = var(stack.back()) + "[r]";
@@ -189,7 +240,7 @@ int spec_generate_source(uint32_t cmd_count, const uint32_t *words, uint32_t n_w
         if (stack.size() > RM_STACK_MAX) { if (err) *err = "value stack deeper than 32"; return RM_E_STACK_OVERFLOW; }
         body += "        float " + var(i) + "[R];\n        RM_FOR_R " + var(i) + "[r] = " + e + ";\n";
     }
-    if (cmd_count != 0 && stack.size() != 1) { if (err) *err = "value stack does not end with one value"; return RM_E_STACK_UNBALANCED; }
+    if (cmd_count != 0 && (stack.size() != 1 || pos.size() != 1)) { if (err) *err = "value stack does not end with one value"; return RM_E_STACK_UNBALANCED; }
 
     // rays per thread from the code-size estimate: the march loop's copy of map_scene has to stay in the instruction cache
     if (R == 0) R = env_int("RM_SPEC_R");

@@ -10,7 +10,7 @@ namespace {
 constexpr int kSimpleThreads = 128;
 
 // March one ray exactly as ray_march (wgsl:87-131).  Returns the sample code (see rm_kernels.h).
-template <bool EX>
+template <bool EX, bool EXT>
 __device__ __forceinline__ float march_one(const FrameParams &fp, const float4 *prog, const float ro[3],
                                            const float rd[3], int &cls, float &t_out, uint32_t &n_step) {
     using A = Arith<EX>;
@@ -19,15 +19,15 @@ __device__ __forceinline__ float march_one(const FrameParams &fp, const float4 *
     for (uint32_t it = 0; it < fp.max_iter; ++it) {  // wgsl:90
         const float px = A::mad(rd[0], dist, ro[0]), py = A::mad(rd[1], dist, ro[1]),
                     pz = A::mad(rd[2], dist, ro[2]);  // wgsl:91
-        const float s = map_eval1<EX>(prog, fp.n_insn, fp.max_dist, px, py, pz);  // wgsl:94
+        const float s = map_eval1<EX, EXT>(prog, fp.n_insn, fp.max_dist, px, py, pz);  // wgsl:94
         ++n_step;
         if (s < fp.min_dist) {  // wgsl:97
             // calculate_normal wgsl:135-144: taps (+,-,-) (-,-,+) (-,+,-) (+,+,+)
             const float e = RM_NORMAL_EPS;
-            const float m0 = map_eval1<EX>(prog, fp.n_insn, fp.max_dist, __fadd_rn(px, e), __fadd_rn(py, -e), __fadd_rn(pz, -e));
-            const float m1 = map_eval1<EX>(prog, fp.n_insn, fp.max_dist, __fadd_rn(px, -e), __fadd_rn(py, -e), __fadd_rn(pz, e));
-            const float m2 = map_eval1<EX>(prog, fp.n_insn, fp.max_dist, __fadd_rn(px, -e), __fadd_rn(py, e), __fadd_rn(pz, -e));
-            const float m3 = map_eval1<EX>(prog, fp.n_insn, fp.max_dist, __fadd_rn(px, e), __fadd_rn(py, e), __fadd_rn(pz, e));
+            const float m0 = map_eval1<EX, EXT>(prog, fp.n_insn, fp.max_dist, __fadd_rn(px, e), __fadd_rn(py, -e), __fadd_rn(pz, -e));
+            const float m1 = map_eval1<EX, EXT>(prog, fp.n_insn, fp.max_dist, __fadd_rn(px, -e), __fadd_rn(py, -e), __fadd_rn(pz, e));
+            const float m2 = map_eval1<EX, EXT>(prog, fp.n_insn, fp.max_dist, __fadd_rn(px, -e), __fadd_rn(py, e), __fadd_rn(pz, -e));
+            const float m3 = map_eval1<EX, EXT>(prog, fp.n_insn, fp.max_dist, __fadd_rn(px, e), __fadd_rn(py, e), __fadd_rn(pz, e));
             const float nx = A::add(A::add(A::add(m0, -m1), -m2), m3);
             const float ny = A::add(A::add(A::add(-m0, -m1), m2), m3);
             const float nz = A::add(A::add(A::add(-m0, m1), -m2), m3);
@@ -44,7 +44,7 @@ __device__ __forceinline__ float march_one(const FrameParams &fp, const float4 *
     return c[0] > 0.2f ? RM_CODE_FLOOR_LIGHT : RM_CODE_FLOOR_DARK;
 }
 
-template <bool EX>
+template <bool EX, bool EXT>
 __global__ void __launch_bounds__(kSimpleThreads)
 k_samples_simple(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ prog_g, float *__restrict__ codes,
                  DebugOut dbg) {
@@ -62,7 +62,7 @@ k_samples_simple(const __grid_constant__ FrameParams fp, const RmInsn *__restric
         const uint32_t px = (uint32_t)(pix % fp.W), py = frame_row(fp, (uint32_t)(pix / fp.W));
         float ro[3], rd[3], t;
         gen_ray<EX>(fp, px, py, sample, ro, rd);
-        const float code = march_one<EX>(fp, s_prog, ro, rd, cls, t, n_step);
+        const float code = march_one<EX, EXT>(fp, s_prog, ro, rd, cls, t, n_step);
         codes[idx] = code;
         if (dbg.cls) dbg.cls[idx] = (uint8_t)cls;
         if (dbg.t) dbg.t[idx] = t;
@@ -102,7 +102,7 @@ k_resolve(const __grid_constant__ FrameParams fp, const float *__restrict__ code
     *reinterpret_cast<uint32_t *>(dst + (size_t)dst_row(fp, y) * pitch + (size_t)x * 4) = resolve_pixel(c);
 }
 
-template <bool EX>
+template <bool EX, bool EXT>
 __global__ void __launch_bounds__(kSimpleThreads)
 k_map(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ prog_g, const float *__restrict__ pts,
       unsigned long long n, float *__restrict__ out) {
@@ -111,7 +111,7 @@ k_map(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ prog_g,
     for (uint32_t i = threadIdx.x; i < nq; i += blockDim.x) s_prog[i] = reinterpret_cast<const float4 *>(prog_g)[i];
     __syncthreads();
     const unsigned long long idx = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx < n) out[idx] = map_eval1<EX>(s_prog, fp.n_insn, fp.max_dist, pts[3 * idx], pts[3 * idx + 1], pts[3 * idx + 2]);
+    if (idx < n) out[idx] = map_eval1<EX, EXT>(s_prog, fp.n_insn, fp.max_dist, pts[3 * idx], pts[3 * idx + 1], pts[3 * idx + 2]);
 }
 
 __global__ void __launch_bounds__(256) k_ffma_probe(int iters, float *sink) {
@@ -137,7 +137,7 @@ cudaError_t set_smem(K kernel, size_t bytes) {
 
 }  // namespace
 
-cudaError_t launch_samples_simple(bool exact, const FrameParams &fp, const RmInsn *prog_dev, float *codes_dev,
+cudaError_t launch_samples_simple(bool exact, bool extended, const FrameParams &fp, const RmInsn *prog_dev, float *codes_dev,
                                   DebugOut dbg, cudaStream_t st) {
     const unsigned long long total = (unsigned long long)fp.nrows * fp.W * 16ull;
     if (total == 0) return cudaSuccess;
@@ -145,13 +145,14 @@ cudaError_t launch_samples_simple(bool exact, const FrameParams &fp, const RmIns
     if (blocks > 0x7fffffffull) return cudaErrorInvalidValue;
     const size_t smem = (size_t)fp.n_insn * sizeof(RmInsn);
     cudaError_t e;
-    if (exact) {
-        if ((e = set_smem(k_samples_simple<true>, smem)) != cudaSuccess) return e;
-        k_samples_simple<true><<<(unsigned)blocks, kSimpleThreads, smem, st>>>(fp, prog_dev, codes_dev, dbg);
-    } else {
-        if ((e = set_smem(k_samples_simple<false>, smem)) != cudaSuccess) return e;
-        k_samples_simple<false><<<(unsigned)blocks, kSimpleThreads, smem, st>>>(fp, prog_dev, codes_dev, dbg);
-    }
+#define RM_SIMPLE_LAUNCH(EXV, EXTV)                                                                    \
+    do {                                                                                               \
+        if ((e = set_smem(k_samples_simple<EXV, EXTV>, smem)) != cudaSuccess) return e;                \
+        k_samples_simple<EXV, EXTV><<<(unsigned)blocks, kSimpleThreads, smem, st>>>(fp, prog_dev, codes_dev, dbg); \
+    } while (0)
+    if (exact) { if (extended) RM_SIMPLE_LAUNCH(true, true); else RM_SIMPLE_LAUNCH(true, false); }
+    else { if (extended) RM_SIMPLE_LAUNCH(false, true); else RM_SIMPLE_LAUNCH(false, false); }
+#undef RM_SIMPLE_LAUNCH
     return cudaGetLastError();
 }
 
@@ -162,19 +163,20 @@ cudaError_t launch_resolve(const FrameParams &fp, const float *codes_dev, uint8_
     return cudaGetLastError();
 }
 
-cudaError_t launch_map(bool exact, const FrameParams &fp, const RmInsn *prog_dev, const float *pts_dev,
+cudaError_t launch_map(bool exact, bool extended, const FrameParams &fp, const RmInsn *prog_dev, const float *pts_dev,
                        unsigned long long n, float *out_dev, cudaStream_t st) {
     if (n == 0) return cudaSuccess;
     const size_t smem = (size_t)fp.n_insn * sizeof(RmInsn);
     const unsigned blocks = (unsigned)((n + kSimpleThreads - 1) / kSimpleThreads);
     cudaError_t e;
-    if (exact) {
-        if ((e = set_smem(k_map<true>, smem)) != cudaSuccess) return e;
-        k_map<true><<<blocks, kSimpleThreads, smem, st>>>(fp, prog_dev, pts_dev, n, out_dev);
-    } else {
-        if ((e = set_smem(k_map<false>, smem)) != cudaSuccess) return e;
-        k_map<false><<<blocks, kSimpleThreads, smem, st>>>(fp, prog_dev, pts_dev, n, out_dev);
-    }
+#define RM_MAP_LAUNCH(EXV, EXTV)                                                              \
+    do {                                                                                      \
+        if ((e = set_smem(k_map<EXV, EXTV>, smem)) != cudaSuccess) return e;                  \
+        k_map<EXV, EXTV><<<blocks, kSimpleThreads, smem, st>>>(fp, prog_dev, pts_dev, n, out_dev); \
+    } while (0)
+    if (exact) { if (extended) RM_MAP_LAUNCH(true, true); else RM_MAP_LAUNCH(true, false); }
+    else { if (extended) RM_MAP_LAUNCH(false, true); else RM_MAP_LAUNCH(false, false); }
+#undef RM_MAP_LAUNCH
     return cudaGetLastError();
 }
 

@@ -2,6 +2,7 @@
 #include "rm_program.h"
 
 #include <cmath>
+#include <algorithm>
 #include <cstring>
 
 #include "../../include/rm_b200.h"
@@ -16,11 +17,15 @@ inline float as_f32(uint32_t u) {
 }
 struct Cmd {
     uint32_t type;
-    float p[6];
+    float p[9];
+    uint32_t bits0;  // first parameter word as sent (ScalePop must repeat ScalePush's s bit for bit)
 };
 inline bool is_binary(uint32_t t) {
     return t == RM_OP_UNION || t == RM_OP_SUBTRACTION || t == RM_OP_INTERSECTION || t == RM_OP_SMOOTH_UNION;
 }
+inline bool is_primitive(uint32_t t) { return t == RM_OP_SPHERE || t == RM_OP_BOX || t == RM_OP_PLANE; }
+inline bool is_xf_push(uint32_t t) { return t == RM_OP_TRANSLATION_PUSH || t == RM_OP_ROTATION_PUSH || t == RM_OP_SCALE_PUSH; }
+inline bool is_xf_pop(uint32_t t) { return t == RM_OP_TRANSLATION_POP || t == RM_OP_ROTATION_POP || t == RM_OP_SCALE_POP; }
 inline uint32_t combine_of(uint32_t t) {
     switch (t) {
         case RM_OP_UNION: return CB_UNION;
@@ -46,6 +51,135 @@ void smooth_constants(float k, float *inv_k, float *c4k, bool *k_pow2) {
     *k_pow2 = m == 0.5f && std::fpclassify(k) == FP_NORMAL && std::fpclassify(*inv_k) == FP_NORMAL;
 }
 
+namespace {
+
+void finish_flags(RmInsn &in) {
+    const uint32_t src = opcode_src_ext(in.op), cb = opcode_cb_ext(in.op);
+    static const uint32_t cb_flag[6] = {FLAG_FIRST, FLAG_PUSH, FLAG_UNION, FLAG_SUB, FLAG_INTER, FLAG_SMOOTH};
+    in.flags |= cb_flag[cb] | (src == SRC_BOX ? FLAG_BOX : 0u) | (src == SRC_POP ? FLAG_POP : 0u) | (src == SRC_PLANE ? FLAG_PLANE : 0u);
+}
+
+// Programs with N4 commands (see rm_program.h).  `cmds` is the parsed stream; counts and `extended` are set in `prog`.
+int lower_extended(const std::vector<Cmd> &cmds, Program &prog, Program *out) {
+    const uint32_t n = (uint32_t)cmds.size();
+    // pass 2a: value-stack and group discipline, command by command as the sequential semantics would run
+    // (same rules as oracle/rm_oracle.c validate_program)
+    struct Group { uint32_t type, depth, s_bits; };
+    std::vector<Group> groups;
+    uint32_t depth = 0, max_depth = 0;
+    for (uint32_t i = 0; i < n; ++i) {
+        const Cmd &c = cmds[i];
+        if (is_xf_push(c.type)) {
+            if (groups.size() >= RM_POS_STACK_MAX) return RM_E_STACK_OVERFLOW;
+            groups.push_back(Group{c.type, depth, c.bits0});
+        } else if (is_xf_pop(c.type)) {
+            // closes the innermost group: same kind, and exactly one value was produced inside it
+            if (groups.empty() || groups.back().type + 1u != c.type || depth != groups.back().depth + 1u) return RM_E_STACK_UNBALANCED;
+            if (c.type == RM_OP_SCALE_POP && c.bits0 != groups.back().s_bits) return RM_E_BAD_PARAM;
+            groups.pop_back();
+        } else if (is_binary(c.type)) {
+            // an operator inside a group may only consume values produced inside it
+            if (depth - (groups.empty() ? 0u : groups.back().depth) < 2u) return RM_E_STACK_UNBALANCED;
+            depth -= 1;
+        } else {
+            if (depth + 1 > RM_STACK_MAX) return RM_E_STACK_OVERFLOW;
+            depth += 1;
+            if (depth > max_depth) max_depth = depth;
+        }
+    }
+    if (depth < 1 || !groups.empty()) return RM_E_STACK_UNBALANCED;
+
+    // pass 2b: resolve the position stack.  Value commands keep their order; every primitive gets the chain of push
+    // commands in force (indices into cmds, outermost first); T/R pops vanish, ScalePop becomes acc *= s.
+    struct VCmd { uint32_t cmd; bool accmul; std::vector<uint32_t> chain; };
+    std::vector<VCmd> v;
+    std::vector<uint32_t> open;
+    for (uint32_t i = 0; i < n; ++i) {
+        const Cmd &c = cmds[i];
+        if (is_xf_push(c.type)) open.push_back(i);
+        else if (is_xf_pop(c.type)) {
+            open.pop_back();
+            if (c.type == RM_OP_SCALE_POP) v.push_back(VCmd{i, true, {}});
+        } else v.push_back(VCmd{i, false, is_primitive(c.type) ? open : std::vector<uint32_t>()});
+    }
+
+    // pass 2c: emission — the reference-set algorithm (top of stack in the accumulator, primitive + operator fused)
+    // plus "set the evaluation point" instructions whenever the chain in force changes
+    std::vector<uint32_t> cur;  // chain whose result q holds (empty: q == p, the state at the start of every evaluation)
+    auto emit_chain = [&](const std::vector<uint32_t> &chain) {
+        if (chain == cur) return;
+        if (chain.empty()) {
+            RmInsn in{};
+            in.op = XOP_RESET; in.flags = FLAG_XF; in.slot = 1;
+            prog.insns.push_back(in);
+        } else {
+            size_t start = 0;  // a chain that extends the current one continues from q
+            if (!cur.empty() && cur.size() < chain.size() && std::equal(cur.begin(), cur.end(), chain.begin())) start = cur.size();
+            for (size_t k = start; k < chain.size(); ++k) {
+                const Cmd &p = cmds[chain[k]];
+                RmInsn in{};
+                in.flags = FLAG_XF;
+                in.slot = k == 0 ? 1u : 0u;  // bit 0: base = p
+                if (p.type == RM_OP_TRANSLATION_PUSH) {
+                    in.op = XOP_TRANSLATE; in.cx = p.p[0]; in.cy = p.p[1]; in.cz = p.p[2];
+                } else if (p.type == RM_OP_ROTATION_PUSH) {
+                    in.op = XOP_ROTATE;
+                    in.cx = p.p[0]; in.cy = p.p[1]; in.cz = p.p[2]; in.r0 = p.p[3]; in.r1 = p.p[4]; in.r2 = p.p[5];
+                    in.k = p.p[6]; in.inv_k = p.p[7]; in.c4k = p.p[8];
+                } else {
+                    in.op = XOP_SCALE; in.cx = p.p[0]; in.cy = 1.0f / p.p[0];
+                }
+                prog.insns.push_back(in);
+            }
+        }
+        cur = chain;
+    };
+    depth = 0;
+    const uint32_t nv = (uint32_t)v.size();
+    for (uint32_t i = 0; i < nv; ++i) {
+        const Cmd &c = cmds[v[i].cmd];
+        RmInsn in{};
+        if (v[i].accmul) {
+            in.op = XOP_ACCMUL; in.flags = FLAG_ACCMUL; in.cx = c.p[0];
+            prog.insns.push_back(in);
+            continue;
+        }
+        if (!is_binary(c.type)) {
+            emit_chain(v[i].chain);
+            in.cx = c.p[0]; in.cy = c.p[1]; in.cz = c.p[2]; in.r0 = c.p[3];
+            uint32_t src = c.type == RM_OP_SPHERE ? SRC_SPHERE : (c.type == RM_OP_BOX ? SRC_BOX : SRC_PLANE);
+            if (c.type == RM_OP_BOX) { in.r1 = c.p[4]; in.r2 = c.p[5]; }
+            if (depth >= 1 && i + 1 < nv && !v[i + 1].accmul && is_binary(cmds[v[i + 1].cmd].type)) {
+                const Cmd &o = cmds[v[i + 1].cmd];  // fused: acc = op(acc, prim); T/R pops in between change nothing
+                in.op = opcode(src, combine_of(o.type));
+                if (o.type == RM_OP_SMOOTH_UNION) set_k(in, o.p[0]);
+                ++i;
+            } else if (depth == 0) {
+                in.op = opcode(src, CB_FIRST);
+                depth = 1;
+            } else {
+                in.op = opcode(src, CB_PUSH);
+                in.slot = depth - 1;
+                depth += 1;
+            }
+        } else {
+            in.op = opcode(SRC_POP, combine_of(c.type));
+            in.slot = depth - 2;
+            if (c.type == RM_OP_SMOOTH_UNION) set_k(in, c.p[0]);
+            depth -= 1;
+        }
+        finish_flags(in);
+        prog.insns.push_back(in);
+    }
+    prog.cmd_count = n;
+    prog.max_depth = max_depth;
+    prog.n_spill = max_depth > 0 ? max_depth - 1 : 0;
+    if (out) *out = std::move(prog);
+    return RM_OK;
+}
+
+}  // namespace
+
 int decode_program(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, uint32_t max_words,
                    Program *out) {
     if (out) *out = Program();
@@ -70,14 +204,23 @@ int decode_program(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, 
             case RM_OP_SUBTRACTION: prog.n_sub++; break;
             case RM_OP_INTERSECTION: prog.n_inter++; break;
             case RM_OP_SMOOTH_UNION: np = 1; prog.n_smooth++; break;
+            case RM_OP_PLANE: np = 4; prog.n_plane++; prog.extended = true; break;
+            case RM_OP_TRANSLATION_PUSH: np = 3; prog.n_translate++; prog.extended = true; break;
+            case RM_OP_ROTATION_PUSH: np = 9; prog.n_rotate++; prog.extended = true; break;
+            case RM_OP_SCALE_PUSH: np = 1; prog.n_scale++; prog.extended = true; break;
+            case RM_OP_TRANSLATION_POP: case RM_OP_ROTATION_POP: prog.extended = true; break;
+            case RM_OP_SCALE_POP: np = 1; prog.extended = true; break;
             default: return RM_E_BAD_OPCODE;
         }
         if (ptr + np > n_words) return RM_E_STACK_UNBALANCED;
         for (uint32_t j = 0; j < np; ++j) c.p[j] = as_f32(words[ptr + j]);
+        if (np) c.bits0 = words[ptr];
         ptr += np;
-        if (c.type == RM_OP_SMOOTH_UNION && !(c.p[0] > 0.0f && std::isfinite(c.p[0]))) return RM_E_BAD_PARAM;
+        if ((c.type == RM_OP_SMOOTH_UNION || c.type == RM_OP_SCALE_PUSH) && !(c.p[0] > 0.0f && std::isfinite(c.p[0])))
+            return RM_E_BAD_PARAM;
         cmds.push_back(c);
     }
+    if (prog.extended) return lower_extended(cmds, prog, out);
 
     // pass 2: stack discipline + emission with top-of-stack caching and prim/op fusion
     uint32_t depth = 0, max_depth = 0;

@@ -11,6 +11,15 @@
 //     acc = op(acc, prim(p)), which is the whole program for left-deep chains;
 //   * per-instruction constants that are exact (k*0.25, 1/k when k is a power of two) are
 //     precomputed.  Nothing here changes evaluation order or rounding.
+//
+// N4 extension (include/rm_b200.h: Plane, Translation / Rotation / Scale Push / Pop).  The position stack of the
+// sequential semantics is resolved here too: every primitive knows the chain of transforms in force (outermost first),
+// and the instruction stream carries "set the evaluation point" instructions — q = step(p) for the first step of a
+// chain, q = step(q) for the following ones — emitted only when the chain changes (a chain that extends the previous
+// one only emits the new steps).  Pops emit nothing, except ScalePop: acc = acc * s.  The operations a ray executes on
+// its way to a primitive are therefore exactly those of the push commands enclosing it, in order: same bits as the
+// oracle's position stack.  Programs with such commands are `extended` and run on the kernels' EXT instantiations;
+// all other programs decode exactly as before and run on the unchanged ones.
 #pragma once
 #ifdef __CUDACC_RTC__  // runtime compilation of specialised kernels (rm_jit.cu): no host headers there
 typedef unsigned char uint8_t;
@@ -42,6 +51,15 @@ enum : uint32_t {
     SRC_POP = 0,     // b = acc, a = spill[slot]     (binary op whose right operand is a subtree)
     SRC_SPHERE = 1,  // b = sphere(p), a = acc       wgsl:229-233
     SRC_BOX = 2,     // b = box(p),    a = acc       wgsl:235-240
+    SRC_PLANE = 3,   // b = plane(p),  a = acc       N4 (extended programs only)
+};
+// extended instructions that are not value producers (RmInsn::op; FLAG_XF / FLAG_ACCMUL set)
+enum : uint32_t {
+    XOP_TRANSLATE = 32,  // q = base - (cx,cy,cz)
+    XOP_ROTATE = 33,     // q = transpose(M) * base, M row-major in cx,cy,cz,r0,r1,r2,k,inv_k,c4k
+    XOP_SCALE = 34,      // q = base / cx   (fast mode: base * cy, cy = 1/s)
+    XOP_RESET = 35,      // q = p           (the chain in force became empty)
+    XOP_ACCMUL = 36,     // acc = acc * cx  (ScalePop)
 };
 // RmInsn::flags: one-hot description of the fused op, so that the interpreter dispatches with
 // single-bit tests (LOP3 -> predicate, branch) in frequency order instead of a jump table.
@@ -55,21 +73,28 @@ enum : uint32_t {
     FLAG_INTER = 1u << 6,
     FLAG_PUSH = 1u << 7,
     FLAG_FIRST = 1u << 8,
+    // extended programs only (N4)
+    FLAG_PLANE = 1u << 9,
+    FLAG_XF = 1u << 10,      // XOP_TRANSLATE / ROTATE / SCALE / RESET; slot bit 0: base = p (first step of a chain), else base = q
+    FLAG_ACCMUL = 1u << 11,  // XOP_ACCMUL
 };
 
 // RmInsn::op is a DENSE fused opcode 0..15 so that the interpreter dispatches through a single
 // jump table:  0..3 = POP x {UNION,SUB,INTER,SMOOTH};  4..9 = SPHERE x {FIRST..SMOOTH};
-// 10..15 = BOX x {FIRST..SMOOTH}.
+// 10..15 = BOX x {FIRST..SMOOTH}; extended programs add 16..21 = PLANE x {FIRST..SMOOTH} and the XOP_* values.
 #define RM_HD
 #ifdef __CUDACC__
 #undef RM_HD
 #define RM_HD __host__ __device__
 #endif
 RM_HD constexpr uint32_t opcode(uint32_t src, uint32_t cb) {
-    return src == SRC_POP ? cb - CB_UNION : (src == SRC_SPHERE ? 4u + cb : 10u + cb);
+    return src == SRC_POP ? cb - CB_UNION : (src == SRC_SPHERE ? 4u + cb : (src == SRC_BOX ? 10u + cb : 16u + cb));
 }
 RM_HD constexpr uint32_t opcode_src(uint32_t op) { return op < 4u ? SRC_POP : (op < 10u ? SRC_SPHERE : SRC_BOX); }
 RM_HD constexpr uint32_t opcode_cb(uint32_t op) { return op < 4u ? op + CB_UNION : (op < 10u ? op - 4u : op - 10u); }
+// the same for extended programs (value-producing instructions only: op < 22)
+RM_HD constexpr uint32_t opcode_src_ext(uint32_t op) { return op < 16u ? opcode_src(op) : SRC_PLANE; }
+RM_HD constexpr uint32_t opcode_cb_ext(uint32_t op) { return op < 16u ? opcode_cb(op) : op - 16u; }
 
 // One decoded instruction = 3 x 16 bytes (three broadcast LDS.128).
 struct alignas(16) RmInsn {
@@ -89,9 +114,14 @@ struct Program {
     uint32_t max_depth = 0;   // value-stack depth of the original program (<= 32)
     uint32_t n_spill = 0;     // spill slots used (= max_depth - 1, or 0)
     uint32_t n_sphere = 0, n_box = 0, n_union = 0, n_sub = 0, n_inter = 0, n_smooth = 0;
-    // algorithmic flops of one map_scene evaluation (SURVEY.md §8(a) FLOP table)
+    // N4: any Plane / transform command present -> the kernels' EXT instantiations run it
+    bool extended = false;
+    uint32_t n_plane = 0, n_translate = 0, n_rotate = 0, n_scale = 0;
+    // algorithmic flops of one map_scene evaluation (SURVEY.md §8(a) FLOP table; N4, counted the same literal way on
+    // the sequential semantics: plane 3 mul + 3 add, translation 3 sub, rotation 9 mul + 6 add, scale 3 div + 1 mul)
     uint32_t flops_per_eval() const {
-        return 10 * n_sphere + 22 * n_box + n_union + 2 * n_sub + n_inter + 10 * n_smooth;
+        return 10 * n_sphere + 22 * n_box + n_union + 2 * n_sub + n_inter + 10 * n_smooth + 6 * n_plane + 3 * n_translate +
+               15 * n_rotate + 4 * n_scale;
     }
 };
 

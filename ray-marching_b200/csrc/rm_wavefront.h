@@ -28,11 +28,12 @@ cudaError_t launch_wavefront2(WavefrontState *ws, bool exact, const FrameParams 
 
 // Shallow-program kernel (rm_direct.cu): 4 sample rays per thread, fused in-order resolve, no queues.
 // early_out: opt-in exact early-out of the interpreter (rm_wavefront_common.cuh), bit-identical output.
-cudaError_t launch_direct(bool exact, bool early_out, const FrameParams &fp, const RmInsn *prog_dev, uint8_t *dst, size_t pitch,
-                          unsigned long long *counters, cudaStream_t st);
+// extended: the program holds N4 instructions (Program::extended) -> EXT interpreter (early_out is then ignored).
+cudaError_t launch_direct(bool exact, bool early_out, bool extended, const FrameParams &fp, const RmInsn *prog_dev, uint8_t *dst,
+                          size_t pitch, unsigned long long *counters, cudaStream_t st);
 
 // The same kernel with the per-sample classes / distances of its own march written out (verification, rm_paint_aov).
-cudaError_t launch_direct_aov(bool exact, const FrameParams &fp, const RmInsn *prog_dev, uint8_t *dst, size_t pitch, uint8_t *cls,
-                              float *t, cudaStream_t st);
+cudaError_t launch_direct_aov(bool exact, bool extended, const FrameParams &fp, const RmInsn *prog_dev, uint8_t *dst, size_t pitch,
+                              uint8_t *cls, float *t, cudaStream_t st);
 
 }  // namespace rm

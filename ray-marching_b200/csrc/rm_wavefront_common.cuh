@@ -53,8 +53,8 @@ __device__ __forceinline__ float prim_eval(float x, float y, float z, const floa
         break;
 
 // acc = min(acc, v) etc. with the accumulator tied to one register (no copies around the loop)
-__device__ __forceinline__ void acc_min(float &acc, float v) { asm("min.f32 %0, %0, %1;" : "+f"(acc) : "f"(v)); }
-__device__ __forceinline__ void acc_max(float &acc, float v) { asm("max.f32 %0, %0, %1;" : "+f"(acc) : "f"(v)); }
+__device__ __forceinline__ void acc_min(float &acc, float v) { RM_PTX_MIN_ACC(acc, v); }
+__device__ __forceinline__ void acc_max(float &acc, float v) { RM_PTX_MAX_ACC(acc, v); }
 
 // Early-out (EO, opt-in, off in every default path): for acc = op(acc, prim(p)) with op in {union, smooth-union,
 // subtraction} the accumulator is provably unchanged — bit for bit, in both arithmetic modes — when a cheap lower bound
@@ -64,21 +64,45 @@ __device__ __forceinline__ void acc_max(float &acc, float v) { asm("max.f32 %0, 
 // If that holds for all R rays of the thread the rest of the instruction is skipped (sqrt, the blend, most of the box).
 // The slack (1e-4) covers the few roundings between the bound and the value for coordinates up to max_dist = 100.
 #define RM_EO_SLACK 1e-4f
-template <bool EX, int R, bool EO = false>
+// EXT (N4, rm_program.h): the program may hold Plane primitives and the XOP_* instructions that maintain the
+// evaluation point q of the R rays; primitives then read q.  EXT = false is the reference-set interpreter, unchanged.
+template <bool EX, int R, bool EO = false, bool EXT = false>
 __device__ __forceinline__ void map_evalR(const float4 *__restrict__ prog, uint32_t n_insn, float max_dist,
                                           const float (&px)[R], const float (&py)[R], const float (&pz)[R],
                                           float (&acc)[R], float (*spill)[R]) {
+    static_assert(!(EO && EXT), "the early-out bounds are written for the reference instruction set");
     if (n_insn == 0) {  // wgsl:189-191
         RM_FOR_R acc[r] = max_dist;
         return;
     }
     RM_FOR_R acc[r] = 0.0f;
+    float qx[R], qy[R], qz[R];  // EXT only: evaluation point in force (starts as the ray position)
+    if (EXT) { RM_FOR_R { qx[r] = px[r]; qy[r] = py[r]; qz[r] = pz[r]; } }
+#define RM_EVX (EXT ? qx[r] : px[r])
+#define RM_EVY (EXT ? qy[r] : py[r])
+#define RM_EVZ (EXT ? qz[r] : pz[r])
     // not unrolled: unrolling by 2 removes the 8 accumulator copies ptxas leaves at the back-edge, but measured
     // slower on B200 (cfg3 48.94 vs 48.64 ms, cfg2 2.77 vs 2.32 ms: larger code, remainder loop) — profiles/r1_s2_NOTES.md
 #pragma unroll 1
     for (uint32_t i = 0; i < n_insn; ++i) {
         const float4 q0 = prog[3 * i], q1 = prog[3 * i + 1], q2 = prog[3 * i + 2];
         const uint32_t fl = __float_as_uint(q2.w);
+        if (EXT && (fl & (FLAG_XF | FLAG_ACCMUL))) {
+            if (fl & FLAG_ACCMUL) {  // ScalePop: the child's distance back in the parent's units
+                RM_FOR_R acc[r] = Arith<EX>::mul(acc[r], q0.x);
+                continue;
+            }
+            const uint32_t xop = __float_as_uint(q2.y);
+            if (__float_as_uint(q2.z) & 1u) { RM_FOR_R { qx[r] = px[r]; qy[r] = py[r]; qz[r] = pz[r]; } }  // chain starts at p
+            if (xop == XOP_TRANSLATE) {
+                RM_FOR_R xf_translate<EX>(qx[r], qy[r], qz[r], q0.x, q0.y, q0.z, qx[r], qy[r], qz[r]);
+            } else if (xop == XOP_ROTATE) {
+                RM_FOR_R xf_rotate<EX>(qx[r], qy[r], qz[r], q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w, q2.x, qx[r], qy[r], qz[r]);
+            } else if (xop == XOP_SCALE) {
+                RM_FOR_R xf_scale<EX>(qx[r], qy[r], qz[r], q0.x, q0.y, qx[r], qy[r], qz[r]);
+            }  // XOP_RESET: the copy above is all of it
+            continue;
+        }
         // Dispatch on one-hot flag bits, most frequent fused ops first (primitive kind, then
         // smooth-union / union / subtraction / intersection / push / first).
         if (!(fl & FLAG_POP)) {
@@ -109,9 +133,11 @@ __device__ __forceinline__ void map_evalR(const float4 *__restrict__ prog, uint3
             }
             float v[R];
             if (fl & FLAG_BOX) {
-                RM_FOR_R v[r] = sd_box<EX>(px[r], py[r], pz[r], q0.x, q0.y, q0.z, q0.w, q1.x, q1.y);
+                RM_FOR_R v[r] = sd_box<EX>(RM_EVX, RM_EVY, RM_EVZ, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y);
+            } else if (EXT && (fl & FLAG_PLANE)) {
+                RM_FOR_R v[r] = sd_plane<EX>(RM_EVX, RM_EVY, RM_EVZ, q0.x, q0.y, q0.z, q0.w);
             } else {
-                RM_FOR_R v[r] = sd_sphere<EX>(px[r], py[r], pz[r], q0.x, q0.y, q0.z, q0.w);
+                RM_FOR_R v[r] = sd_sphere<EX>(RM_EVX, RM_EVY, RM_EVZ, q0.x, q0.y, q0.z, q0.w);
             }
             if (fl & FLAG_SMOOTH) {
                 RM_FOR_R op_smooth_acc<EX>(acc[r], v[r], q1.z, q1.w, q2.x, (fl & FLAG_K_POW2) != 0);
@@ -142,6 +168,9 @@ __device__ __forceinline__ void map_evalR(const float4 *__restrict__ prog, uint3
             }
         }
     }
+#undef RM_EVX
+#undef RM_EVY
+#undef RM_EVZ
 }
 
 // ---- rare per-ray events, kept OUT OF LINE (one copy each) so that the per-iteration instruction

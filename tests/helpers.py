@@ -21,6 +21,10 @@ ORACLE_SO = ORACLE_DIR / "_build" / "librm_oracle.so"
 
 # opcodes — /root/reference/src/ray_marching/csg/builder.rs:1-24 (+ extensions X1/X2)
 OP_SPHERE, OP_BOX, OP_UNION, OP_SUBTRACTION, OP_INTERSECTION, OP_SMOOTH_UNION = 0, 1, 100, 101, 102, 103
+# N4 extension at the values the reference's enum reserves in comments (builder.rs:8,16-23)
+OP_PLANE = 2
+OP_TRANSLATION_PUSH, OP_TRANSLATION_POP, OP_ROTATION_PUSH, OP_ROTATION_POP, OP_SCALE_PUSH, OP_SCALE_POP = 200, 201, 202, 203, 204, 205
+POS_STACK_MAX = 8
 
 DEFAULT_LIMITS = (0.01, 100.0, 100)  # renderer.rs:133-137
 
@@ -145,6 +149,94 @@ def sphere(c, r):
 
 def box(c, r):
     return [OP_BOX, fbits(c[0]), fbits(c[1]), fbits(c[2]), fbits(r[0]), fbits(r[1]), fbits(r[2])]
+
+
+def plane(n, hgt):
+    return [OP_PLANE, fbits(n[0]), fbits(n[1]), fbits(n[2]), fbits(hgt)]
+
+
+def translated(t, child):
+    """(words, cmds) of `child` evaluated in a frame moved by t: Push, child, Pop."""
+    w, c = child
+    return [OP_TRANSLATION_PUSH, fbits(t[0]), fbits(t[1]), fbits(t[2])] + list(w) + [OP_TRANSLATION_POP], c + 2
+
+
+def rotated(R, child):
+    """R: 3x3 rotation matrix (object -> world), sent row-major."""
+    w, c = child
+    R = np.asarray(R, np.float32).reshape(9)
+    return [OP_ROTATION_PUSH] + [fbits(x) for x in R] + list(w) + [OP_ROTATION_POP], c + 2
+
+
+def scaled(sc, child):
+    w, c = child
+    return [OP_SCALE_PUSH, fbits(sc)] + list(w) + [OP_SCALE_POP, fbits(sc)], c + 2
+
+
+def rotation_matrix(axis, angle) -> np.ndarray:
+    """Rodrigues formula in float64, rounded to float32 on use."""
+    a = np.asarray(axis, np.float64)
+    a = a / np.linalg.norm(a)
+    K = np.array([[0, -a[2], a[1]], [a[2], 0, -a[0]], [-a[1], a[0], 0]])
+    return np.eye(3) + math.sin(angle) * K + (1 - math.cos(angle)) * (K @ K)
+
+
+def random_program(rng, n_leaves, right_bias=0.3, ext=False, depth=0):
+    """Random valid postfix program with mixed tree shapes (value-stack depth <= 32).  ext=True also draws N4
+    commands: plane leaves and sub-trees wrapped in translation / rotation / scale groups (nesting <= 8).
+    -> (words, cmd_count)."""
+    def leaf():
+        c = rng.uniform(-2, 2, 3)
+        r = rng.random()
+        if ext and r < 0.15:
+            n = rng.normal(size=3)
+            n = (n / np.linalg.norm(n)).astype(np.float32)
+            return plane(n, rng.uniform(0.5, 2.5)), 1
+        if r < 0.55:
+            return sphere(c, rng.uniform(0.2, 1.0)), 1
+        return box(c, rng.uniform(0.2, 1.0, 3)), 1
+
+    def op():
+        r = rng.random()
+        if r < 0.3:
+            return [OP_UNION]
+        if r < 0.5:
+            return [OP_SUBTRACTION]
+        if r < 0.65:
+            return [OP_INTERSECTION]
+        k = [0.25, 0.5, 0.3, 0.1, 1.0][rng.integers(5)]
+        return [OP_SMOOTH_UNION, fbits(k)]
+
+    def wrap(node, d):
+        r = rng.random()
+        if r < 0.4:
+            return translated(rng.uniform(-1.5, 1.5, 3), node)
+        if r < 0.75:
+            return rotated(rotation_matrix(rng.normal(size=3), rng.uniform(-3.1, 3.1)), node)
+        return scaled([0.5, 2.0, 0.75, 1.3, 3.0][rng.integers(5)], node)
+
+    def tree(n, d):
+        if n == 1:
+            node = leaf()
+        else:
+            nl = 1 if rng.random() > right_bias else int(rng.integers(1, n))
+            nl = n - nl if rng.random() < 0.5 else nl
+            nl = min(max(nl, 1), n - 1)
+            wrap_here = ext and d < POS_STACK_MAX and rng.random() < 0.35
+            dd = d + 1 if wrap_here else d
+            wa, ca = tree(nl, dd)
+            wb, cb = tree(n - nl, dd)
+            node = (wa + wb + op(), ca + cb + 1)
+            if wrap_here:
+                node = wrap(node, d)
+            return node
+        if ext and d < POS_STACK_MAX and rng.random() < 0.35:
+            node = wrap(node, d)
+            if d + 1 < POS_STACK_MAX and rng.random() < 0.3:  # a chain of two transforms around one child
+                node = wrap(node, d + 1)
+        return node
+
+    return tree(n_leaves, depth)
 
 
 def scene_s0():

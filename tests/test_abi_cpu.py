@@ -49,6 +49,15 @@ def test_strerror_covers_codes(rm):
     (h.sphere((0, 0, 0), 1) * 2 + [103, h.fbits(0.0)], 3, -8),
     (h.sphere((0, 0, 0), 1) * 2 + [103, h.fbits(float("nan"))], 3, -8),
     (h.sphere((0, 0, 0), 1) * 2 + [103, h.fbits(0.25)], 3, 0),
+    # N4 (plane, space-transform groups)
+    (h.plane((0, 1, 0), 1.5), 1, 0),
+    (h.translated((1, 2, 3), (h.sphere((0, 0, 0), 1), 1))[0], 3, 0),
+    (h.scaled(2.0, h.rotated(np.eye(3), (h.box((0, 0, 0), (1, 1, 1)), 1)))[0], 5, 0),
+    ([201], 1, -5),
+    ([200, 0, 0, 0] + h.sphere((0, 0, 0), 1) + [203], 3, -5),
+    ([204, h.fbits(2.0)] + h.sphere((0, 0, 0), 1) + [205, h.fbits(4.0)], 3, -8),
+    ([204, h.fbits(-2.0)] + h.sphere((0, 0, 0), 1) + [205, h.fbits(-2.0)], 3, -8),
+    ([200, 0, 0, 0] * 9 + h.sphere((0, 0, 0), 1) + [201] * 9, 19, -4),
 ])
 def test_validate_program_codes(rm, words, count, code):
     assert rm.validate_program(count, words) == code
@@ -56,15 +65,16 @@ def test_validate_program_codes(rm, words, count, code):
 
 def test_validation_agrees_with_oracle_on_random_streams(rm):
     rng = np.random.default_rng(0)
-    ops = [0, 1, 100, 101, 102, 103, 7]
+    ops = [0, 1, 100, 101, 102, 103, 7, 2, 200, 201, 202, 203, 204, 205]
     agree = 0
-    for _ in range(3000):
+    for it in range(6000):
         n = int(rng.integers(1, 12))
         words = []
         for _ in range(n):
-            t = ops[rng.integers(len(ops))]
+            t = ops[rng.integers(7 if it < 3000 else len(ops))]
             words.append(t)
-            words += [h.fbits(rng.uniform(0.1, 1))] * {0: 4, 1: 6, 103: 1}.get(t, 0)
+            words += [h.fbits([0.5, 0.25][rng.integers(2)] if it >= 3000 else rng.uniform(0.1, 1))] * {
+                0: 4, 1: 6, 103: 1, 2: 4, 200: 3, 202: 9, 204: 1, 205: 1}.get(t, 0)
         if rng.random() < 0.1:
             words = words[:-1]
         a = rm.validate_program(n, words) == 0

@@ -94,3 +94,21 @@ def test_generated_source_compiles_for_sm_100a(rm, scene, mode):
         pytest.skip("no libnvrtc in this environment: " + r["log"][:200])
     assert r["rc"] == 0, r["log"]
     assert r["cubin_bytes"] > 10000 and r["compile_ms"] > 0
+
+
+def test_extended_program_generates_position_ssa_and_compiles_for_sm_100a(rm):
+    """N4: the evaluation point is an SSA value too (q<i>x/y/z defined by the Push, dropped by the Pop)."""
+    inner = (h.sphere((0, 0, 0), 1.0) + h.plane((0, 1, 0), 0.5) + [103, h.fbits(0.25)], 3)
+    words, cmd = h.scaled(2.0, h.rotated(h.rotation_matrix((0, 0, 1), 0.5), h.translated((1, 0, 0), inner)))
+    words, cmd = words + h.box((0, 0, 0), (1, 1, 1)) + [100], cmd + 2
+    src = rm.spec_source(cmd, words)
+    assert "xf_scale<EX>(px[r], py[r], pz[r]," in src and "q0x[r], q0y[r], q0z[r])" in src
+    assert "xf_rotate<EX>(q0x[r], q0y[r], q0z[r]," in src and "xf_translate<EX>(q1x[r], q1y[r], q1z[r]," in src
+    assert "sd_sphere<EX>(q2x[r], q2y[r], q2z[r]," in src and "sd_plane<EX>(q2x[r], q2y[r], q2z[r]," in src
+    assert "v8[r] = Arith<EX>::mul(v5[r]," in src          # ScalePop (command 8) rescales the group's value
+    assert "sd_box<EX>(px[r], py[r], pz[r]," in src         # after the pops the root point is in force again
+    for mode in (0, 1):
+        r = rm.spec_compile_check(cmd, words, mode)
+        if r["rc"] == -9 and "NVRTC is not available" in r["log"]:
+            pytest.skip("no libnvrtc in this environment: " + r["log"][:200])
+        assert r["rc"] == 0, r["log"]
