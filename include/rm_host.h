@@ -20,7 +20,9 @@ extern "C" {
 
 enum { RMH_NONE = -1, RMH_E_INVALID = -2, RMH_E_PANIC = -3, RMH_E_DEVICE = -4 };
 /* node / template kinds: CSGNode (csg/mod.rs:28-45) + extensions */
-enum { RMH_SPHERE = 0, RMH_BOX = 1, RMH_UNION = 2, RMH_SUBTRACTION = 3, RMH_INTERSECTION = 4, RMH_SMOOTH_UNION = 5 };
+enum { RMH_SPHERE = 0, RMH_BOX = 1, RMH_UNION = 2, RMH_SUBTRACTION = 3, RMH_INTERSECTION = 4, RMH_SMOOTH_UNION = 5,
+       /* N4: the kinds csg/mod.rs:34,41-44 reserves in comments */
+       RMH_PLANE = 6, RMH_TRANSLATION = 7, RMH_ROTATION = 8, RMH_SCALE = 9 };
 /* ValueType tags (csg_node_graph.rs:24-29) */
 enum { RMH_VT_SCALAR = 0, RMH_VT_VEC3 = 1, RMH_VT_CSGNODE = 2 };
 /* OrbitCameraControllerEvent (camera.rs:15-19) */
@@ -33,6 +35,13 @@ RMH_API const char *rmh_last_error(void);
 RMH_API int rmh_node_sphere(const float center[3], float radius);
 RMH_API int rmh_node_box(const float center[3], const float radius[3]);
 RMH_API int rmh_node_binary(int kind, int node_a, int node_b, float k);
+/* N4 (reserved at csg/mod.rs:34,41-44; builder.rs:8,16-23).  Plane: the normal is normalised; RMH_E_PANIC for a zero
+ * normal or a scale factor that is not finite and > 0.  Space transforms take ONE child and flatten to Push, child, Pop. */
+RMH_API int rmh_node_plane(const float normal[3], float offset);
+RMH_API int rmh_node_translation(int child, const float offset[3]);
+RMH_API int rmh_node_rotation(int child, const float rotation_wijk[4]);       /* unit quaternion */
+RMH_API int rmh_node_rotation_matrix(int child, const float m9_row_major[9]); /* object -> world */
+RMH_API int rmh_node_scale(int child, float factor);
 /* BuildCommands::build_commands into a fresh CSGCommandBufferBuilder (csg/mod.rs:16-19,
  * builder.rs:26-62).  Writes up to cap words; returns the word count; *cmd_count = builder.cmd_count. */
 RMH_API int rmh_build_commands(int node, uint32_t *words, uint32_t cap, uint32_t *cmd_count);

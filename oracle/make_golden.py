@@ -18,6 +18,10 @@ CASES = [  # name, scene, W, H, yaw, pitch, limits
     ("s1_96x54", "S1", 96, 54, 0.6, 0.4, (0.01, 100.0, 100)),
     ("s2_96x54", "S2", 96, 54, 0.6, 0.4, (0.01, 100.0, 100)),
     ("s2_50x30_limits", "S2", 50, 30, 2.2, -0.3, (0.02, 40.0, 24)),
+    # N4 extension scene (plane + space transforms): kept in its own directory, read by tests/test_oracle_n4.py and
+    # tests/test_n4_gpu.py
+    ("n4/s3_96x54", "S3", 96, 54, 0.6, 0.4, (0.01, 100.0, 100)),
+    ("n4/s3_64x40_limits", "S3", 64, 40, 2.2, 0.7, (0.02, 40.0, 24)),
 ]
 
 if __name__ == "__main__":
@@ -27,6 +31,7 @@ if __name__ == "__main__":
         cmd, words = h.SCENES[scene]()
         u = h.orbit_uniforms(W, H, yaw=yaw, pitch=pitch)
         r = h.oracle_render(u, cmd, words, W, H, limits=h.limits_bytes(*lim), aov=True)
+        (out / f"{name}.npz").parent.mkdir(exist_ok=True)
         np.savez_compressed(out / f"{name}.npz", uniforms=np.frombuffer(u, np.uint8), cmd_count=np.uint32(cmd),
                             words=words, W=np.uint32(W), H=np.uint32(H), limits=np.frombuffer(h.limits_bytes(*lim), np.uint8),
                             rgba=r["rgba"], cls=r["cls"], t=r["t"], counters=r["counters"])

@@ -10,12 +10,13 @@ import numpy as np
 
 HOST_LIB_PATH = Path(__file__).resolve().parent / "librm_host.so"
 NONE, E_INVALID, E_PANIC, E_DEVICE = -1, -2, -3, -4
-SPHERE, BOX, UNION, SUBTRACTION, INTERSECTION, SMOOTH_UNION = range(6)
+SPHERE, BOX, UNION, SUBTRACTION, INTERSECTION, SMOOTH_UNION, PLANE, TRANSLATION, ROTATION, SCALE = range(10)
 VT_SCALAR, VT_VEC3, VT_CSGNODE = range(3)
 EV_PAN, EV_ORBIT, EV_DOLLY = range(3)
 
 HOST_SYMBOLS = [
-    "rmh_reset", "rmh_last_error", "rmh_node_sphere", "rmh_node_box", "rmh_node_binary", "rmh_build_commands",
+    "rmh_reset", "rmh_last_error", "rmh_node_sphere", "rmh_node_box", "rmh_node_binary", "rmh_node_plane", "rmh_node_translation",
+    "rmh_node_rotation", "rmh_node_rotation_matrix", "rmh_node_scale", "rmh_build_commands",
     "rmh_template_name", "rmh_template_param_count", "rmh_template_param", "rmh_template_evaluate", "rmh_orbit_new",
     "rmh_orbit_update", "rmh_orbit_state", "rmh_orbit_set", "rmh_orbit_camera", "rmh_camera_view", "rmh_uniforms",
     "rmh_limits_default", "rmh_graph_new", "rmh_graph_add_root", "rmh_graph_add_node", "rmh_graph_remove_node",
@@ -40,6 +41,11 @@ def lib() -> C.CDLL:
         L.rmh_node_sphere.argtypes = [C.c_void_p, C.c_float]
         L.rmh_node_box.argtypes = [C.c_void_p, C.c_void_p]
         L.rmh_node_binary.argtypes = [C.c_int, C.c_int, C.c_int, C.c_float]
+        L.rmh_node_plane.argtypes = [C.c_void_p, C.c_float]
+        L.rmh_node_translation.argtypes = [C.c_int, C.c_void_p]
+        L.rmh_node_rotation.argtypes = [C.c_int, C.c_void_p]
+        L.rmh_node_rotation_matrix.argtypes = [C.c_int, C.c_void_p]
+        L.rmh_node_scale.argtypes = [C.c_int, C.c_float]
         L.rmh_build_commands.argtypes = [C.c_int, C.c_void_p, C.c_uint32, C.c_void_p]
         L.rmh_template_param.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p]
         L.rmh_template_evaluate.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
@@ -76,6 +82,37 @@ def box(center, radius) -> int:
 
 def binary(kind: int, a: int, b: int, k: float = 0.25) -> int:
     return lib().rmh_node_binary(kind, a, b, float(k))
+
+
+def _checked(hnd: int, what: str) -> int:
+    if hnd < 0:
+        raise ValueError(f"{what}: {lib().rmh_last_error().decode() or hnd}")
+    return hnd
+
+
+# N4 node kinds (reserved in the reference at csg/mod.rs:34,41-44): one child, flattened as Push, child, Pop
+def plane(normal, offset) -> int:
+    n = _f3(normal)
+    return _checked(lib().rmh_node_plane(n.ctypes.data, float(offset)), "plane")
+
+
+def translation(child: int, offset) -> int:
+    t = _f3(offset)
+    return _checked(lib().rmh_node_translation(child, t.ctypes.data), "translation")
+
+
+def rotation(child: int, rotation_wijk) -> int:
+    q = np.ascontiguousarray(np.asarray(rotation_wijk, np.float32).reshape(4))
+    return _checked(lib().rmh_node_rotation(child, q.ctypes.data), "rotation")
+
+
+def rotation_matrix(child: int, m) -> int:
+    a = np.ascontiguousarray(np.asarray(m, np.float32).reshape(9))
+    return _checked(lib().rmh_node_rotation_matrix(child, a.ctypes.data), "rotation_matrix")
+
+
+def scale(child: int, factor) -> int:
+    return _checked(lib().rmh_node_scale(child, float(factor)), "scale")
 
 
 def build_commands(node: int):

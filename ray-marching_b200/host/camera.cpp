@@ -49,6 +49,18 @@ static Mat4 rotation_matrix(const Quat &q) {  // UnitQuaternion::to_rotation_mat
     return m;
 }
 
+Quat quat_from_axis_angle(const Vec3 &axis, float angle) {
+    const float n = std::sqrt(axis[0] * axis[0] + axis[1] * axis[1] + axis[2] * axis[2]);
+    if (!(n > 0.0f)) return Quat{};  // no axis: identity
+    const float s = std::sin(angle * 0.5f) / n;
+    return Quat{std::cos(angle * 0.5f), axis[0] * s, axis[1] * s, axis[2] * s};
+}
+
+std::array<float, 9> quat_to_matrix3(const Quat &q) {
+    const Mat4 m = rotation_matrix(q);  // column-major 4x4
+    return {m[0], m[4], m[8], m[1], m[5], m[9], m[2], m[6], m[10]};
+}
+
 Mat4 Camera::view() const {
     // rotation.inverse() * Translation3::from(-position)  (camera.rs:10-12) as a homogeneous matrix:
     // [ R^T | R^T * (-position) ]

@@ -1,5 +1,6 @@
 // csg.cpp — CSG node model, command-buffer builder and node templates (see rm_host.hpp for the
 // reference lines each item mirrors).
+#include <cmath>
 #include <cstring>
 #include <stdexcept>
 
@@ -56,8 +57,62 @@ CSGNode CSGNode::Subtraction(CSGNode a, CSGNode b) { return binary(Kind::Subtrac
 CSGNode CSGNode::Intersection(CSGNode a, CSGNode b) { return binary(Kind::Intersection, std::move(a), std::move(b)); }
 CSGNode CSGNode::SmoothUnion(CSGNode a, CSGNode b, float k) { return binary(Kind::SmoothUnion, std::move(a), std::move(b), k); }
 
+CSGNode CSGNode::Plane(const Vec3 &normal, float offset) {
+    const float len = std::sqrt(normal[0] * normal[0] + normal[1] * normal[1] + normal[2] * normal[2]);
+    if (!(len > 0.0f) || !std::isfinite(len)) throw std::invalid_argument("Plane: normal must be finite and non-zero");
+    CSGNode n;
+    n.kind = Kind::Plane;
+    n.center = {normal[0] / len, normal[1] / len, normal[2] / len};
+    n.k = offset;
+    return n;
+}
+static CSGNode unary(CSGNode::Kind kind, CSGNode child) {
+    CSGNode n;
+    n.kind = kind;
+    n.a = std::make_shared<const CSGNode>(std::move(child));
+    return n;
+}
+CSGNode CSGNode::Translation(CSGNode child, const Vec3 &offset) {
+    CSGNode n = unary(Kind::Translation, std::move(child));
+    n.center = offset;
+    return n;
+}
+CSGNode CSGNode::RotationMatrix(CSGNode child, const std::array<float, 9> &m) {
+    CSGNode n = unary(Kind::Rotation, std::move(child));
+    n.rotation = m;
+    return n;
+}
+CSGNode CSGNode::Rotation(CSGNode child, const Quat &q) { return RotationMatrix(std::move(child), quat_to_matrix3(q)); }
+CSGNode CSGNode::Scale(CSGNode child, float factor) {
+    if (!(factor > 0.0f) || !std::isfinite(factor)) throw std::invalid_argument("Scale: factor must be finite and > 0");
+    CSGNode n = unary(Kind::Scale, std::move(child));
+    n.k = factor;
+    return n;
+}
+
 void CSGNode::build_commands(CSGCommandBufferBuilder &builder) const {
     switch (kind) {
+        case Kind::Plane:  // N4: opcode, then params (the order of sphere.rs:15-21)
+            builder.push_command(CSGCommandType::Plane).push_param_vec3(center).push_param_float(k);
+            return;
+        case Kind::Translation:  // Push, the one child, Pop (builder.rs:16-19)
+            builder.push_command(CSGCommandType::TranslationPush).push_param_vec3(center);
+            a->build_commands(builder);
+            builder.push_command(CSGCommandType::TranslationPop);
+            return;
+        case Kind::Rotation:  // the matrix row by row (builder.rs:20-21)
+            builder.push_command(CSGCommandType::RotationPush)
+                .push_param_vec3({rotation[0], rotation[1], rotation[2]})
+                .push_param_vec3({rotation[3], rotation[4], rotation[5]})
+                .push_param_vec3({rotation[6], rotation[7], rotation[8]});
+            a->build_commands(builder);
+            builder.push_command(CSGCommandType::RotationPop);
+            return;
+        case Kind::Scale:  // the Pop repeats the factor: the child's distance is multiplied by it (builder.rs:22-23)
+            builder.push_command(CSGCommandType::ScalePush).push_param_float(k);
+            a->build_commands(builder);
+            builder.push_command(CSGCommandType::ScalePop).push_param_float(k);
+            return;
         case Kind::Sphere:  // sphere.rs:15-21
             builder.push_command(CSGCommandType::Sphere).push_param_vec3(center).push_param_float(radius[0]);
             return;
@@ -84,6 +139,10 @@ const char *CSGNodeTemplate::name() const {
         case Kind::Union: return "Union";              // stringify!($name), operations/mod.rs:25-27
         case Kind::Subtraction: return "Subtraction";
         case Kind::Intersection: return "Intersection";
+        case Kind::Plane: return "Plane";
+        case Kind::Translation: return "Translation";
+        case Kind::Rotation: return "Rotation";
+        case Kind::Scale: return "Scale";
         default: return "SmoothUnion";
     }
 }
@@ -96,6 +155,14 @@ std::vector<std::pair<std::string, ValueType>> CSGNodeTemplate::input_params() c
             return {{"center", ValueType::Vec3v({0, 0, 0})}, {"radius", ValueType::Vec3v({1, 1, 1})}};
         case Kind::SmoothUnion:
             return {{"A", ValueType::CSGNode(std::nullopt)}, {"B", ValueType::CSGNode(std::nullopt)}, {"k", ValueType::Scalar(0.25f)}};
+        case Kind::Plane:
+            return {{"normal", ValueType::Vec3v({0, 1, 0})}, {"offset", ValueType::Scalar(0.0f)}};
+        case Kind::Translation:
+            return {{"A", ValueType::CSGNode(std::nullopt)}, {"offset", ValueType::Vec3v({0, 0, 0})}};
+        case Kind::Rotation:
+            return {{"A", ValueType::CSGNode(std::nullopt)}, {"axis", ValueType::Vec3v({0, 1, 0})}, {"angle", ValueType::Scalar(0.0f)}};
+        case Kind::Scale:
+            return {{"A", ValueType::CSGNode(std::nullopt)}, {"factor", ValueType::Scalar(1.0f)}};
         default:  // operations/mod.rs:29-42
             return {{"A", ValueType::CSGNode(std::nullopt)}, {"B", ValueType::CSGNode(std::nullopt)}};
     }
@@ -118,11 +185,20 @@ std::optional<CSGNode> CSGNodeTemplate::evaluate(const std::map<std::string, Val
             return CSGNode::Sphere(unwrap(get(p, "center").to_vec3(), "center"), unwrap(get(p, "radius").to_scalar(), "radius"));
         case Kind::Box:  // box.rs:45-49
             return CSGNode::Box(unwrap(get(p, "center").to_vec3(), "center"), unwrap(get(p, "radius").to_vec3(), "radius"));
+        case Kind::Plane:
+            return CSGNode::Plane(unwrap(get(p, "normal").to_vec3(), "normal"), unwrap(get(p, "offset").to_scalar(), "offset"));
         default:
             break;
     }
     auto lhs = get(p, "A").to_csg_node();  // operations/mod.rs:47  (`?` -> None)
     if (!lhs) return std::nullopt;
+    switch (kind) {  // N4 space transforms: one connection-only input, then constants
+        case Kind::Translation: return CSGNode::Translation(*lhs, unwrap(get(p, "offset").to_vec3(), "offset"));
+        case Kind::Rotation:
+            return CSGNode::Rotation(*lhs, quat_from_axis_angle(unwrap(get(p, "axis").to_vec3(), "axis"), unwrap(get(p, "angle").to_scalar(), "angle")));
+        case Kind::Scale: return CSGNode::Scale(*lhs, unwrap(get(p, "factor").to_scalar(), "factor"));
+        default: break;
+    }
     auto rhs = get(p, "B").to_csg_node();  // operations/mod.rs:48
     if (!rhs) return std::nullopt;
     switch (kind) {
@@ -134,7 +210,8 @@ std::optional<CSGNode> CSGNodeTemplate::evaluate(const std::map<std::string, Val
 }
 
 std::vector<CSGNodeTemplate> CSGNodeTemplate::all() {
-    return {{Kind::Sphere}, {Kind::Box}, {Kind::Union}, {Kind::Subtraction}, {Kind::Intersection}, {Kind::SmoothUnion}};
+    return {{Kind::Sphere}, {Kind::Box}, {Kind::Union}, {Kind::Subtraction}, {Kind::Intersection}, {Kind::SmoothUnion},
+            {Kind::Plane}, {Kind::Translation}, {Kind::Rotation}, {Kind::Scale}};
 }
 
 }  // namespace csg

@@ -63,6 +63,27 @@ int rmh_node_binary(int kind, int a, int b, float k) {
         default: return RMH_E_INVALID;
     }
 }
+int rmh_node_plane(const float n[3], float offset) {
+    return guarded([&] { return add_node(csg::CSGNode::Plane({n[0], n[1], n[2]}, offset)); });
+}
+int rmh_node_translation(int child, const float t[3]) {
+    if (!node_ok(child)) return RMH_E_INVALID;
+    return add_node(csg::CSGNode::Translation(g_nodes[child], {t[0], t[1], t[2]}));
+}
+int rmh_node_rotation(int child, const float q[4]) {
+    if (!node_ok(child)) return RMH_E_INVALID;
+    return add_node(csg::CSGNode::Rotation(g_nodes[child], Quat{q[0], q[1], q[2], q[3]}));
+}
+int rmh_node_rotation_matrix(int child, const float m[9]) {
+    if (!node_ok(child)) return RMH_E_INVALID;
+    std::array<float, 9> a;
+    std::memcpy(a.data(), m, sizeof(float) * 9);
+    return add_node(csg::CSGNode::RotationMatrix(g_nodes[child], a));
+}
+int rmh_node_scale(int child, float factor) {
+    if (!node_ok(child)) return RMH_E_INVALID;
+    return guarded([&] { return add_node(csg::CSGNode::Scale(g_nodes[child], factor)); });
+}
 int rmh_build_commands(int node, uint32_t *words, uint32_t cap, uint32_t *cmd_count) {
     if (!node_ok(node)) return RMH_E_INVALID;
     csg::CSGCommandBufferBuilder b;
@@ -156,7 +177,7 @@ int rmh_graph_new(void) {
 }
 int rmh_graph_add_root(int g) { return GRAPH_OK(g) ? g_graphs[g].add_root() : RMH_E_INVALID; }
 int rmh_graph_add_node(int g, int kind) {
-    if (!GRAPH_OK(g) || kind < 0 || kind > 5) return RMH_E_INVALID;
+    if (!GRAPH_OK(g) || kind < 0 || kind > RMH_SCALE) return RMH_E_INVALID;
     return g_graphs[g].add_node(csg::CSGNodeTemplate{tkind(kind)});
 }
 int rmh_graph_remove_node(int g, int node) {

@@ -10,7 +10,9 @@
 //   Uniforms, RayMarchLimits, RayMarchingResources,
 //   RayMarchingCallback{prepare,paint}               src/ray_marching/renderer.rs:29-256
 //   CSGNodeGraph::evaluate_root + Evaluator          src/csg_node_graph.rs:235-309   (headless: no egui)
-// Extensions not in the reference: Intersection (opcode 102), SmoothUnion (103, k).
+// Extensions not in the reference: Intersection (opcode 102), SmoothUnion (103, k); and N4
+// (SURVEY.md 8(f)): the node kinds the reference's enums reserve in comments (csg/mod.rs:34,41-44, builder.rs:8,16-23):
+// Plane, Translation, Rotation, Scale.
 #pragma once
 #include <array>
 #include <cstdint>
@@ -26,11 +28,16 @@ struct rm_ctx;
 namespace ray_marching {
 
 using Vec3 = std::array<float, 3>;
+struct Quat { float w = 1, i = 0, j = 0, k = 0; };  // nalgebra UnitQuaternion<f32>
 
 namespace csg {
 
 // builder.rs:1-24 (#[repr(u32)])
-enum class CSGCommandType : uint32_t { Sphere = 0, Box = 1, Union = 100, Subtraction = 101, Intersection = 102, SmoothUnion = 103 };
+enum class CSGCommandType : uint32_t {
+    Sphere = 0, Box = 1, Plane = 2,                                           // builder.rs:6-8
+    Union = 100, Subtraction = 101, Intersection = 102, SmoothUnion = 103,    // builder.rs:12-14
+    TranslationPush = 200, TranslationPop = 201, RotationPush = 202, RotationPop = 203, ScalePush = 204, ScalePop = 205,  // :18-23
+};
 
 // builder.rs:26-62
 struct CSGCommandBufferBuilder {
@@ -46,12 +53,13 @@ using NodeBox = std::shared_ptr<const CSGNode>;  // Box<CSGNode>; immutable, so 
 
 // csg/mod.rs:28-45 (enum_dispatch over the node structs) + BuildCommands (csg/mod.rs:16-19)
 struct CSGNode {
-    enum class Kind { Sphere, Box, Union, Subtraction, Intersection, SmoothUnion };
+    enum class Kind { Sphere, Box, Union, Subtraction, Intersection, SmoothUnion, Plane, Translation, Rotation, Scale };
     Kind kind = Kind::Sphere;
-    Vec3 center{0, 0, 0};   // sphere.rs:11, box.rs:10
+    Vec3 center{0, 0, 0};   // sphere.rs:11, box.rs:10; Plane: unit normal; Translation: offset
     Vec3 radius{1, 1, 1};   // sphere: radius[0] (sphere.rs:12); box: radius xyz (box.rs:11)
-    float k = 0.25f;        // SmoothUnion only
-    NodeBox a, b;           // binary operators: .0 and .1 (operations/mod.rs:9)
+    float k = 0.25f;        // SmoothUnion: k; Plane: offset h; Scale: factor
+    std::array<float, 9> rotation{1, 0, 0, 0, 1, 0, 0, 0, 1};  // Rotation: row-major matrix, object -> world
+    NodeBox a, b;           // binary operators: .0 and .1 (operations/mod.rs:9); space transforms: a = the one child
 
     static CSGNode Sphere(const Vec3 &center, float radius);
     static CSGNode Box(const Vec3 &center, const Vec3 &radius);
@@ -59,10 +67,19 @@ struct CSGNode {
     static CSGNode Subtraction(CSGNode a, CSGNode b);
     static CSGNode Intersection(CSGNode a, CSGNode b);
     static CSGNode SmoothUnion(CSGNode a, CSGNode b, float k);
+    // N4.  Plane: dot(p, n) + offset with n normalised here (throws std::invalid_argument for a zero / non-finite
+    // normal).  Space transforms have one child ("1 child, transforms space", builder.rs:16-17) and flatten to
+    // Push, child, Pop.  Scale is uniform and must be finite and > 0 (throws otherwise).
+    static CSGNode Plane(const Vec3 &normal, float offset);
+    static CSGNode Translation(CSGNode child, const Vec3 &offset);
+    static CSGNode Rotation(CSGNode child, const Quat &q);                       // unit quaternion, as camera.rs uses
+    static CSGNode RotationMatrix(CSGNode child, const std::array<float, 9> &m);  // row-major, object -> world
+    static CSGNode Scale(CSGNode child, float factor);
     // post-order walk: A, B, then the operator (operations/mod.rs:13-17); primitives: opcode then
     // params (sphere.rs:15-21, box.rs:14-20)
     void build_commands(CSGCommandBufferBuilder &builder) const;
-    bool is_binary() const { return kind != Kind::Sphere && kind != Kind::Box; }
+    bool is_binary() const { return kind == Kind::Union || kind == Kind::Subtraction || kind == Kind::Intersection || kind == Kind::SmoothUnion; }
+    bool is_transform() const { return kind == Kind::Translation || kind == Kind::Rotation || kind == Kind::Scale; }
 };
 
 }  // namespace csg
@@ -85,21 +102,22 @@ struct ValueType {
 namespace csg {
 // csg/mod.rs:21-26,47-65 — the editor's node templates (egui's InputParamKind is UI-only and dropped)
 struct CSGNodeTemplate {
-    enum class Kind { Sphere, Box, Union, Subtraction, Intersection, SmoothUnion };
+    enum class Kind { Sphere, Box, Union, Subtraction, Intersection, SmoothUnion, Plane, Translation, Rotation, Scale };
     Kind kind;
     const char *name() const;                                             // "Sphere", "Box", "Union", "Subtraction", ...
     std::vector<std::pair<std::string, ValueType>> input_params() const;  // names + defaults (sphere.rs:28-43 ...)
     // None when a connection-only input is missing (operations/mod.rs:47-48); throws std::runtime_error
     // where the reference unwrap()s (wrong value type / missing key: sphere.rs:47-48, box.rs:46-47)
     std::optional<CSGNode> evaluate(const std::map<std::string, ValueType> &input_params) const;
-    static std::vector<CSGNodeTemplate> all();  // csg/mod.rs:56-64 (+ the two extension operators)
+    static std::vector<CSGNodeTemplate> all();  // csg/mod.rs:56-64 (+ the two extension operators + the four N4 kinds)
 };
 }  // namespace csg
 
 // ---- camera.rs -------------------------------------------------------------------------------
-struct Quat { float w = 1, i = 0, j = 0, k = 0; };  // nalgebra UnitQuaternion<f32>
 Quat quat_from_euler_angles(float roll, float pitch, float yaw);  // UnitQuaternion::from_euler_angles
 Vec3 quat_rotate(const Quat &q, const Vec3 &v);
+Quat quat_from_axis_angle(const Vec3 &axis, float angle);        // UnitQuaternion::from_axis_angle (axis normalised here)
+std::array<float, 9> quat_to_matrix3(const Quat &q);             // UnitQuaternion::to_rotation_matrix, row-major
 using Mat4 = std::array<float, 16>;  // column-major, like nalgebra storage / WGSL mat4x4
 
 struct Camera {                // camera.rs:3-13

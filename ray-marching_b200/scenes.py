@@ -60,7 +60,29 @@ def node_s2(n_leaves: int = 32, seed: int = 0x5EED0040, k: float = 0.25) -> int:
     return acc
 
 
-NODES = {"S0": node_s0, "S1": node_s1, "S2": node_s2}
+def _rot_y(angle: float) -> np.ndarray:
+    """row-major rotation about +y (object -> world), float64 rounded to float32"""
+    c, s = math.cos(angle), math.sin(angle)
+    return np.array([[c, 0, s], [0, 1, 0], [-s, 0, c]], np.float64).astype(np.float32)
+
+
+def node_s3(n_inst: int = 8, k: float = 0.25) -> int:
+    """N4 scene (plane + space transforms): a ring of n_inst instances — instance i is Rotation(y, 2*pi*i/n) of
+    Translation((1.6, 0.1*i - 0.3, 0)) of a leaf in its own frame (even i: Box r=(0.35,0.5,0.2); odd i: Scale(0.8) of
+    Subtraction(Sphere r=0.6, Box r=(0.7,0.2,0.2)) — smooth-united left to right, then Union with the plane y = -1."""
+    acc = None
+    for i in range(n_inst):
+        if i % 2 == 0:
+            leaf = host.box((0, 0, 0), (0.35, 0.5, 0.2))
+        else:
+            leaf = host.scale(host.binary(host.SUBTRACTION, host.sphere((0, 0, 0), 0.6), host.box((0, 0, 0), (0.7, 0.2, 0.2))), 0.8)
+        inst = host.rotation_matrix(host.translation(leaf, (1.6, np.float32(0.1) * np.float32(i) - np.float32(0.3), 0.0)),
+                                    _rot_y(2 * math.pi * i / n_inst))
+        acc = inst if acc is None else host.binary(host.SMOOTH_UNION, acc, inst, k)
+    return host.binary(host.UNION, acc, host.plane((0, 1, 0), 1.0))
+
+
+NODES = {"S0": node_s0, "S1": node_s1, "S2": node_s2, "S3": node_s3}
 
 
 def program(scene: str):

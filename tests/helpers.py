@@ -339,4 +339,27 @@ def orbit_uniforms(W: int, H: int, yaw=0.0, pitch=0.0, radius=5.0, target=(0, 0,
     return uniforms_bytes(float(W), float(H), eye, R)
 
 
-SCENES = {"S0": scene_s0, "S1": scene_s1, "S2": scene_s2}
+def scene_s3(n_inst: int = 8, k: float = 0.25):
+    """S3 (N4): ring of rotated + translated instances, every other one scaled, over the plane y = -1
+    (definition: ray-marching_b200/scenes.py node_s3; built here independently from the word builders)."""
+    w: list[int] = []
+    cmds = 0
+    for i in range(n_inst):
+        if i % 2 == 0:
+            leaf = (box((0, 0, 0), (0.35, 0.5, 0.2)), 1)
+        else:
+            leaf = scaled(0.8, (sphere((0, 0, 0), 0.6) + box((0, 0, 0), (0.7, 0.2, 0.2)) + [OP_SUBTRACTION], 3))
+        a = 2 * math.pi * i / n_inst
+        R = np.array([[math.cos(a), 0, math.sin(a)], [0, 1, 0], [-math.sin(a), 0, math.cos(a)]])
+        ty = np.float32(0.1) * np.float32(i) - np.float32(0.3)
+        iw, ic = rotated(R, translated((1.6, ty, 0.0), leaf))
+        w += iw
+        cmds += ic
+        if i >= 1:
+            w += [OP_SMOOTH_UNION, fbits(k)]
+            cmds += 1
+    w += plane((0, 1, 0), 1.0) + [OP_UNION]
+    return cmds + 2, np.array(w, np.uint32)
+
+
+SCENES = {"S0": scene_s0, "S1": scene_s1, "S2": scene_s2, "S3": scene_s3}

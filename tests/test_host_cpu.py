@@ -201,3 +201,92 @@ def test_graph_evaluator_memoises_shared_nodes(host):
     assert g.evaluations == 3              # but only sp, u1, u2 were evaluated
     g.connect(u2, u1, "B")                 # a cycle: the reference would recurse forever; reported as a panic
     assert g.evaluate_root() == host.E_PANIC
+
+
+# ---- N4: the node kinds the reference reserves in comments (csg/mod.rs:34,41-44; builder.rs:8,16-23) ----------------
+def test_n4_nodes_flatten_to_push_child_pop(host):
+    s = host.sphere((0, 0, 0), 1.0)
+    cnt, w = host.build_commands(host.translation(s, (1, 2, 3)))
+    assert cnt == 3 and w.tolist() == h.translated((1, 2, 3), (h.sphere((0, 0, 0), 1.0), 1))[0]
+    cnt, w = host.build_commands(host.scale(s, 2.5))
+    assert cnt == 3 and w.tolist() == h.scaled(2.5, (h.sphere((0, 0, 0), 1.0), 1))[0]
+    R = [[0, -1, 0], [1, 0, 0], [0, 0, 1]]
+    cnt, w = host.build_commands(host.rotation_matrix(s, R))
+    assert cnt == 3 and w.tolist() == h.rotated(R, (h.sphere((0, 0, 0), 1.0), 1))[0]
+    # the plane's normal is normalised by the constructor; opcode first, then normal, then offset
+    cnt, w = host.build_commands(host.plane((0, 2, 0), 1.5))
+    assert cnt == 1 and w.tolist() == h.plane((0, 1, 0), 1.5)
+    n = np.array([1, 2, 2], np.float32)
+    w = host.build_commands(host.plane(n, -0.5))[1]
+    np.testing.assert_allclose(w[1:4].view(np.float32), n / 3, rtol=1e-6)
+
+
+def test_n4_rotation_from_quaternion_is_the_same_rotation_the_camera_uses(host):
+    # a quarter turn about z as a unit quaternion (w, i, j, k) -> row-major matrix, object -> world
+    q = (math.cos(math.pi / 4), 0, 0, math.sin(math.pi / 4))
+    w = host.build_commands(host.rotation(host.sphere((0, 0, 0), 1.0), q))[1]
+    m = w[1:10].view(np.float32).reshape(3, 3)
+    np.testing.assert_allclose(m, [[0, -1, 0], [1, 0, 0], [0, 0, 1]], atol=1e-6)
+    # and for a general axis it agrees with Rodrigues' formula (helpers.rotation_matrix)
+    axis, ang = np.array([1.0, 2.0, 3.0]), 0.7
+    a = axis / np.linalg.norm(axis)
+    q = (math.cos(ang / 2), *(a * math.sin(ang / 2)))
+    w = host.build_commands(host.rotation(host.sphere((0, 0, 0), 1.0), q))[1]
+    np.testing.assert_allclose(w[1:10].view(np.float32).reshape(3, 3), h.rotation_matrix(axis, ang), atol=1e-6)
+
+
+def test_n4_nested_tree_is_valid_and_means_what_it_says(host):
+    # Scale(2, Rotation(Translation(Union(sphere, box)))) smooth-united with a ground plane
+    inner = host.binary(host.UNION, host.sphere((0, 0, 0), 0.5), host.box((0.6, 0, 0), (0.3, 0.3, 0.3)))
+    R = h.rotation_matrix((0, 0, 1), 0.5)
+    node = host.scale(host.rotation_matrix(host.translation(inner, (1, 0, 0)), R), 2.0)
+    scene = host.binary(host.SMOOTH_UNION, node, host.plane((0, 1, 0), 1.5), 0.25)
+    cnt, w = host.build_commands(scene)
+    assert cnt == 11 and h.oracle_validate(cnt, w) == 0
+    exp = h.scaled(2.0, h.rotated(R, h.translated((1, 0, 0), (h.sphere((0, 0, 0), 0.5) + h.box((0.6, 0, 0), (0.3, 0.3, 0.3)) + [100], 3))))
+    assert w.tolist() == exp[0] + h.plane((0, 1, 0), 1.5) + [103, h.fbits(0.25)]
+    # the centre of the inner sphere ends up at 2 * R (1,0,0) in the world
+    c = 2.0 * (R @ np.array([1.0, 0, 0]))
+    d = h.oracle_map(cnt, w, np.array([c], np.float32))
+    assert abs(d[0] - (-1.0)) < 1e-5  # radius 0.5 scaled by 2
+
+
+def test_n4_constructors_reject_what_the_validator_would(host):
+    s = host.sphere((0, 0, 0), 1.0)
+    for bad in (0.0, -1.0, float("inf"), float("nan")):
+        with pytest.raises(ValueError):
+            host.scale(s, bad)
+    with pytest.raises(ValueError):
+        host.plane((0, 0, 0), 1.0)
+    with pytest.raises(ValueError):
+        host.translation(12345, (0, 0, 0))  # not a node handle
+
+
+def test_n4_templates_and_graph(host):
+    names = [host.lib().rmh_template_name(k).decode() for k in range(10)]
+    assert names[6:] == ["Plane", "Translation", "Rotation", "Scale"]
+    assert [(n, t) for n, t, _ in host.template_params(host.PLANE)] == [("normal", host.VT_VEC3), ("offset", host.VT_SCALAR)]
+    assert [(n, t) for n, t, _ in host.template_params(host.TRANSLATION)] == [("A", host.VT_CSGNODE), ("offset", host.VT_VEC3)]
+    assert [(n, t) for n, t, _ in host.template_params(host.ROTATION)] == [("A", host.VT_CSGNODE), ("axis", host.VT_VEC3), ("angle", host.VT_SCALAR)]
+    p = host.template_params(host.SCALE)
+    assert [(n, t) for n, t, _ in p] == [("A", host.VT_CSGNODE), ("factor", host.VT_SCALAR)] and p[1][2][0] == 1.0
+    # a missing child propagates None like the binary operators' `?` (operations/mod.rs:47-48)
+    assert host.template_evaluate(host.SCALE, {"A": ("node", host.NONE), "factor": ("scalar", 2.0)}) == host.NONE
+    assert host.template_evaluate(host.SCALE, {"A": ("node", host.sphere((0, 0, 0), 1)), "factor": ("scalar", -2.0)}) == host.E_PANIC
+    # the editor graph: Sphere -> Translation -> Rotation(defaults: angle 0 = identity) -> Root
+    g = host.Graph()
+    root = g.add_root()
+    sp = g.add_node(host.SPHERE)
+    tr = g.add_node(host.TRANSLATION)
+    g.set_vec3(tr, "offset", (0, 1, 0))
+    ro = g.add_node(host.ROTATION)
+    g.connect(sp, tr, "A")
+    g.connect(tr, ro, "A")
+    g.connect(ro, root, "SDF")
+    cnt, w = host.build_commands(g.evaluate_root())
+    assert cnt == 5 and w[0] == 202 and w[10] == 200 and w[-2:].tolist() == [201, 203]
+    np.testing.assert_array_equal(w[1:10].view(np.float32), np.eye(3, dtype=np.float32).reshape(9))
+    pts = np.random.default_rng(0).uniform(-3, 3, (100, 3)).astype(np.float32)
+    np.testing.assert_allclose(h.oracle_map(cnt, w, pts), h.oracle_map(1, h.sphere((0, 1, 0), 1.0), pts), atol=1e-6)
+    g.disconnect(tr, "A")
+    assert g.evaluate_root() == host.NONE

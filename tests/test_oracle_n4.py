@@ -132,3 +132,35 @@ def test_rendered_frame_agrees_between_the_two_restatements():
     assert np.array_equal(a["t"].view(np.uint32), b["t"].view(np.uint32))
     assert np.array_equal(a["counters"], b["counters"])
     assert (a["cls"] == 2).mean() > 0.2
+
+
+# ---- golden frames of the N4 scene S3 (tests/golden/n4, made by oracle/make_golden.py) -------------------------------
+from pathlib import Path  # noqa: E402
+
+GOLDEN_N4 = sorted((Path(__file__).resolve().parent / "golden" / "n4").glob("*.npz"))
+
+
+@pytest.mark.parametrize("path", GOLDEN_N4, ids=lambda p: p.stem)
+def test_n4_golden_frames_are_reproduced_by_both_restatements(path):
+    z = np.load(path)
+    g = {k: z[k] for k in z.files}
+    lim = g["limits"].tobytes()
+    W, H, cmd = int(g["W"]), int(g["H"]), int(g["cmd_count"])
+    r = h.oracle_render(g["uniforms"].tobytes(), cmd, g["words"], W, H, limits=lim, aov=True)
+    assert np.array_equal(r["rgba"], g["rgba"]) and np.array_equal(r["cls"], g["cls"])
+    assert np.array_equal(r["t"].view(np.uint32), g["t"].view(np.uint32))
+    assert np.array_equal(r["counters"], g["counters"])
+    limits = (*np.frombuffer(lim[:8], np.float32), int(np.frombuffer(lim[8:], np.uint32)[0]))
+    n = np_oracle.render(g["uniforms"].tobytes(), cmd, g["words"], W, H, limits)
+    assert np.array_equal(n["rgba"], g["rgba"]) and np.array_equal(n["cls"], g["cls"])
+    hit = g["cls"] == 2
+    assert np.array_equal(n["t"][hit], g["t"][hit])
+    assert np.array_equal(n["counters"], g["counters"])
+
+
+def test_s3_definition():
+    cmd, words = h.scene_s3()
+    assert cmd == 65 and len(words) == 244 and h.oracle_validate(cmd, words) == 0
+    # the first instance (i = 0: identity rotation, translation (1.6, -0.3, 0)) is the box centred there
+    d = h.oracle_map(cmd, words, np.array([[1.6, -0.3, 0.0]], np.float32))
+    assert abs(d[0] - (-0.2)) < 1e-5
