@@ -3,7 +3,7 @@
 "Mrays/s and FPS at 4K on fixed CSG scene, 1/2/4/8 B200; % FP32 roofline").
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--mode fast|exact]
-                  [--workload cfg3|cfg2|cfg1|cfg4|cfg5] [--kernel wavefront|simple]
+                  [--workload cfg3|cfg2|cfg1|cfg4|cfg5|n4] [--kernel wavefront|simple]
 
 A "step" is one pass of the hot path over one batch: rm_paint of the workload's frame(s).
   cfg3 (default)  configs[2]: deep CSG scene S2 (64 graph nodes, smooth-min) at 3840x2160 — the config
@@ -38,9 +38,13 @@ WORKLOADS = {
     "cfg3": ("S2", 3840, 2160, 1, "configs[2]: deep CSG S2 (32 leaves, 28 smooth-unions, 3 subtractions; 251 words) 3840x2160"),
     "cfg4": ("S2", 7680, 4320, 1, "configs[3]: S2 at 7680x4320, one frame row-sharded in interleaved 16-row strips, NCCL gather to rank 0"),
     "cfg5": ("S1", 1920, 1080, 1024, "configs[4]: 1024 orbit poses of S1 at 1920x1080, frame-parallel"),
+    # not a BASELINE.json config: the N4 extension scene (plane + translation / rotation / scale groups), single GPU
+    "n4": ("S3", 1920, 1080, 1, "extension (SURVEY 8(f) N4, not a BASELINE config): S3, 8 rotated / translated / scaled instances over a plane, 1920x1080"),
 }
 F_STEP, F_HIT, F_SAMPLE, F_FLOOR, F_PIXEL = 9, 75, 87, 14, 31  # SURVEY.md §8(a) FLOP table
-OP_FLOPS = {0: (10, 4), 1: (22, 6), 100: (1, 0), 101: (2, 0), 102: (1, 0), 103: (10, 1)}  # opcode: (flops, params)
+OP_FLOPS = {0: (10, 4), 1: (22, 6), 100: (1, 0), 101: (2, 0), 102: (1, 0), 103: (10, 1),  # opcode: (flops, params)
+            # N4, counted the same literal way: plane 3 mul + 3 add, translation 3 sub, rotation 9 mul + 6 add, scale 3 div + 1 mul
+            2: (6, 4), 200: (3, 3), 201: (0, 0), 202: (15, 9), 203: (0, 0), 204: (3, 1), 205: (1, 1)}
 
 
 def f_map(words, cmd_count) -> int:
@@ -113,8 +117,8 @@ def ncu_traffic(workload: str, kernel: str, specialised: bool = False):
 
 
 def cpu_sample_rows(H: int, n: int):
-    step = max(1, H // n)
-    return list(range(step // 2, H, step))[:n]
+    n = max(1, min(n, H))
+    return sorted({min(H - 1, int((i + 0.5) * H / n)) for i in range(n)})  # evenly spaced over the whole frame
 
 
 def run_cpu_oracle(cmd, words, W, H, uniforms, rows):
@@ -444,6 +448,9 @@ def main():
             u0 = scenes.orbit_uniforms(W, H, yaw=yaw0, pitch=pitch)
             rows = cpu_sample_rows(H, 108)
             v, nthreads, dt = run_cpu_oracle(cmd, words, W, H, u0, rows)
+            if dt < 10.0 and len(rows) < H:  # size the sample for 10-30 s of CPU work on this box's cores
+                rows = cpu_sample_rows(H, min(H, max(len(rows) + 1, int(len(rows) * 14.0 / max(dt, 0.05)))))
+                v, nthreads, dt = run_cpu_oracle(cmd, words, W, H, u0, rows)
             line["cpu_baseline"] = {"value": v, "unit": "Mrays/s", "cores": nthreads, "kind": "port",
                                     "sample": f"{len(rows)} evenly spaced rows of the {W}x{H} {scene} frame ({len(rows) * W * 16} rays, {dt:.1f} s)"}
         print(json.dumps(line))

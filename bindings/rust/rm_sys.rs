@@ -15,6 +15,17 @@ use core::ffi::{c_char, c_void};
 pub const RM_OK: i32 = 0;
 pub const RM_E_INVALID_ARG: i32 = -1;
 pub const RM_E_JIT: i32 = -9;
+pub const RM_E_UNSUPPORTED: i32 = -10;
+// command opcodes beyond the reference's four (builder.rs:1-24): the values its #[repr(u32)] enum reserves in comments
+pub const RM_OP_PLANE: u32 = 2;
+pub const RM_OP_INTERSECTION: u32 = 102;
+pub const RM_OP_SMOOTH_UNION: u32 = 103;
+pub const RM_OP_TRANSLATION_PUSH: u32 = 200;
+pub const RM_OP_TRANSLATION_POP: u32 = 201;
+pub const RM_OP_ROTATION_PUSH: u32 = 202;
+pub const RM_OP_ROTATION_POP: u32 = 203;
+pub const RM_OP_SCALE_PUSH: u32 = 204;
+pub const RM_OP_SCALE_POP: u32 = 205;
 pub const RM_MODE_EXACT: i32 = 0;
 pub const RM_MODE_FAST: i32 = 1;
 pub const RM_KERNEL_WAVEFRONT: i32 = 0;
