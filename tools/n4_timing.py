@@ -4,7 +4,9 @@ the EXT interpreter build of the production kernel against the run-time speciali
 the context's stream (rm_mark / rm_elapsed_ms), L2 flushed between frames.  No torch: starts in about a second.
 Prints one JSON line per variant.  Not a BASELINE.json config — bench.py --workload n4 is the full-contract form.
 
-  python tools/n4_timing.py [--width 1920 --height 1080 --frames 10]
+  python tools/n4_timing.py [--width 1920 --height 1080 --frames 10] [--scene S3|short] [--lib other/librm_b200.so]
+--scene short: Translation(SmoothUnion(Sphere, Plane)), 3 decoded instructions -> the 4-rays-per-thread variant.
+--lib: time another build of the library (e.g. one compiled with -DRM_DIRECT_MINB8_EXT=...).
 """
 import argparse
 import importlib
@@ -26,11 +28,20 @@ def main():
     ap.add_argument("--height", type=int, default=1080)
     ap.add_argument("--frames", type=int, default=10)
     ap.add_argument("--scene", default="S3")
+    ap.add_argument("--lib", default=None)
+    ap.add_argument("--variants", default="interpreter,specialised")
     a = ap.parse_args()
     rm = rm_import.load()
+    if a.lib:
+        rm.LIB_PATH = Path(a.lib).resolve()
     scenes = importlib.import_module("ray_marching_b200.scenes")
+    host = importlib.import_module("ray_marching_b200.host")
     W, H = a.width, a.height
-    cmd, words = scenes.program(a.scene)
+    if a.scene == "short":
+        cmd, words = host.build_commands(host.translation(host.binary(host.SMOOTH_UNION, host.sphere((0, 0, 0), 1.0),
+                                                                         host.plane((0, 1, 0), 0.8), 0.5), (0.5, 0.2, 0.0)))
+    else:
+        cmd, words = scenes.program(a.scene)
     u = scenes.orbit_uniforms(W, H, yaw=0.6, pitch=0.4)
     fmap = bench.f_map(words, cmd)
     with rm.Context(0) as ctx:
@@ -43,7 +54,7 @@ def main():
         counters = ctx.get_counters()
         ctx.set_counters(False)
         flops = bench.frame_flops(counters, fmap, W * H)
-        for variant in ("interpreter", "specialised"):
+        for variant in a.variants.split(","):
             if variant == "specialised":
                 ctx.specialize()
             info = ctx.spec_info()
@@ -62,7 +73,8 @@ def main():
                               "Mrays/s": W * H * 16 / (m * 1e-3) / 1e6, "f_map_flops_per_eval": fmap,
                               "frac_of_fp32_peak": flops / (m * 1e-3) / 1e12 / peak["tflops"], "fp32_peak_tflops": peak["tflops"],
                               "rays_per_thread": info["rays_per_thread"] if info["active"] else None,
-                              "counters": [int(x) for x in counters], "cmd_count": int(cmd), "n_words": int(len(words))}))
+                              "counters": [int(x) for x in counters], "cmd_count": int(cmd), "n_words": int(len(words)),
+                              "lib": str(rm.LIB_PATH.name if not a.lib else a.lib)}))
 
 
 if __name__ == "__main__":
