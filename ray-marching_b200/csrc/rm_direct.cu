@@ -35,9 +35,11 @@ constexpr int TILE_W_D = RM_DIRECT_TILE_W;
 #define RM_DIRECT_MINB4 8
 #endif
 // Extended programs (N4: plane, space transforms) also carry the evaluation point q of every ray (3 R registers) through
-// the interpreter loop; fewer resident blocks keep that out of local memory (ptxas -v: see build.log).  Not yet measured.
+// the interpreter loop.  Measured on B200 at 1080p (tools/n4_timing.py, profiles/r1_s17_*): 8-ray variant on scene S3 with
+// 4 / 5 / 6 / 7 resident blocks 21.47 / 21.44 / 21.54 / 20.73 ms; 4-ray variant on a 3-instruction program with
+// 6 / 8 / 10 blocks 2.877 / 2.905 / 3.069 ms.
 #ifndef RM_DIRECT_MINB8_EXT
-#define RM_DIRECT_MINB8_EXT 5
+#define RM_DIRECT_MINB8_EXT 7
 #endif
 #ifndef RM_DIRECT_MINB4_EXT
 #define RM_DIRECT_MINB4_EXT 6
