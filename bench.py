@@ -134,6 +134,18 @@ def run_cpu_oracle(cmd, words, W, H, uniforms, rows):
     return len(rows) * W * 16 / dt / 1e6, nthreads, dt
 
 
+def measure_cpu_baseline(cmd, words, W, H, uniforms, scene, first_rows: int = 108, target_s: float = 14.0) -> dict:
+    """The cpu_baseline object of the JSON line: the CPU oracle port on all host threads, on evenly spaced rows of the
+    workload frame.  A first pass of `first_rows` rows sizes the sample for 10-30 s of CPU work on this box."""
+    rows = cpu_sample_rows(H, first_rows)
+    v, nthreads, dt = run_cpu_oracle(cmd, words, W, H, uniforms, rows)
+    if dt < 10.0 and len(rows) < H:
+        rows = cpu_sample_rows(H, min(H, max(len(rows) + 1, int(len(rows) * target_s / max(dt, 0.05)))))
+        v, nthreads, dt = run_cpu_oracle(cmd, words, W, H, uniforms, rows)
+    return {"value": v, "unit": "Mrays/s", "cores": nthreads, "kind": "port",
+            "sample": f"{len(rows)} evenly spaced rows of the {W}x{H} {scene} frame ({len(rows) * W * 16} rays, {dt:.1f} s)"}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -445,14 +457,7 @@ def main():
             line["e2e"] = {"value": rays_step_total / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": e2e_ms,
                            "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h}
         if not args.no_cpu_baseline and world == 1:
-            u0 = scenes.orbit_uniforms(W, H, yaw=yaw0, pitch=pitch)
-            rows = cpu_sample_rows(H, 108)
-            v, nthreads, dt = run_cpu_oracle(cmd, words, W, H, u0, rows)
-            if dt < 10.0 and len(rows) < H:  # size the sample for 10-30 s of CPU work on this box's cores
-                rows = cpu_sample_rows(H, min(H, max(len(rows) + 1, int(len(rows) * 14.0 / max(dt, 0.05)))))
-                v, nthreads, dt = run_cpu_oracle(cmd, words, W, H, u0, rows)
-            line["cpu_baseline"] = {"value": v, "unit": "Mrays/s", "cores": nthreads, "kind": "port",
-                                    "sample": f"{len(rows)} evenly spaced rows of the {W}x{H} {scene} frame ({len(rows) * W * 16} rays, {dt:.1f} s)"}
+            line["cpu_baseline"] = measure_cpu_baseline(cmd, words, W, H, scenes.orbit_uniforms(W, H, yaw=yaw0, pitch=pitch), scene)
         print(json.dumps(line))
     ctx.close()
     if dist is not None:

@@ -26,8 +26,7 @@ CXX = ["g++", "-O1", "-std=c++17", "-ffp-contract=off", "-fPIC", "-shared", f"-I
 PTS = np.random.default_rng(11).uniform(-4, 4, (1003, 3)).astype(np.float32)  # not a multiple of 8: ragged last group
 
 
-@pytest.fixture(scope="module")
-def hc():
+def load_hostcheck():
     out = HC_DIR / "_build" / "libhostcheck.so"
     out.parent.mkdir(exist_ok=True)
     deps = [HC_DIR / "hostcheck.cpp", HC_DIR / "shim" / "cuda_runtime.h"] + [CSRC / f for f in (
@@ -40,6 +39,11 @@ def hc():
     lib.hc_decode.restype = C.c_int
     lib.hc_decode.argtypes = [C.c_uint32, u32p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_uint32, u32p, C.POINTER(C.c_int), u32p]
     return lib
+
+
+@pytest.fixture(scope="module")
+def hc():
+    return load_hostcheck()
 
 
 def hc_map(lib, cmd, words, pts, exact=True, R=1, force_ext=False):
