@@ -111,15 +111,21 @@ RM_API void rm_destroy(rm_ctx *ctx);
 RM_API int rm_set_limits(rm_ctx *ctx, const void *limits12);
 RM_API int rm_set_mode(rm_ctx *ctx, int mode);
 RM_API int rm_get_mode(rm_ctx *ctx);
+/* Programs that use the N4 commands (RM_OP_PLANE, RM_OP_*_PUSH / _POP) are painted by RM_KERNEL_DIRECT (interpreted or
+ * specialised) and RM_KERNEL_SIMPLE; with one of the two wavefront kernels selected, painting such a program returns
+ * RM_E_UNSUPPORTED. */
 RM_API int rm_set_kernel(rm_ctx *ctx, int kernel);
 /* Opt-in (default 0), RM_KERNEL_DIRECT only: skip the rest of a primitive+operator instruction when a cheap lower bound of
  * the primitive proves the accumulator unchanged.  Output is bit-identical; the work done per map_scene evaluation is not
- * the shader's literal arithmetic any more, so numbers measured with it are reported separately. */
+ * the shader's literal arithmetic any more, so numbers measured with it are reported separately.
+ * Ignored for programs that use the N4 commands (the bounds are written for the reference instruction set). */
 RM_API int rm_set_early_out(rm_ctx *ctx, int on);
 
 /* ---- per frame: replaces RayMarchingCallback::prepare, renderer.rs:196-242 ------------------ */
-/* Validates the program (opcodes, word count, stack discipline), then uploads the 144-byte
- * uniform block and the command words.  Inputs are borrowed for the call only. */
+/* Validates the program (opcodes, word count, stack discipline, transform groups), then uploads the 144-byte
+ * uniform block and the command words.  Inputs are borrowed for the call only.
+ * RM_E_PROGRAM_TOO_LARGE also when a program with deeply nested transform groups decodes to more instructions than the
+ * context's capacity in words (the evaluation point is re-established whenever the chain of groups in force changes). */
 RM_API int rm_prepare(rm_ctx *ctx, const void *uniforms144, uint32_t cmd_count, const uint32_t *words,
                       uint32_t n_words);
 /* Uniform-only update (new camera pose, program unchanged) — SURVEY.md §8(f) N2/N3. */
