@@ -239,6 +239,20 @@ def random_program(rng, n_leaves, right_bias=0.3, ext=False, depth=0):
     return tree(n_leaves, depth)
 
 
+def program_longer_than_its_words(n_leaves: int = 80):
+    """A contrived N4 program that decodes to MORE instructions than it has words: a union chain of leaves, each in its
+    own Scale group, inside 7 nested Translation groups — every leaf's chain differs from the previous one in its last
+    step, so the decoder re-establishes all 8 steps per leaf (11 instructions against 10 words).  -> (words, cmds)"""
+    w, c = scaled(1.5, (sphere((0, 0, 0), 0.3), 1))
+    for i in range(1, n_leaves):
+        lw, lc = scaled(1.5 + 0.01 * i, (sphere((0.1 * i, 0, 0), 0.3), 1))
+        w, c = w + lw + [OP_UNION], c + lc + 1
+    node = (w, c)
+    for d in range(7):
+        node = translated((0.01 * d, 0, 0), node)
+    return node
+
+
 def scene_s0():
     """S0: single default sphere (sphere.rs:33-43 template defaults).  -> (cmd_count, words)"""
     return 1, np.array(sphere((0, 0, 0), 1.0), np.uint32)

@@ -170,6 +170,15 @@ def test_lowering_reuses_a_chain_and_extends_a_prefix(hc):
     assert [int(i[10]) & 1 for i in insns if int(i[9]) in (32, 34)] == [1, 0]
 
 
+def test_instruction_stream_can_outgrow_the_word_stream(hc):
+    # the reason rm_prepare checks the decoded length against the context's capacity (tests/test_n4_gpu.py)
+    words, cmd = h.program_longer_than_its_words()
+    rc, insns, ext, _ = hc_decode(hc, cmd, words)
+    assert rc == 0 and ext and len(insns) > len(words), (len(insns), len(words))
+    pts = PTS[:64]
+    assert same_bits(hc_map(hc, cmd, words, pts, True, 8), h.oracle_map(cmd, words, pts))
+
+
 def test_flops_per_eval_counts_the_sequential_semantics(hc):
     w, c = h.translated((1, 2, 3), (h.sphere((0, 0, 0), 1) + h.plane((0, 1, 0), 1) + [h.OP_UNION], 3))
     w, c = h.scaled(2.0, h.rotated(np.eye(3), (w, c)))

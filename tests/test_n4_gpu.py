@@ -169,29 +169,17 @@ def test_earlier_generation_kernels_refuse_extended_programs(rm, ctx, kernel):
 
 
 def test_instruction_capacity_is_checked(rm):
-    # alternating chains re-establish the evaluation point per primitive: more instructions than words fit
-    words, cmd = [], 0
-    inner = (h.sphere((0, 0, 0), 0.3), 1)
-    for d in range(8):
-        inner = h.scaled(1.0 + 0.01 * d, inner)
-    w, c = inner
-    # (deep, shallow) pairs: every primitive sees a chain that is not an extension of the previous one
-    prog, n = list(w), c
-    for i in range(5):
-        prog += h.sphere((i, 0, 0), 0.2) + [h.OP_UNION] + list(w) + [h.OP_UNION]
-        n += 2 + c + 1
-    with rm.Context(0, max_words=len(prog)) as small:
-        u = h.orbit_uniforms(16, 16)
-        try:
-            small.prepare(u, n, prog)
-            ok = True
-        except rm.RmError as e:
-            ok = False
-            assert e.code == -2
-        # either it fits (and renders exactly) or it is refused with PROGRAM_TOO_LARGE — never a buffer overrun
-        if ok:
-            small.set_mode(rm.MODE_EXACT)
-            assert np.array_equal(small.render(u, n, prog, 16, 16), h.oracle_render(u, n, prog, 16, 16)["rgba"])
+    # a program that decodes to more instructions than it has words (tests/test_hostcheck_cpu.py shows it does): a context
+    # sized for exactly its words refuses it, a larger one renders it — never a buffer overrun
+    words, cmd = h.program_longer_than_its_words()
+    u = h.orbit_uniforms(16, 16)
+    with rm.Context(0, max_words=len(words)) as small:
+        with pytest.raises(rm.RmError) as e:
+            small.prepare(u, cmd, words)
+        assert e.value.code == -2
+    with rm.Context(0, max_words=2 * len(words)) as big:
+        big.set_mode(rm.MODE_EXACT)
+        assert np.array_equal(big.render(u, cmd, words, 16, 16), h.oracle_render(u, cmd, words, 16, 16)["rgba"])
 
 
 def test_host_callback_renders_an_n4_tree(rm):
