@@ -161,6 +161,10 @@ def main():
     ap.add_argument("--early-out", action="store_true",
                     help="opt-in exact early-out of the interpreter (bit-identical output, but NOT the shader's literal arithmetic "
                          "per evaluation: reported separately, never the headline)")
+    ap.add_argument("--e2e", default="serial", choices=["serial", "pipelined"],
+                    help="end-to-end leg of the single-frame workloads.  serial (default): rm_prepare + rm_paint + rm_download per step, "
+                         "each step waits for its frame.  pipelined: the steps go through rm_paint_poses_host, which copies frame k to "
+                         "host memory while frame k+1 renders (every step still uploads its uniforms and returns its frame)")
     ap.add_argument("--gather", default="p2p", choices=["p2p", "nccl"],
                     help="cfg4, N>1: p2p = every rank stores its strips straight into rank 0's frame over NVLink "
                          "(rm_paint_strips_into); nccl = packed bands + NCCL gather + re-order on rank 0")
@@ -370,7 +374,23 @@ def main():
 
     # ---- e2e: host buffers in, host result out, through the public C-ABI calls (cfg1-3: prepare + paint + download)
     e2e_ms_local, h2d, d2h = None, 0, 0
-    if not strong:
+    if not strong and args.e2e == "pipelined":
+        n_e2e = max(3, min(args.steps, 10))
+        ring_frames = 3
+        pinned = rm.PinnedBuffer(ring_frames * W * H * 4)
+        batch = uniforms * n_e2e                   # one 144-byte block per step, in host memory
+        ctx.prepare(uniforms, cmd, words)
+        ctx.paint_poses_host(batch[:2 * 144], 2, W, H, pinned.ptr, W * H * 4, ring_frames)  # warm-up (allocates the device ring)
+        barrier()
+        t0 = time.perf_counter()
+        up0 = ctx.program_uploads
+        ctx.prepare(uniforms, cmd, words)          # unchanged words: only the uniforms are replaced
+        ctx.paint_poses_host(batch, n_e2e, W, H, pinned.ptr, W * H * 4, ring_frames)  # returns with every frame in host memory
+        e2e_ms_local = (time.perf_counter() - t0) * 1e3 / n_e2e
+        h2d, d2h = 144 + 12 + (ctx.program_uploads - up0) * (4 + int(len(words)) * 4) // n_e2e, W * H * 4
+        config["e2e_mode"] = "pipelined: rm_paint_poses_host, frame k copied to host while frame k+1 renders"
+        pinned.free()
+    elif not strong:
         pinned = rm.PinnedBuffer(W * H * 4)
         n_e2e = max(3, min(args.steps, 10))
         for it in range(2 + n_e2e):
