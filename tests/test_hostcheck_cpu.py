@@ -170,6 +170,14 @@ def test_lowering_reuses_a_chain_and_extends_a_prefix(hc):
     assert [int(i[10]) & 1 for i in insns if int(i[9]) in (32, 34)] == [1, 0]
 
 
+def test_documented_instruction_counts(hc):
+    # DESIGN.md 6.4 / profiles/r1_s17_NOTES.md quote these
+    for scene, n_insn, ext in (("S0", 1, False), ("S1", 3, False), ("S2", 32, False), ("S3", 42, True)):
+        cmd, words = h.SCENES[scene]()
+        rc, insns, e, _ = hc_decode(hc, cmd, words)
+        assert rc == 0 and len(insns) == n_insn and e == ext, (scene, len(insns), e)
+
+
 def test_instruction_stream_can_outgrow_the_word_stream(hc):
     # the reason rm_prepare checks the decoded length against the context's capacity (tests/test_n4_gpu.py)
     words, cmd = h.program_longer_than_its_words()
