@@ -6,6 +6,7 @@
 #include <atomic>
 #include <chrono>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -23,6 +24,16 @@ namespace {
 constexpr uint32_t kMaxWordsCap = 3072;  // decoded program must fit in shared memory (48 B/insn)
 constexpr int kEventSlots = 16;
 constexpr size_t kFlushBytes = 256ull << 20;
+// EXPERIMENTAL, off unless RM_N4_COLLAPSE=1 is in the environment: programs with N4 commands prepared in fast mode are
+// decoded with one similarity per primitive instead of one instruction per transform step (rm_program.h).  Exact mode is
+// never affected; without the variable every code path below is what it was.
+bool n4_collapse_enabled() {
+    static const bool on = [] {
+        const char *s = std::getenv("RM_N4_COLLAPSE");
+        return s && s[0] == '1';
+    }();
+    return on;
+}
 }  // namespace
 
 struct rm_ctx {
@@ -55,6 +66,7 @@ struct rm_ctx {
     uint32_t max_iter = 100;
     float uniforms[36] = {};
     Program prog;
+    bool prog_collapsed = false;  // prog was decoded with collapse_chains (RM_N4_COLLAPSE experiment, fast mode only)
     RmInsn *d_prog = nullptr;
     RmInsn *h_prog = nullptr;  // pinned staging
     size_t prog_cap = 0;       // instructions
@@ -249,6 +261,13 @@ int rm_set_limits(rm_ctx *c, const void *limits12) {
 int rm_set_mode(rm_ctx *c, int mode) {
     if (!c || (mode != RM_MODE_EXACT && mode != RM_MODE_FAST)) return RM_E_INVALID_ARG;
     c->mode = mode;
+    // RM_N4_COLLAPSE experiment: the decoded form of an extended program depends on the arithmetic mode
+    if (n4_collapse_enabled() && c->prepared && c->prog.extended && c->prog_collapsed != (mode == RM_MODE_FAST)) {
+        float u[36];
+        std::memcpy(u, c->uniforms, sizeof u);
+        const std::vector<uint32_t> words = c->last_words;
+        return rm_prepare(c, u, c->last_cmd_count, words.data(), (uint32_t)words.size());
+    }
     return RM_OK;
 }
 int rm_get_mode(rm_ctx *c) { return c ? c->mode : RM_E_INVALID_ARG; }
@@ -268,13 +287,15 @@ int rm_prepare(rm_ctx *c, const void *uniforms144, uint32_t cmd_count, const uin
     if (n_words && !words) return fail(c, RM_E_INVALID_ARG, "null words");
     // Same command stream as the one already on the device (the reference re-flattens and re-uploads the tree every
     // frame, renderer.rs:224-239; an editor frame usually changes only the camera): only the uniforms change.
+    const bool want_collapse = n4_collapse_enabled() && c->mode == RM_MODE_FAST;  // false unless RM_N4_COLLAPSE=1
     if (c->prepared && cmd_count == c->last_cmd_count && n_words == c->last_words.size() &&
-        (n_words == 0 || std::memcmp(words, c->last_words.data(), (size_t)n_words * sizeof(uint32_t)) == 0)) {
+        (n_words == 0 || std::memcmp(words, c->last_words.data(), (size_t)n_words * sizeof(uint32_t)) == 0) &&
+        (!c->prog.extended || c->prog_collapsed == want_collapse)) {
         std::memcpy(c->uniforms, uniforms144, RM_UNIFORMS_BYTES);
         return RM_OK;
     }
     Program p;
-    int rc = decode_program(cmd_count, words, n_words, c->max_words, &p);
+    int rc = decode_program(cmd_count, words, n_words, c->max_words, &p, want_collapse);
     if (rc != RM_OK) return fail(c, rc, rm_strerror(rc));
     // an extended program (N4) re-establishes the evaluation point whenever the chain of transforms in force changes, so
     // its instruction stream can be longer than its word stream; the device buffer holds max_words instructions
@@ -283,6 +304,7 @@ int rm_prepare(rm_ctx *c, const void *uniforms144, uint32_t cmd_count, const uin
     // the staging buffer may still be in flight from the previous prepare
     RM_CUDA(c, cudaEventSynchronize(c->upload_done));
     c->prog = std::move(p);
+    c->prog_collapsed = want_collapse && c->prog.extended;
     const size_t n = c->prog.insns.size();
     if (n) {
         std::memcpy(c->h_prog, c->prog.insns.data(), n * sizeof(RmInsn));

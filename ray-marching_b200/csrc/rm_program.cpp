@@ -60,7 +60,41 @@ void finish_flags(RmInsn &in) {
 }
 
 // Programs with N4 commands (see rm_program.h).  `cmds` is the parsed stream; counts and `extended` are set in `prog`.
-int lower_extended(const std::vector<Cmd> &cmds, Program &prog, Program *out) {
+// The similarity q = A*p + b that a chain of pushes (outermost first) amounts to, in double precision.
+struct Frame {
+    double A[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};  // row-major
+    double b[3] = {0, 0, 0};
+    bool linear_is_identity() const {
+        static const double I[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
+        return std::equal(A, A + 9, I);
+    }
+};
+Frame compose_chain(const std::vector<Cmd> &cmds, const std::vector<uint32_t> &chain) {
+    Frame f;
+    for (uint32_t idx : chain) {
+        const Cmd &p = cmds[idx];
+        if (p.type == RM_OP_TRANSLATION_PUSH) {  // q - t
+            for (int i = 0; i < 3; ++i) f.b[i] -= (double)p.p[i];
+        } else if (p.type == RM_OP_ROTATION_PUSH) {  // transpose(M) * q, M row-major in p.p
+            double A2[9], b2[3];
+            for (int i = 0; i < 3; ++i) {
+                for (int j = 0; j < 3; ++j) A2[3 * i + j] = (double)p.p[i] * f.A[j] + (double)p.p[3 + i] * f.A[3 + j] + (double)p.p[6 + i] * f.A[6 + j];
+                b2[i] = (double)p.p[i] * f.b[0] + (double)p.p[3 + i] * f.b[1] + (double)p.p[6 + i] * f.b[2];
+            }
+            std::copy(A2, A2 + 9, f.A);
+            std::copy(b2, b2 + 3, f.b);
+        } else {  // q / s
+            for (double &x : f.A) x /= (double)p.p[0];
+            for (double &x : f.b) x /= (double)p.p[0];
+        }
+    }
+    return f;
+}
+
+// collapse_chains (fast arithmetic only; exact mode has to keep the sequential roundings): each primitive's chain is
+// composed on the host into one similarity q = A*p + b; A becomes ONE "q = transpose(M)*p" instruction (none when the
+// chain only translates), b is folded into the primitive's centre (sphere, box) or offset (plane).
+int lower_extended(const std::vector<Cmd> &cmds, Program &prog, Program *out, bool collapse_chains) {
     const uint32_t n = (uint32_t)cmds.size();
     // pass 2a: value-stack and group discipline, command by command as the sequential semantics would run
     // (same rules as oracle/rm_oracle.c validate_program)
@@ -91,7 +125,7 @@ int lower_extended(const std::vector<Cmd> &cmds, Program &prog, Program *out) {
 
     // pass 2b: resolve the position stack.  Value commands keep their order; every primitive gets the chain of push
     // commands in force (indices into cmds, outermost first); T/R pops vanish, ScalePop becomes acc *= s.
-    struct VCmd { uint32_t cmd; bool accmul; std::vector<uint32_t> chain; };
+    struct VCmd { uint32_t cmd; bool accmul; std::vector<uint32_t> chain; };  // collapse_chains: chain is composed at emission
     std::vector<VCmd> v;
     std::vector<uint32_t> open;
     for (uint32_t i = 0; i < n; ++i) {
@@ -134,6 +168,27 @@ int lower_extended(const std::vector<Cmd> &cmds, Program &prog, Program *out) {
         }
         cur = chain;
     };
+    // collapse_chains: the linear part q currently holds (as the float matrix M = transpose(A) of its instruction)
+    bool cur_identity = true;
+    float cur_m[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
+    auto emit_linear = [&](const Frame &f) {
+        float m[9];
+        for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) m[3 * i + j] = (float)f.A[3 * j + i];
+        const bool ident = f.linear_is_identity();
+        if (ident ? cur_identity : (!cur_identity && std::memcmp(m, cur_m, sizeof m) == 0)) return;
+        RmInsn in{};
+        in.flags = FLAG_XF;
+        in.slot = 1;  // always from the ray position
+        if (ident) {
+            in.op = XOP_RESET;
+        } else {
+            in.op = XOP_ROTATE;
+            in.cx = m[0]; in.cy = m[1]; in.cz = m[2]; in.r0 = m[3]; in.r1 = m[4]; in.r2 = m[5]; in.k = m[6]; in.inv_k = m[7]; in.c4k = m[8];
+        }
+        prog.insns.push_back(in);
+        cur_identity = ident;
+        std::memcpy(cur_m, m, sizeof m);
+    };
     depth = 0;
     const uint32_t nv = (uint32_t)v.size();
     for (uint32_t i = 0; i < nv; ++i) {
@@ -145,8 +200,18 @@ int lower_extended(const std::vector<Cmd> &cmds, Program &prog, Program *out) {
             continue;
         }
         if (!is_binary(c.type)) {
-            emit_chain(v[i].chain);
             in.cx = c.p[0]; in.cy = c.p[1]; in.cz = c.p[2]; in.r0 = c.p[3];
+            if (collapse_chains) {
+                const Frame f = compose_chain(cmds, v[i].chain);
+                emit_linear(f);
+                if (c.type == RM_OP_PLANE) {  // dot(A p + b, n) + h = dot(A p, n) + (dot(b, n) + h)
+                    in.r0 = (float)((double)c.p[3] + f.b[0] * (double)c.p[0] + f.b[1] * (double)c.p[1] + f.b[2] * (double)c.p[2]);
+                } else {  // |A p + b - c| = |A p - (c - b)|
+                    in.cx = (float)((double)c.p[0] - f.b[0]); in.cy = (float)((double)c.p[1] - f.b[1]); in.cz = (float)((double)c.p[2] - f.b[2]);
+                }
+            } else {
+                emit_chain(v[i].chain);
+            }
             uint32_t src = c.type == RM_OP_SPHERE ? SRC_SPHERE : (c.type == RM_OP_BOX ? SRC_BOX : SRC_PLANE);
             if (c.type == RM_OP_BOX) { in.r1 = c.p[4]; in.r2 = c.p[5]; }
             if (depth >= 1 && i + 1 < nv && !v[i + 1].accmul && is_binary(cmds[v[i + 1].cmd].type)) {
@@ -181,7 +246,7 @@ int lower_extended(const std::vector<Cmd> &cmds, Program &prog, Program *out) {
 }  // namespace
 
 int decode_program(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, uint32_t max_words,
-                   Program *out) {
+                   Program *out, bool collapse_chains) {
     if (out) *out = Program();
     if (cmd_count == 0) return RM_OK;  // empty scene: map_scene == max_dist (wgsl:188-191)
     if (!words) return RM_E_INVALID_ARG;
@@ -220,7 +285,7 @@ int decode_program(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, 
             return RM_E_BAD_PARAM;
         cmds.push_back(c);
     }
-    if (prog.extended) return lower_extended(cmds, prog, out);
+    if (prog.extended) return lower_extended(cmds, prog, out, collapse_chains);
 
     // pass 2: stack discipline + emission with top-of-stack caching and prim/op fusion
     uint32_t depth = 0, max_depth = 0;

@@ -130,8 +130,14 @@ struct Program {
 void smooth_constants(float k, float *inv_k, float *c4k, bool *k_pow2);
 
 // Returns an RM_* code (rm_b200.h).  `out` may be null for validation only.
+// collapse_chains (EXPERIMENTAL, only meaningful for extended programs painted in fast mode; off everywhere unless the
+// environment variable RM_N4_COLLAPSE=1 is set, see rm_abi.cu): instead of one instruction per transform step, each
+// primitive's chain of groups is composed on the host (double precision) into one similarity q = A*p + b — A is one
+// "q = transpose(M)*p" instruction, shared by consecutive primitives with the same A and absent for translation-only
+// chains, and b moves into the primitive's centre / the plane's offset.  Not the sequential roundings of the oracle:
+// never used in exact mode.  Not yet measured on a GPU.
 int decode_program(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, uint32_t max_words,
-                   Program *out);
+                   Program *out, bool collapse_chains = false);
 #endif  // !__CUDACC_RTC__
 
 }  // namespace rm

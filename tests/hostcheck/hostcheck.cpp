@@ -41,9 +41,9 @@ extern "C" {
 
 // decoded instruction stream (48-byte RmInsn records) of a command stream; returns the RM_* code of rm_prepare
 int hc_decode(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, uint32_t max_words, void *insns, uint32_t cap,
-              uint32_t *n_insn, int *extended, uint32_t *flops_per_eval) {
+              uint32_t *n_insn, int *extended, uint32_t *flops_per_eval, int collapse_chains) {
     Program p;
-    const int rc = decode_program(cmd_count, words, n_words, max_words, &p);
+    const int rc = decode_program(cmd_count, words, n_words, max_words, &p, collapse_chains != 0);
     if (rc != RM_OK) return rc;
     if (n_insn) *n_insn = (uint32_t)p.insns.size();
     if (extended) *extended = p.extended ? 1 : 0;
@@ -54,10 +54,11 @@ int hc_decode(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, uint3
 
 // map_scene at n points through the interpreter the kernels run: rays_per_thread 1 = map_eval1 (verification kernels),
 // 4 / 8 = map_evalR (production kernel).  force_ext runs a reference-set program through the EXT instantiation too.
+// collapse_chains: the experimental fast-mode lowering of rm_program.h (one similarity per primitive).
 int hc_map(int exact, int rays_per_thread, int force_ext, uint32_t cmd_count, const uint32_t *words, uint32_t n_words, float max_dist,
-           const float *pts, uint64_t n, float *out) {
+           const float *pts, uint64_t n, float *out, int collapse_chains) {
     Program p;
-    const int rc = decode_program(cmd_count, words, n_words, 3072, &p);
+    const int rc = decode_program(cmd_count, words, n_words, 3072, &p, collapse_chains != 0);
     if (rc != RM_OK) return rc;
     const bool ext = p.extended || force_ext;
 #define HC_RUN(EXV, EXTV)                                                            \

@@ -35,9 +35,9 @@ def load_hostcheck():
         subprocess.run(CXX + ["-o", str(out), str(HC_DIR / "hostcheck.cpp")], check=True, capture_output=True)
     lib = C.CDLL(str(out))
     lib.hc_map.restype = C.c_int
-    lib.hc_map.argtypes = [C.c_int, C.c_int, C.c_int, C.c_uint32, u32p, C.c_uint32, C.c_float, f32p, C.c_uint64, f32p]
+    lib.hc_map.argtypes = [C.c_int, C.c_int, C.c_int, C.c_uint32, u32p, C.c_uint32, C.c_float, f32p, C.c_uint64, f32p, C.c_int]
     lib.hc_decode.restype = C.c_int
-    lib.hc_decode.argtypes = [C.c_uint32, u32p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_uint32, u32p, C.POINTER(C.c_int), u32p]
+    lib.hc_decode.argtypes = [C.c_uint32, u32p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_uint32, u32p, C.POINTER(C.c_int), u32p, C.c_int]
     return lib
 
 
@@ -46,23 +46,23 @@ def hc():
     return load_hostcheck()
 
 
-def hc_map(lib, cmd, words, pts, exact=True, R=1, force_ext=False):
+def hc_map(lib, cmd, words, pts, exact=True, R=1, force_ext=False, collapse=False):
     w = np.ascontiguousarray(np.asarray(words, np.uint32))
     pts = np.ascontiguousarray(pts, np.float32)
     out = np.zeros(len(pts), np.float32)
     rc = lib.hc_map(int(exact), R, int(force_ext), cmd, w.ctypes.data_as(u32p), w.size, 100.0, pts.ctypes.data_as(f32p),
-                    len(pts), out.ctypes.data_as(f32p))
+                    len(pts), out.ctypes.data_as(f32p), int(collapse))
     assert rc == 0, rc
     return out
 
 
-def hc_decode(lib, cmd, words, max_words=3072):
+def hc_decode(lib, cmd, words, max_words=3072, collapse=False):
     w = np.ascontiguousarray(np.asarray(words, np.uint32))
     w = w if w.size else np.zeros(1, np.uint32)
     buf = np.zeros(4096 * 12, np.uint32)
     n, ext, fl = C.c_uint32(), C.c_int(), C.c_uint32()
     rc = lib.hc_decode(cmd, w.ctypes.data_as(u32p), int(np.asarray(words).size), max_words, buf.ctypes.data_as(C.c_void_p), 4096,
-                       C.byref(n), C.byref(ext), C.byref(fl))
+                       C.byref(n), C.byref(ext), C.byref(fl), int(collapse))
     return rc, buf[:n.value * 12].reshape(-1, 12), bool(ext.value), fl.value
 
 
@@ -185,6 +185,40 @@ def test_instruction_stream_can_outgrow_the_word_stream(hc):
     assert rc == 0 and ext and len(insns) > len(words), (len(insns), len(words))
     pts = PTS[:64]
     assert same_bits(hc_map(hc, cmd, words, pts, True, 8), h.oracle_map(cmd, words, pts))
+
+
+# ---- experimental fast-mode lowering (RM_N4_COLLAPSE=1): one similarity per primitive ------------------------------
+@pytest.mark.parametrize("seed", range(8))
+def test_collapsed_chains_agree_with_the_oracle_within_fast_mode_tolerance(hc, seed):
+    rng = np.random.default_rng(1300 + seed)
+    for n_leaves in (1, 2, 3, 5, 9, 14, 24):
+        words, cmd = h.random_program(rng, n_leaves, ext=True)
+        ref = h.oracle_map(cmd, words, PTS)
+        rc, insns, ext, _ = hc_decode(hc, cmd, words, collapse=True)
+        rc2, insns2, _, _ = hc_decode(hc, cmd, words)
+        assert rc == 0 and rc2 == 0 and len(insns) <= len(insns2)
+        for R in (1, 4, 8):
+            got = hc_map(hc, cmd, words, PTS, False, R, collapse=True)
+            np.testing.assert_allclose(got, ref, rtol=0, atol=1e-4)
+    # the 8-deep nest collapses to ONE transform instruction + the primitive + the scale pops' multiplications
+    words, cmd = _nest8()
+    rc, insns, _, _ = hc_decode(hc, cmd, words, collapse=True)
+    assert [int(i[9]) for i in insns][:2] == [33, 10] and all(int(i[9]) == 36 for i in insns[2:])
+    np.testing.assert_allclose(hc_map(hc, cmd, words, PTS, False, 8, collapse=True), h.oracle_map(cmd, words, PTS), rtol=0, atol=1e-4)
+
+
+def test_collapsed_s3_is_shorter_and_translation_only_chains_cost_nothing(hc):
+    cmd, words = h.scene_s3()
+    assert len(hc_decode(hc, cmd, words, collapse=True)[1]) == 29 and len(hc_decode(hc, cmd, words)[1]) == 42
+    np.testing.assert_allclose(hc_map(hc, cmd, words, PTS, False, 8, collapse=True), h.oracle_map(cmd, words, PTS), rtol=0, atol=1e-4)
+    # Translate(Union(A, Translate(B))): no transform instruction at all, the offsets moved into the centres
+    inner = (h.sphere((0, 0, 0), 1.0) + h.translated((0, 2, 0), (h.box((1, 0, 0), (0.5, 0.5, 0.5)), 1))[0] + [h.OP_UNION], 5)
+    w, c = h.translated((1, 2, 3), inner)
+    rc, insns, ext, _ = hc_decode(hc, c, w, collapse=True)
+    assert rc == 0 and ext and [int(i[9]) for i in insns] == [4, 12]
+    assert insns[0][:3].view(np.float32).tolist() == [1, 2, 3] and insns[1][:3].view(np.float32).tolist() == [2, 4, 3]
+    # without the flag nothing changes: the default lowering is the sequential one
+    assert [int(i[9]) for i in hc_decode(hc, c, w)[1]] == [32, 4, 32, 12]
 
 
 def test_flops_per_eval_counts_the_sequential_semantics(hc):
