@@ -20,6 +20,10 @@ LIB_PATH = PKG_DIR / "librm_b200.so"
 HOST_LIB_PATH = PKG_DIR / "librm_host.so"
 
 RM_OK = 0
+E_PROGRAM_TOO_LARGE, E_BAD_OPCODE, E_STACK_OVERFLOW, E_STACK_UNBALANCED, E_BAD_PARAM, E_JIT, E_UNSUPPORTED = -2, -3, -4, -5, -8, -9, -10
+# command opcodes (include/rm_b200.h): the reference's four, the two extension operators, and the N4 commands
+OP_SPHERE, OP_BOX, OP_PLANE, OP_UNION, OP_SUBTRACTION, OP_INTERSECTION, OP_SMOOTH_UNION = 0, 1, 2, 100, 101, 102, 103
+OP_TRANSLATION_PUSH, OP_TRANSLATION_POP, OP_ROTATION_PUSH, OP_ROTATION_POP, OP_SCALE_PUSH, OP_SCALE_POP = 200, 201, 202, 203, 204, 205
 MODE_EXACT, MODE_FAST = 0, 1
 KERNEL_WAVEFRONT, KERNEL_SIMPLE, KERNEL_WAVEFRONT2, KERNEL_DIRECT = 0, 1, 2, 3
 UNIFORMS_BYTES, LIMITS_BYTES = 144, 12
