@@ -121,3 +121,13 @@ def test_rust_binding_declares_the_same_functions_with_the_same_arity(rm):
     r_decl = {m.group(1): _arg_count(m.group(2)) for m in re.finditer(r"pub fn (rm_\w+)\s*\(([^)]*)\)", rust)}
     assert set(c_decl) == set(rm.ABI_SYMBOLS)
     assert r_decl == c_decl, {k: (c_decl.get(k), r_decl.get(k)) for k in set(c_decl) | set(r_decl) if c_decl.get(k) != r_decl.get(k)}
+
+
+def test_python_constants_agree_with_the_header(rm):
+    hdr = (Path(__file__).resolve().parent.parent / "include" / "rm_b200.h").read_text()
+    seen = 0
+    for name, val in re.findall(r"RM_(OP_\w+|E_\w+|MODE_\w+|KERNEL_\w+) = (-?\d+)", hdr):
+        if hasattr(rm, name):
+            assert getattr(rm, name) == int(val), (name, val)
+            seen += 1
+    assert seen >= 20
