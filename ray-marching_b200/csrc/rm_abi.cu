@@ -13,6 +13,7 @@
 #include <thread>
 
 #include "../../include/rm_b200.h"
+#include "rm_frame.h"
 #include "rm_jit.h"
 #include "rm_kernels.h"
 #include "rm_program.h"
@@ -126,33 +127,7 @@ int ensure(rm_ctx *c, void **p, size_t *cap, size_t need) {
 }
 
 FrameParams make_params(const rm_ctx *c, const float *u, uint32_t W, uint32_t H, uint32_t row0, uint32_t nrows) {
-    FrameParams fp;
-    std::memcpy(fp.extent, u, 8);
-    std::memcpy(fp.inv_proj, u + 4, 64);
-    std::memcpy(fp.inv_view, u + 20, 64);
-    fp.min_dist = c->limits_f[0];
-    fp.max_dist = c->limits_f[1];
-    fp.max_iter = c->max_iter;
-    fp.W = W; fp.H = H; fp.row0 = row0; fp.nrows = nrows;
-    fp.strip_rows = 0; fp.strip_pitch = 0;
-    fp.dst_frame_rows = 0;
-    fp.n_insn = (uint32_t)c->prog.insns.size();
-    // per-frame ray-generation constants: the shader's expressions, one IEEE float operation at a time
-    // (this file is compiled with -ffp-contract=off; volatile keeps the compiler from folding x*0)
-    for (int r = 0; r < 4; ++r) {
-        volatile float acc = fp.inv_view[r] * 0.0f;
-        acc = acc + fp.inv_view[4 + r] * 0.0f;
-        acc = acc + fp.inv_view[8 + r] * 0.0f;
-        acc = acc + fp.inv_view[12 + r] * 1.0f;
-        fp.ro4[r] = acc;
-    }
-    for (int i = 0; i < 4; ++i) {
-        volatile float off = ((float)i + 0.5f) / 4.0f - 0.5f;
-        volatile float qx = off / fp.extent[0], qy = off / fp.extent[1];
-        fp.sample_ax[i] = qx * 2.0f;
-        fp.sample_ay[i] = qy * 2.0f;
-    }
-    return fp;
+    return make_frame_params(u, c->limits_f[0], c->limits_f[1], c->max_iter, (uint32_t)c->prog.insns.size(), W, H, row0, nrows);
 }
 
 int check_band(rm_ctx *c, uint32_t W, uint32_t H, uint32_t row0, uint32_t nrows) {

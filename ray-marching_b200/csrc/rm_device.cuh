@@ -23,12 +23,14 @@
 #define RM_PTX_MAX_ACC(acc, v) asm("max.f32 %0, %0, %1;" : "+f"(acc) : "f"(v))
 #define RM_PTX_SUB_ACC(acc, v) asm("sub.rn.f32 %0, %0, %1;" : "+f"(acc) : "f"(v))
 #define RM_PTX_FMA_ACC(acc, a, b) asm("fma.rn.f32 %0, %1, %2, %0;" : "+f"(acc) : "f"(a), "f"(b))
+#define RM_OPAQUE_F3(a, b, c) asm volatile("" : "+f"(a), "+f"(b), "+f"(c))  /* scheduling fence: values become opaque */
 #else
 #define RM_PTX_SQRT_APPROX(r, a) ((r) = sqrtf(a))
 #define RM_PTX_MIN_ACC(acc, v) ((acc) = fminf((acc), (v)))
 #define RM_PTX_MAX_ACC(acc, v) ((acc) = fmaxf((acc), (v)))
 #define RM_PTX_SUB_ACC(acc, v) ((acc) = (acc) - (v))
 #define RM_PTX_FMA_ACC(acc, a, b) ((acc) = fmaf((a), (b), (acc)))
+#define RM_OPAQUE_F3(a, b, c) ((void)0)
 #endif
 
 namespace rm {

@@ -48,18 +48,6 @@ constexpr int direct_min_blocks(int R, bool EXT) {
     return EXT ? (R == 8 ? RM_DIRECT_MINB8_EXT : RM_DIRECT_MINB4_EXT) : (R == 8 ? RM_DIRECT_MINB8 : RM_DIRECT_MINB4);
 }
 
-// map_scene through the decoded-program interpreter (program in shared memory, spill slots in the thread's frame)
-template <bool EX, int R, bool EO, bool EXT>
-struct InterpMap {
-    const float4 *prog;
-    uint32_t n_insn;
-    float max_dist;
-    float spill[RM_STACK_MAX - 1][R];
-    __device__ __forceinline__ void operator()(const float (&px)[R], const float (&py)[R], const float (&pz)[R], float (&s)[R]) {
-        map_evalR<EX, R, EO, EXT>(prog, n_insn, max_dist, px, py, pz, s, spill);
-    }
-};
-
 template <bool EX, int R, bool COUNT, bool EO, bool EXT>
 __global__ void __launch_bounds__(DIRECT_THREADS, direct_min_blocks(R, EXT))
 k_direct(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ prog_g, uint8_t *__restrict__ dst, size_t pitch,

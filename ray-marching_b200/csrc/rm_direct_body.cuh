@@ -73,7 +73,7 @@ __device__ __forceinline__ void direct_body(const FrameParams &fp, uint8_t *__re
             py_[r] = A::mad(rdy[r], dist[r], ro[1]);
             pz_[r] = A::mad(rdz[r], dist[r], ro[2]);
         }
-        RM_FOR_R asm volatile("" : "+f"(px_[r]), "+f"(py_[r]), "+f"(pz_[r]));
+        RM_FOR_R RM_OPAQUE_F3(px_[r], py_[r], pz_[r]);
         map(px_, py_, pz_, s);
         const bool last = it + 1 >= fp.max_iter;  // loop bound wgsl:90
         RM_FOR_R {
@@ -131,7 +131,7 @@ __device__ __forceinline__ void direct_body(const FrameParams &fp, uint8_t *__re
                 px_[4 * j + 2] = __fadd_rn(hx[j], en); py_[4 * j + 2] = __fadd_rn(hy[j], ep); pz_[4 * j + 2] = __fadd_rn(hz[j], en);
                 px_[4 * j + 3] = __fadd_rn(hx[j], ep); py_[4 * j + 3] = __fadd_rn(hy[j], ep); pz_[4 * j + 3] = __fadd_rn(hz[j], ep);
             }
-            RM_FOR_R asm volatile("" : "+f"(px_[r]), "+f"(py_[r]), "+f"(pz_[r]));
+            RM_FOR_R RM_OPAQUE_F3(px_[r], py_[r], pz_[r]);
             map(px_, py_, pz_, s);
 #pragma unroll
             for (int j = 0; j < R / 4; ++j) {

@@ -173,6 +173,18 @@ __device__ __forceinline__ void map_evalR(const float4 *__restrict__ prog, uint3
 #undef RM_EVZ
 }
 
+// map_scene through the decoded-program interpreter (program in shared memory, spill slots in the thread's frame)
+template <bool EX, int R, bool EO, bool EXT>
+struct InterpMap {
+    const float4 *prog;
+    uint32_t n_insn;
+    float max_dist;
+    float spill[RM_STACK_MAX - 1][R];
+    __device__ __forceinline__ void operator()(const float (&px)[R], const float (&py)[R], const float (&pz)[R], float (&s)[R]) {
+        map_evalR<EX, R, EO, EXT>(prog, n_insn, max_dist, px, py, pz, s, spill);
+    }
+};
+
 // ---- rare per-ray events, kept OUT OF LINE (one copy each) so that the per-iteration instruction
 // footprint of the persistent loop stays inside the instruction cache (profiles/r1_v1_*: the fully
 // inlined R=4 kernel stalled 4.7 cycles per issue on no_instruction) ------------------------------

@@ -49,13 +49,47 @@ static inline int __float2int_rn(float f) {  // cvt.rni.s32.f32: round to neares
     return (int)rintf(f);
 }
 
-// declared so that the kernel-body templates parse; never called on the host
-extern dim3 threadIdx, blockIdx, blockDim;
-float __shfl_sync(unsigned, float, int);
-unsigned __shfl_sync(unsigned, unsigned, int);
-unsigned __reduce_add_sync(unsigned, unsigned);
-unsigned __ballot_sync(unsigned, int);
-int __popc(unsigned);
-int __ffs(int);
-unsigned long long atomicAdd(unsigned long long *, unsigned long long);
-void __syncthreads();
+// ---- one warp = 32 host threads in lock-step at the warp-collective calls --------------------------------------------
+// tests/hostcheck/hostcheck.cpp runs a kernel body once per lane on its own thread (hc_run_grid); threadIdx / blockIdx
+// are per-thread, and the warp collectives exchange values through a slot array guarded by a barrier.  All 32 lanes of
+// a warp reach every collective (the kernel bodies only use them in warp-uniform control flow with a full mask).
+#include <pthread.h>
+
+struct HcWarp {
+    pthread_barrier_t bar;
+    unsigned slot[32];
+};
+struct dim3;
+extern thread_local dim3 threadIdx, blockIdx, blockDim;  // defined (inline) in hc_grid.h
+extern thread_local HcWarp *hc_warp;                     // the warp this lane belongs to
+extern thread_local int hc_lane;
+
+static inline unsigned hc_exchange(unsigned v, int src) {
+    hc_warp->slot[hc_lane] = v;
+    pthread_barrier_wait(&hc_warp->bar);
+    const unsigned r = hc_warp->slot[src & 31];
+    pthread_barrier_wait(&hc_warp->bar);
+    return r;
+}
+static inline unsigned __shfl_sync(unsigned, unsigned v, int src) { return hc_exchange(v, src); }
+static inline float __shfl_sync(unsigned, float v, int src) { return __uint_as_float(hc_exchange(__float_as_uint(v), src)); }
+static inline unsigned __reduce_add_sync(unsigned, unsigned v) {
+    hc_warp->slot[hc_lane] = v;
+    pthread_barrier_wait(&hc_warp->bar);
+    unsigned s = 0;
+    for (int i = 0; i < 32; ++i) s += hc_warp->slot[i];
+    pthread_barrier_wait(&hc_warp->bar);
+    return s;
+}
+static inline unsigned __ballot_sync(unsigned, int pred) {
+    hc_warp->slot[hc_lane] = pred ? 1u : 0u;
+    pthread_barrier_wait(&hc_warp->bar);
+    unsigned m = 0;
+    for (int i = 0; i < 32; ++i) m |= hc_warp->slot[i] << i;
+    pthread_barrier_wait(&hc_warp->bar);
+    return m;
+}
+static inline int __popc(unsigned x) { return __builtin_popcount(x); }
+static inline int __ffs(int x) { return __builtin_ffs(x); }
+static inline unsigned long long atomicAdd(unsigned long long *p, unsigned long long v) { return __atomic_fetch_add(p, v, __ATOMIC_RELAXED); }
+void __syncthreads();  // block-wide barriers only occur in the kernel wrappers (.cu files), which the host check does not compile

@@ -21,7 +21,7 @@ import helpers as h
 HC_DIR = Path(__file__).resolve().parent / "hostcheck"
 CSRC = h.ROOT / "ray-marching_b200" / "csrc"
 u32p, f32p = C.POINTER(C.c_uint32), C.POINTER(C.c_float)
-CXX = ["g++", "-O1", "-std=c++17", "-ffp-contract=off", "-fPIC", "-shared", f"-I{HC_DIR / 'shim'}", f"-I{CSRC}", "-w"]
+CXX = ["g++", "-O1", "-std=c++17", "-ffp-contract=off", "-fPIC", "-shared", "-pthread", f"-I{HC_DIR / 'shim'}", f"-I{CSRC}", "-w"]
 
 PTS = np.random.default_rng(11).uniform(-4, 4, (1003, 3)).astype(np.float32)  # not a multiple of 8: ragged last group
 
@@ -29,8 +29,9 @@ PTS = np.random.default_rng(11).uniform(-4, 4, (1003, 3)).astype(np.float32)  # 
 def load_hostcheck():
     out = HC_DIR / "_build" / "libhostcheck.so"
     out.parent.mkdir(exist_ok=True)
-    deps = [HC_DIR / "hostcheck.cpp", HC_DIR / "shim" / "cuda_runtime.h"] + [CSRC / f for f in (
-        "rm_program.cpp", "rm_program.h", "rm_device.cuh", "rm_wavefront_common.cuh", "rm_wavefront.h")]
+    deps = [HC_DIR / "hostcheck.cpp", HC_DIR / "hc_grid.h", HC_DIR / "shim" / "cuda_runtime.h"] + [CSRC / f for f in (
+        "rm_program.cpp", "rm_program.h", "rm_device.cuh", "rm_wavefront_common.cuh", "rm_wavefront.h", "rm_direct_body.cuh",
+        "rm_frame.h")]
     if not out.exists() or out.stat().st_mtime < max(d.stat().st_mtime for d in deps):
         subprocess.run(CXX + ["-o", str(out), str(HC_DIR / "hostcheck.cpp")], check=True, capture_output=True)
     lib = C.CDLL(str(out))
