@@ -173,6 +173,21 @@ def test_fast_mode_on_the_host_is_inside_the_gates(hc):
         assert ((got["cls"] == 2) != (ref["cls"] == 2)).any(-1).mean() <= 2e-3, name
 
 
+def test_collapsed_lowering_through_the_whole_kernel_body_is_inside_the_gates(hc):
+    # RM_N4_COLLAPSE experiment (rm_program.h): one similarity per primitive, fast mode only
+    cmd, words = h.scene_s3()
+    W, H = 48, 27
+    u = h.orbit_uniforms(W, H, yaw=0.6, pitch=0.4)
+    ref = h.oracle_render(u, cmd, words, W, H, aov=True)
+    got = paint(hc, cmd, words, u, W, H, exact=-1, aov=True)
+    d = np.abs(got["rgba"].astype(int) - ref["rgba"].astype(int)).max(-1)
+    assert (d > 2).mean() <= 2e-3
+    assert ((got["cls"] == 2) != (ref["cls"] == 2)).any(-1).mean() <= 2e-3
+    both = (got["cls"] == 2) & (ref["cls"] == 2)
+    rel = np.abs(got["t"][both] - ref["t"][both]) / np.maximum(np.abs(ref["t"][both]), 1e-6)
+    assert (rel > 1e-4).mean() <= 2e-3
+
+
 # ---- the run-time generated kernel (rm_jit.cu): the emitted `rm_spec` function itself, compiled for the host -------------
 SPEC_DRIVER = """
 #include "rm_frame.h"
