@@ -105,7 +105,8 @@ def ncu_traffic(workload: str, kernel: str, specialised: bool = False):
     workload + kernel (profiles/*.ncu_summary.csv), or None.  Not measured live: a profiler is never in a timed run."""
     name = {("cfg3", "wavefront2", False): "r1_s3_wavefront2_R8_cfg3.ncu_summary.csv",
             ("cfg3", "direct", False): "r1_final_direct_R8_cfg3.ncu_summary.csv",
-            ("cfg3", "direct", True): "r1_s14_spec_R2_cfg3.ncu_summary.csv"}.get((workload, kernel, specialised))
+            ("cfg3", "direct", True): "r1_s14_spec_R2_cfg3.ncu_summary.csv",
+            ("n4", "direct", True): "r1_s17_spec_R4_s3.ncu_summary.csv"}.get((workload, kernel, specialised))
     if not name or not (ROOT / "profiles" / name).exists():
         return None, None
     tot, unit_scale = 0.0, {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
