@@ -34,6 +34,7 @@
  *   round = rintf under the default RNE mode (Q7); f32→i32 saturating, NaN→0 (Q6).
  *   unorm8 = floor(clamp(v,0,1)*255 + 0.5).
  */
+#include <float.h>
 #include <math.h>
 #include <stdint.h>
 #include <stdlib.h>
@@ -235,11 +236,15 @@ static int validate_program(uint32_t cmd_count, const uint32_t *w, uint32_t n_wo
         default: return RMO_E_BAD_PROGRAM;
         }
         if (ptr + np > n_words) return RMO_E_BAD_PROGRAM;
+        /* NaN parameters are refused (the product's decoder does the same): with them min/max as `(b < a) ? b : a` and
+         * as IEEE minNum/maxNum differ, and the shader's own result is NaN everywhere */
+        for (uint32_t j = 0; j < np; ++j) { float f = f_bits(w[ptr + j]); if (f != f) return RMO_E_BAD_PROGRAM; }
+        if (t == 103u) { float k = f_bits(w[ptr]); if (!(k > 0.0f) || k > FLT_MAX) return RMO_E_BAD_PROGRAM; }
         if (pops == -1) { /* push: opens a group that must produce exactly one value */
             if (psp >= RMO_POS_STACK_MAX) return RMO_E_BAD_PROGRAM;
             if (t == 204u) {
                 float s = f_bits(w[ptr]);
-                if (!(s > 0.0f) || s > 3.0e38f) return RMO_E_BAD_PROGRAM;
+                if (!(s > 0.0f) || s > FLT_MAX) return RMO_E_BAD_PROGRAM;
             }
             g_op[psp] = t; g_sp[psp] = sp; g_s[psp] = (t == 204u) ? w[ptr] : 0u;
             ++psp;

@@ -44,6 +44,10 @@ struct rm_ctx {
     cudaStream_t stream = nullptr;
     cudaEvent_t events[kEventSlots] = {};
     cudaEvent_t upload_done = nullptr;
+    // recorded behind every paint on the stream it was launched on: the kernels stage d_prog block by block for as long
+    // as they run, so the next program upload (ctx stream) has to wait for it
+    cudaEvent_t paint_done = nullptr;
+    bool paint_pending = false;
     int mode = RM_MODE_EXACT;
     int kernel = RM_KERNEL_DIRECT;
     bool prepared = false;
@@ -180,6 +184,7 @@ int rm_create_ex(int cuda_device, uint32_t max_words, rm_ctx **out) {
     bool ok = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) == cudaSuccess;
     for (int i = 0; ok && i < kEventSlots; ++i) ok = cudaEventCreate(&c->events[i]) == cudaSuccess;
     ok = ok && cudaEventCreateWithFlags(&c->upload_done, cudaEventDisableTiming) == cudaSuccess;
+    ok = ok && cudaEventCreateWithFlags(&c->paint_done, cudaEventDisableTiming) == cudaSuccess;
     c->prog_cap = max_words;
     ok = ok && cudaMalloc(&c->d_prog, c->prog_cap * sizeof(RmInsn)) == cudaSuccess;
     ok = ok && cudaMallocHost(&c->h_prog, c->prog_cap * sizeof(RmInsn)) == cudaSuccess;
@@ -204,6 +209,7 @@ void rm_destroy(rm_ctx *c) {
     wavefront_destroy(&c->wf);
     for (auto &e : c->events) if (e) cudaEventDestroy(e);
     if (c->upload_done) cudaEventDestroy(c->upload_done);
+    if (c->paint_done) cudaEventDestroy(c->paint_done);
     if (c->d_prog) cudaFree(c->d_prog);
     if (c->h_prog) cudaFreeHost(c->h_prog);
     for (void *p : c->shared_opened) cudaIpcCloseMemHandle(p);
@@ -281,6 +287,11 @@ int rm_prepare(rm_ctx *c, const void *uniforms144, uint32_t cmd_count, const uin
     c->prog = std::move(p);
     c->prog_collapsed = want_collapse && c->prog.extended;
     const size_t n = c->prog.insns.size();
+    // paints still running on a caller-supplied stream read d_prog until they finish: the upload goes behind them
+    if (c->paint_pending) {
+        RM_CUDA(c, cudaStreamWaitEvent(c->stream, c->paint_done, 0));
+        c->paint_pending = false;
+    }
     if (n) {
         std::memcpy(c->h_prog, c->prog.insns.data(), n * sizeof(RmInsn));
         RM_CUDA(c, cudaMemcpyAsync(c->d_prog, c->h_prog, n * sizeof(RmInsn), cudaMemcpyHostToDevice, c->stream));

@@ -283,6 +283,10 @@ int decode_program(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, 
         ptr += np;
         if ((c.type == RM_OP_SMOOTH_UNION || c.type == RM_OP_SCALE_PUSH) && !(c.p[0] > 0.0f && std::isfinite(c.p[0])))
             return RM_E_BAD_PARAM;
+        // A NaN parameter makes every distance NaN in the shader; the kernels' min / max (fminf / fmaxf drop a NaN
+        // operand) and the literal `(b < a) ? b : a` of the restatement then part ways, so it is refused here and by
+        // the oracle's validator alike.  Infinite values are accepted (a box radius of +inf is a slab).
+        for (uint32_t j = 0; j < np; ++j) if (c.p[j] != c.p[j]) return RM_E_BAD_PARAM;
         cmds.push_back(c);
     }
     if (prog.extended) return lower_extended(cmds, prog, out, collapse_chains);

@@ -1,4 +1,5 @@
 // host_abi.cpp — extern "C" view of the C++ host (include/rm_host.h).
+#include <stdexcept>
 #include <cmath>
 #include <cstring>
 #include <memory>
@@ -194,7 +195,16 @@ int rmh_graph_set_vec3(int g, int node, const char *param, const float v[3]) {
 }
 int rmh_graph_connect(int g, int from, int to, const char *param) {
     if (!GRAPH_OK(g)) return RMH_E_INVALID;
-    return guarded([&] { g_graphs[g].connect(from, to, param); return 0; });
+    try {
+        g_graphs[g].connect(from, to, param);
+    } catch (const std::invalid_argument &e) {  // DataType mismatch: the editor refuses the connection, nothing panics
+        g_err = e.what();
+        return RMH_E_INVALID;
+    } catch (const std::exception &e) {
+        g_err = e.what();
+        return RMH_E_PANIC;
+    }
+    return 0;
 }
 int rmh_graph_disconnect(int g, int to, const char *param) {
     if (!GRAPH_OK(g)) return RMH_E_INVALID;

@@ -51,6 +51,11 @@ void CSGNodeGraph::connect(NodeId from_node, NodeId to_node, const std::string &
     if (to_node < 0 || to_node >= (NodeId)nodes_.size() || !nodes_[to_node].alive) throw std::out_of_range("node id");
     for (auto &in : nodes_[to_node].inputs)
         if (in.name == to_param) {
+            // csg_node_graph.rs:17-22,84-101: ports carry a DataType and the editor only joins ports of EQUAL type.  Every
+            // node's single output is DataType::CSGNode ("SDF", :153-158), so a Scalar / Vec3 input refuses the connection
+            // (left as it was) instead of failing later in to_vec3().unwrap()
+            if (in.value.tag != ValueType::Tag::CSGNode)
+                throw std::invalid_argument("DataType mismatch: an SDF output cannot feed the Scalar / Vec3 input " + to_param);
             in.connection = from_node;
             return;
         }

@@ -49,6 +49,11 @@ def test_strerror_covers_codes(rm):
     (h.sphere((0, 0, 0), 1) * 2 + [103, h.fbits(0.0)], 3, -8),
     (h.sphere((0, 0, 0), 1) * 2 + [103, h.fbits(float("nan"))], 3, -8),
     (h.sphere((0, 0, 0), 1) * 2 + [103, h.fbits(0.25)], 3, 0),
+    # NaN parameters are refused (the shader's result would be NaN everywhere); infinite radii are accepted (a slab)
+    ([0, h.fbits(float("nan")), 0, 0, h.fbits(1.0)], 1, -8),
+    ([1, 0, 0, 0, h.fbits(1.0), h.fbits(float("nan")), h.fbits(1.0)], 1, -8),
+    ([1, 0, 0, 0, h.fbits(float("inf")), h.fbits(1.0), h.fbits(float("inf"))], 1, 0),
+    ([200, 0, h.fbits(float("nan")), 0] + h.sphere((0, 0, 0), 1) + [201], 3, -8),
     # N4 (plane, space-transform groups)
     (h.plane((0, 1, 0), 1.5), 1, 0),
     (h.translated((1, 2, 3), (h.sphere((0, 0, 0), 1), 1))[0], 3, 0),
@@ -63,6 +68,14 @@ def test_validate_program_codes(rm, words, count, code):
     assert rm.validate_program(count, words) == code
 
 
+def test_nan_and_bad_k_are_refused_by_the_oracle_validator_too():
+    assert h.oracle_validate(1, [0, h.fbits(float("nan")), 0, 0, h.fbits(1.0)]) != 0
+    assert h.oracle_validate(1, [1, 0, 0, 0, h.fbits(float("inf")), h.fbits(1.0), h.fbits(float("inf"))]) == 0
+    two = h.sphere((0, 0, 0), 1) * 2
+    for k, ok in ((0.25, True), (0.0, False), (-1.0, False), (float("inf"), False), (float("nan"), False), (3.2e38, True)):
+        assert (h.oracle_validate(3, two + [103, h.fbits(k)]) == 0) == ok, k
+
+
 def test_validation_agrees_with_oracle_on_random_streams(rm):
     rng = np.random.default_rng(0)
     ops = [0, 1, 100, 101, 102, 103, 7, 2, 200, 201, 202, 203, 204, 205]
@@ -73,7 +86,10 @@ def test_validation_agrees_with_oracle_on_random_streams(rm):
         for _ in range(n):
             t = ops[rng.integers(7 if it < 3000 else len(ops))]
             words.append(t)
-            words += [h.fbits([0.5, 0.25][rng.integers(2)] if it >= 3000 else rng.uniform(0.1, 1))] * {
+            val = [0.5, 0.25][rng.integers(2)] if it >= 3000 else rng.uniform(0.1, 1)
+            if rng.random() < 0.03:
+                val = [float("nan"), float("inf"), 0.0, -0.5, 3.2e38][rng.integers(5)]
+            words += [h.fbits(val)] * {
                 0: 4, 1: 6, 103: 1, 2: 4, 200: 3, 202: 9, 204: 1, 205: 1}.get(t, 0)
         if rng.random() < 0.1:
             words = words[:-1]

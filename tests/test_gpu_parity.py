@@ -225,12 +225,18 @@ def test_limits_are_runtime_values(rm, ctx):
         assert np.array_equal(img, ref), lim
 
 
-def test_pose_batch_matches_single_frames(rm, ctx):
+@pytest.mark.parametrize("kernel", ["direct", "simple", "wavefront", "wavefront2"])
+@pytest.mark.parametrize("max_iter", [100, 70000])
+def test_pose_batch_matches_single_frames(rm, ctx, kernel, max_iter):
+    """Also with the kernels that park per-sample codes in ctx-wide scratch (simple, and the wavefront kernels' max_iter >
+    65535 path): their frames must not overlap on two streams."""
     import torch
     cmd, words = h.scene_s1()
     W, H, n = 128, 72, 5
     poses = [h.orbit_uniforms(W, H, yaw=2 * np.pi * k / n, pitch=0.4) for k in range(n)]
     ctx.set_mode(rm.MODE_FAST)
+    ctx.set_kernel({"wavefront": rm.KERNEL_WAVEFRONT, "simple": rm.KERNEL_SIMPLE, "wavefront2": rm.KERNEL_WAVEFRONT2, "direct": rm.KERNEL_DIRECT}[kernel])
+    ctx.set_limits(0.01, 100.0, max_iter)
     singles = [ctx.render(p, cmd, words, W, H) for p in poses]
     buf = torch.empty((n, H, W, 4), dtype=torch.uint8, device="cuda:0")
     ctx.prepare(poses[0], cmd, words)
@@ -260,6 +266,31 @@ def test_pose_batch_to_host_matches_single_frames(rm, ctx):
     for k in range(n - ring, n):  # the last `ring` poses are the ones left in the wrapping host ring
         assert np.array_equal(got[k % ring], singles[k]), k
     buf.free()
+
+
+def test_prepare_of_new_words_waits_for_paints_on_a_caller_stream(rm, ctx):
+    """the kernels stage d_prog block by block while they run; rm_prepare with different words right behind
+    a paint on an EXTERNAL stream must not overwrite the program under it."""
+    import torch
+    W, H = 1920, 1080                      # long enough a kernel (interpreter, exact mode) for the upload to land inside it
+    cmd2, w2 = h.scene_s2()
+    cmd1, w1 = h.scene_s1()
+    u = h.orbit_uniforms(W, H, yaw=0.6, pitch=0.4)
+    ctx.set_mode(rm.MODE_EXACT)
+    alone = ctx.render(u, cmd2, w2, W, H)
+    st = torch.cuda.Stream(torch.device("cuda", 0))
+    buf = torch.zeros((H, W, 4), dtype=torch.uint8, device="cuda:0")
+    for _ in range(3):
+        buf.zero_()
+        torch.cuda.synchronize()
+        ctx.prepare(u, cmd2, w2)
+        ctx.paint(W, H, 0, H, buf.data_ptr(), W * 4, st.cuda_stream)
+        ctx.prepare(u, cmd1, w1)            # different words, immediately
+        ctx.sync()
+        st.synchronize()
+        assert np.array_equal(buf.cpu().numpy(), alone)
+    small = ctx.render(h.orbit_uniforms(96, 54, yaw=0.6, pitch=0.4), cmd1, w1, 96, 54)   # and the new program is in force
+    assert np.array_equal(small, h.oracle_render(h.orbit_uniforms(96, 54, yaw=0.6, pitch=0.4), cmd1, w1, 96, 54)["rgba"])
 
 
 def test_program_is_uploaded_only_when_the_words_change(rm, ctx):

@@ -184,6 +184,23 @@ def test_graph_evaluate_root(host):
     assert g.evaluate_root() == host.NONE
 
 
+def test_graph_connect_refuses_a_data_type_mismatch(host):
+    # csg_node_graph.rs:17-22,84-101: the editor only joins ports of equal DataType; every node output is an SDF
+    g = host.Graph()
+    root = g.add_root()
+    sp, bx, un = g.add_node(host.SPHERE), g.add_node(host.BOX), g.add_node(host.UNION)
+    assert g.connect(bx, sp, "center") == host.E_INVALID    # SDF -> Vec3
+    assert g.connect(bx, sp, "radius") == host.E_INVALID    # SDF -> Scalar
+    assert g.connect(sp, bx, "radius") == host.E_INVALID    # SDF -> Vec3 (box radius)
+    sm = g.add_node(host.SMOOTH_UNION)
+    assert g.connect(sp, sm, "k") == host.E_INVALID
+    assert g.connect(sp, sm, "A") == 0 and g.connect(bx, sm, "B") == 0 and g.connect(sm, root, "SDF") == 0
+    # the refused connections left the inputs as they were: the tree is SmoothUnion(Sphere default, Box default)
+    cnt, w = host.build_commands(g.evaluate_root())
+    assert cnt == 3 and w.tolist() == h.sphere((0, 0, 0), 1.0) + h.box((0, 0, 0), (1, 1, 1)) + [h.OP_SMOOTH_UNION, w.tolist()[-1]]
+    assert g.connect(un, un, "nope") == host.E_PANIC         # unknown port: still where the reference would panic
+
+
 def test_graph_evaluator_memoises_shared_nodes(host):
     # csg_node_graph.rs:284-289: output_cache — a node feeding two inputs is evaluated once
     g = host.Graph()

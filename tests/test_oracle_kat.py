@@ -132,3 +132,105 @@ def test_k8_stack_depth_limits():
     assert h.oracle_validate(63, right_deep) == 0
     left_deep = s + (s + [h.OP_UNION]) * 40       # depth 2, any length
     assert h.oracle_validate(81, left_deep) == 0
+
+
+# ---- round 2: the four shader facts VERDICT r1 listed as not yet pinned by any KAT ---------------------------------
+def _sample_rays(u: bytes, W: int, H: int, px: int, py: int):
+    """fs_main's 16 sample rays of pixel (px, py) restated in float64 from the shader text (wgsl:39-62 + the A1 closed
+    form) — independent of the oracle's C.  -> (origin[3], dirs[16, 3]) with sample index 4*i + j, i -> x, j -> y."""
+    f = np.frombuffer(u, np.float32).astype(np.float64)
+    ext, ip, iv = f[0:2], f[4:20].reshape(4, 4).T, f[20:36].reshape(4, 4).T
+    ro = iv @ np.array([0.0, 0.0, 0.0, 1.0])
+    sx, sy = (px + 0.5) / W * 2 - 1, 1 - (py + 0.5) / H * 2
+    dirs = []
+    for i in range(4):
+        for j in range(4):
+            off = (np.array([i, j], np.float64) + 0.5) / 4 - 0.5
+            p = np.array([sx, sy]) + off / ext * 2.0
+            d4 = iv @ (ip @ np.array([p[0], p[1], -1.0, 1.0])) - ro
+            dirs.append((d4 / np.linalg.norm(d4))[:3])
+    return ro[:3], np.array(dirs)
+
+
+def test_k9_q2_surfaces_facing_away_from_the_light_are_lit():
+    # wgsl:100-103: direction_to_light = normalize(pos - light) points FROM the light, so the point of the unit sphere
+    # opposite the light (2,-5,3) has dot(normal, l) = +1 and shows the full albedo, while the point facing the light has
+    # dot = -1 and gets the 0.02 floor.  K2 pinned only the floor; this pins the lit side.
+    c, w = h.scene_s0()
+    L = np.array([2.0, -5.0, 3.0])
+    away = -L / np.linalg.norm(L)
+    r = h.oracle_trace(c, w, (away * 5).astype(np.float32), (-away).astype(np.float32))
+    assert r["cls"] == 2 and abs(r["t"] - 4.0) < 1e-5
+    np.testing.assert_allclose(r["rgb"], [0.4, 0.7, 0.1], atol=4e-3)   # normal from 1e-4 central differences in f32
+    r = h.oracle_trace(c, w, (-away * 5).astype(np.float32), away.astype(np.float32))
+    np.testing.assert_allclose(r["rgb"], [0.008, 0.014, 0.002], rtol=1e-6)
+    # the same through the whole pass: orbit camera placed opposite the light, centre pixel = gamma(albedo)
+    pitch = math.asin(away[1])
+    yaw = math.atan2(-away[0], away[2])   # eye = (-sin(yaw) cos(pitch), sin(pitch), cos(yaw) cos(pitch)) * radius
+    eye, _ = h.orbit_camera(radius=5.0, yaw=yaw, pitch=pitch)
+    np.testing.assert_allclose(eye, away * 5, atol=1e-9)
+    img = h.oracle_render(h.orbit_uniforms(64, 48, yaw=yaw, pitch=pitch), c, w, 64, 48)["rgba"]
+    expect = np.floor(np.sqrt([0.4, 0.7, 0.1]) * 255 + 0.5)
+    assert np.abs(img[24, 32, :3].astype(int) - expect).max() <= 1, (img[24, 32], expect)
+
+
+@pytest.mark.parametrize("x,ix_rne,ix_half_away", [(2.0, 2, 3), (3.0, 4, 4), (0.0, 0, 1), (-1.0, 0, -1), (-2.0, -2, -2), (4.0, 4, 5)])
+def test_k10_checker_index_rounds_half_to_even(x, ix_rne, ix_half_away):
+    # wgsl:125: ipos = vec2<i32>(round(pos + .5)); WGSL round = ties to even (Q7).  A ray straight down from (x, 1, 0.25)
+    # lands on the floor at exactly (x, 0.25): x + 0.5 is a tie, z + 0.5 = 0.75 -> 1.  Empty scene: no hit, 100 steps.
+    r = h.oracle_trace(0, [], [x, 1.0, 0.25], [0.0, -1.0, 0.0])
+    assert r["cls"] == 1 and r["t"] == 2.5
+    col = (ix_rne ^ 1) & 1
+    np.testing.assert_allclose(r["rgb"], np.float32([0.1, 0.1, 0.2]) + np.float32(0.2) * np.float32(col), rtol=1e-6)
+    if ((ix_half_away ^ 1) & 1) != col:  # the cases that tell ties-to-even from ties-away
+        other = np.float32([0.1, 0.1, 0.2]) + np.float32(0.2) * np.float32((ix_half_away ^ 1) & 1)
+        assert np.abs(r["rgb"] - other).max() > 0.1
+
+
+def test_k11_sample_order_i_is_x_and_j_is_y():
+    # wgsl:44-56: aa_offset = (vec2(i, j) + 0.5)/4 - 0.5 — the OUTER loop index i offsets x, the inner j offsets y, and
+    # pt_screen.y points up (A1).  Sample s = 4*i + j.  On the sphere's left silhouette edge (vertical at mid height)
+    # the hit pattern of a pixel depends on i only and the hits are the samples with the LARGER i (further right); on
+    # its top edge (horizontal at the centre column) it depends on j only and the hits are the SMALLER j (further down).
+    c, w = h.scene_s0()
+    W, H = 640, 480
+    u = h.orbit_uniforms(W, H)
+    out = h.oracle_render(u, c, w, W, H, aov=True)
+    hit = (out["cls"] == 2).reshape(H, W, 4, 4)  # [.., i, j]
+    row = H // 2
+    mixed = [x for x in range(W // 2) if 0 < hit[row, x].sum() < 16]
+    assert mixed, "no partially covered pixel on the left edge"
+    pat = hit[row, mixed[0]]
+    assert (pat == pat[:, :1]).all(), pat          # constant along j
+    per_i = pat[:, 0]
+    assert per_i[-1] and not per_i[0] and (np.diff(per_i.astype(int)) >= 0).all(), per_i   # hits at larger i (right)
+    col = W // 2
+    mixed_y = [y for y in range(H // 2) if 0 < hit[y, col].sum() < 16]
+    assert mixed_y, "no partially covered pixel on the top edge"
+    pat = hit[mixed_y[0], col]
+    assert (pat == pat[:1, :]).all(), pat          # constant along i
+    per_j = pat[0, :]
+    assert per_j[0] and not per_j[-1] and (np.diff(per_j.astype(int)) <= 0).all(), per_j   # hits at smaller j (lower)
+    # and the rays themselves: fs_main's sample rays restated from the text reproduce the oracle's per-sample classes
+    for px, py in ((mixed[0], row), (col, mixed_y[0])):
+        ro, dirs = _sample_rays(u, W, H, px, py)
+        cls = [h.oracle_trace(c, w, ro.astype(np.float32), d.astype(np.float32))["cls"] for d in dirs]
+        assert cls == out["cls"][py, px].tolist()
+
+
+def test_k12_gamma_is_applied_per_sample_before_the_mean():
+    # wgsl:68-73: color = sqrt(color) per sample, THEN the 16 are averaged.  With an odd height and pitch 0 the horizon
+    # runs through the middle of the centre row: 8 samples of such a pixel see the sky (0), 8 the far floor.
+    c, w = h.scene_s0()
+    W, H = 64, 49
+    u = h.orbit_uniforms(W, H)
+    out = h.oracle_render(u, c, w, W, H, aov=True)
+    px, py = 3, H // 2
+    cls = out["cls"][py, px]
+    assert sorted(set(cls.tolist())) == [0, 1] and (cls == 1).sum() == 8
+    ro, dirs = _sample_rays(u, W, H, px, py)
+    cols = np.array([h.oracle_trace(c, w, ro.astype(np.float32), d.astype(np.float32))["rgb"] for d in dirs], np.float64)
+    gamma_then_mean = np.floor(np.clip(np.sqrt(cols).sum(0) / 16, 0, 1) * 255 + 0.5)
+    mean_then_gamma = np.floor(np.clip(np.sqrt(cols.sum(0) / 16), 0, 1) * 255 + 0.5)
+    assert np.abs(gamma_then_mean - mean_then_gamma).max() > 10       # the two orders are far apart for this pixel
+    assert np.abs(out["rgba"][py, px, :3].astype(int) - gamma_then_mean).max() <= 1, (out["rgba"][py, px], gamma_then_mean)
