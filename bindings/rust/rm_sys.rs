@@ -79,6 +79,8 @@ extern "C" {
     pub fn rm_shared_frame_close(ctx: *mut RmCtx, dev_ptr: *mut c_void) -> i32;
     pub fn rm_copy_to_host(ctx: *mut RmCtx, dev_ptr: *const c_void, host: *mut c_void, bytes: usize,
                            cuda_stream: *mut c_void) -> i32;
+    pub fn rm_copy_strips_to_host(ctx: *mut RmCtx, band_dev: *const c_void, w: u32, h: u32, strip_rows: u32, first_strip: u32,
+                                  strip_step: u32, host_frame: *mut c_void, cuda_stream: *mut c_void) -> i32;
     pub fn rm_paint_poses(ctx: *mut RmCtx, uniforms144_array: *const u8, n_poses: u32, w: u32, h: u32,
                           dst_rgba8_dev: *mut c_void, pitch_bytes: usize, frame_stride_bytes: usize,
                           cuda_stream: *mut c_void) -> i32;
@@ -119,6 +121,8 @@ extern "C" {
     pub fn rm_launch_count(ctx: *mut RmCtx) -> u64;
     pub fn rm_host_alloc(bytes: usize) -> *mut c_void;
     pub fn rm_host_free(p: *mut c_void);
+    pub fn rm_host_register(p: *mut c_void, bytes: usize) -> i32;
+    pub fn rm_host_unregister(p: *mut c_void) -> i32;
 
     pub fn rm_last_error(ctx: *mut RmCtx) -> *const c_char;
     pub fn rm_strerror(code: i32) -> *const c_char;

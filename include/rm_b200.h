@@ -203,6 +203,13 @@ RM_API int rm_shared_frame_open(rm_ctx *ctx, const void *handle64, void **dev_pt
 RM_API int rm_shared_frame_close(rm_ctx *ctx, void *dev_ptr);
 /* Device -> host copy of any device pointer this process can address; synchronises the stream. */
 RM_API int rm_copy_to_host(rm_ctx *ctx, const void *dev_ptr, void *host, size_t bytes, void *cuda_stream);
+/* Config 4 end to end: copies the strips a shard painted PACKED (rm_paint_strips with the same plan; band_dev NULL = the
+ * ctx-owned buffer) to their rows of a whole W x H frame in HOST memory (pitch 4*W) — one strided cudaMemcpy2DAsync
+ * (plus one for a partial last strip) on the stream, then synchronises it.  With one process per GPU and host_frame a
+ * buffer every process has page-locked (rm_host_register of one shared mapping) the frame leaves over all the GPUs' PCIe
+ * links at once instead of through GPU 0's. */
+RM_API int rm_copy_strips_to_host(rm_ctx *ctx, const void *band_dev, uint32_t W, uint32_t H, uint32_t strip_rows,
+                                  uint32_t first_strip, uint32_t strip_step, void *host_frame, void *cuda_stream);
 /* Pose batch (config 5): paints n_poses frames from an array of 144-byte uniform blocks held in
  * HOST memory; frame p goes to dst + p*frame_stride_bytes (device memory), or, when dst is NULL,
  * every frame overwrites the ctx-owned buffer (throughput mode). */
@@ -284,6 +291,10 @@ RM_API uint64_t rm_launch_count(rm_ctx *ctx);
 /* Pinned host memory for rm_download / e2e runs. */
 RM_API void *rm_host_alloc(size_t bytes);
 RM_API void rm_host_free(void *p);
+/* Page-locks (cudaHostRegister, portable) / releases host memory the caller owns, e.g. a POSIX shared-memory mapping
+ * that several processes copy their strips into (rm_copy_strips_to_host).  0 or RM_E_CUDA. */
+RM_API int rm_host_register(void *p, size_t bytes);
+RM_API int rm_host_unregister(void *p);
 
 RM_API const char *rm_last_error(rm_ctx *ctx);
 RM_API const char *rm_strerror(int code);

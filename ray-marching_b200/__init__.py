@@ -32,7 +32,7 @@ UNIFORMS_BYTES, LIMITS_BYTES = 144, 12
 ABI_SYMBOLS = [
     "rm_create", "rm_create_ex", "rm_destroy", "rm_set_limits", "rm_set_mode", "rm_get_mode", "rm_set_kernel", "rm_set_early_out",
     "rm_prepare", "rm_prepare_uniforms", "rm_program_uploads", "rm_validate_program", "rm_paint", "rm_paint_strips", "rm_paint_strips_into", "rm_shared_frame_create", "rm_shared_frame_open",
-    "rm_shared_frame_close", "rm_copy_to_host", "rm_paint_poses", "rm_paint_poses_host", "rm_download",
+    "rm_shared_frame_close", "rm_copy_to_host", "rm_copy_strips_to_host", "rm_host_register", "rm_host_unregister", "rm_paint_poses", "rm_paint_poses_host", "rm_download",
     "rm_sync", "rm_paint_debug", "rm_paint_aov", "rm_map", "rm_set_counters", "rm_get_counters", "rm_mark", "rm_elapsed_ms",
     "rm_flush_l2", "rm_fp32_peak", "rm_launch_count", "rm_host_alloc", "rm_host_free", "rm_last_error",
     "rm_strerror", "rm_version",
@@ -93,6 +93,9 @@ def lib() -> C.CDLL:
             "rm_shared_frame_open": (i, [vp, vp, C.POINTER(vp)]),
             "rm_shared_frame_close": (i, [vp, vp]),
             "rm_copy_to_host": (i, [vp, vp, vp, sz, vp]),
+            "rm_copy_strips_to_host": (i, [vp, vp, u32, u32, u32, u32, u32, vp, vp]),
+            "rm_host_register": (i, [vp, sz]),
+            "rm_host_unregister": (i, [vp]),
             "rm_download": (i, [vp, vp, sz]),
             "rm_sync": (i, [vp]),
             "rm_paint_debug": (i, [vp, u32, u32, u32, u32, vp, vp, vp, vp]),
@@ -166,6 +169,19 @@ def spec_compile_check(cmd_count: int, words, mode: int = MODE_FAST, rays_per_th
     rc = lib().rm_spec_compile_check(cmd_count, w.ctypes.data if w.size else None, w.size, mode, rays_per_thread,
                                      C.byref(cb), C.byref(ms), log, 16384)
     return {"rc": rc, "cubin_bytes": int(cb.value), "compile_ms": ms.value, "log": log.value.decode(errors="replace")}
+
+
+def host_register(ptr: int, nbytes: int) -> None:
+    """Page-locks caller-owned host memory (e.g. a shared-memory mapping) so that device copies into it are DMA."""
+    rc = lib().rm_host_register(ptr, nbytes)
+    if rc != RM_OK:
+        raise RmError(rc, "rm_host_register failed")
+
+
+def host_unregister(ptr: int) -> None:
+    rc = lib().rm_host_unregister(ptr)
+    if rc != RM_OK:
+        raise RmError(rc, "rm_host_unregister failed")
 
 
 class PinnedBuffer:
@@ -308,6 +324,11 @@ class Context:
         assert out.flags["C_CONTIGUOUS"]
         self._chk(self._L.rm_copy_to_host(self._h, dev_ptr, out.ctypes.data, nbytes or out.nbytes, stream))
         return out
+
+    def copy_strips_to_host(self, band_ptr: int | None, W: int, H: int, strip_rows: int, first_strip: int, strip_step: int,
+                            host_frame_ptr: int, stream: int | None = None):
+        """Packed strips of this shard (band_ptr None = the ctx-owned buffer) -> their rows of a whole host frame."""
+        self._chk(self._L.rm_copy_strips_to_host(self._h, band_ptr, W, H, strip_rows, first_strip, strip_step, host_frame_ptr, stream))
 
     def paint_poses(self, uniforms_array: bytes, n_poses: int, W: int, H: int, dst_ptr: int | None = None,
                     pitch: int = 0, frame_stride: int = 0, stream: int | None = None):

@@ -58,3 +58,45 @@ def test_reference_arm_prints_one_contract_line():
     assert d["impl"] == "reference" and d["unit"] == "Mrays/s" and d["value"] > 0 and d["vs_baseline"] is None
     assert d["e2e"] == {"value": d["value"], "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
     assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["value"] == d["value"] and "workload" in d["config"]
+
+
+def test_reference_arm_maps_nothing_of_the_product():
+    """the CPU arm must not load librm_b200.so / librm_host.so — only the oracle."""
+    code = ("import sys; sys.argv = ['bench.py', '--impl', 'reference', '--workload', 'cfg1', '--steps', '1', '--warmup', '3'];"
+            f"sys.path.insert(0, {str(ROOT)!r}); import bench; bench.main();"
+            "maps = open('/proc/self/maps').read();"
+            "print('MAPPED', sorted({ln.split('/')[-1].strip() for ln in maps.splitlines() if 'librm_' in ln}));"
+            "print('MODS', sorted(m for m in sys.modules if 'ray_marching' in m or m == 'rm_import' or m == 'torch'))")
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert "MAPPED ['librm_oracle.so']" in r.stdout, r.stdout[-500:]
+    assert "MODS []" in r.stdout, r.stdout[-500:]
+    d = json.loads([ln for ln in r.stdout.splitlines() if ln.startswith("{")][0])
+    assert "ms_per_step_covers" in d and "bounded sample" in d["ms_per_step_covers"] and d["ms_whole_step_at_this_rate"] > 0
+
+
+def test_parity_stats_gates():
+    rng = np.random.default_rng(0)
+    ref = rng.integers(0, 255, (3, 40, 4), dtype=np.uint8)
+    cls = rng.integers(0, 3, (3, 40, 16), dtype=np.uint8)
+    t = rng.uniform(1, 9, (3, 40, 16)).astype(np.float32)
+    s = bench.parity_stats(ref.copy(), ref, cls.copy(), cls, t.copy(), t)
+    assert s["rgba_identical"] and s["aov_identical"] and s["gates_ok"] and s["hitmask_pix_frac"] == 0 and s["t_rel_max"] == 0
+    img = ref.copy()
+    img[0, 0, 0] = (int(ref[0, 0, 0]) + 3) % 256 if ref[0, 0, 0] < 250 else ref[0, 0, 0] - 3
+    cls2 = cls.copy()
+    cls2[1, 5, 3] = 2 if cls[1, 5, 3] != 2 else 0
+    t2 = t.copy()
+    both = (cls == 2) & (cls2 == 2)
+    idx = tuple(np.argwhere(both)[0])
+    t2[idx] *= np.float32(1.01)
+    s = bench.parity_stats(img, ref, cls2, cls, t2, t)
+    assert s["rgba_max"] == 3 and abs(s["rgba_gt2_frac"] - 1 / 120) < 1e-9 and abs(s["hitmask_pix_frac"] - 1 / 120) < 1e-9
+    assert 0.009 < s["t_rel_max"] < 0.011 and not s["gates_ok"] and not s["aov_identical"]
+
+
+def test_hbm_peak_comes_from_measured_peaks_json():
+    p = bench.measured_peaks()
+    if (ROOT / "MEASURED_PEAKS.json").exists():
+        assert p["hbm_gbs"] == json.loads((ROOT / "MEASURED_PEAKS.json").read_text())["hbm_gbs"]
+    assert "6531.9" not in (ROOT / "bench.py").read_text()
