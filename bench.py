@@ -327,6 +327,7 @@ class Rig:
             except rm.RmError as e:  # no NVRTC on the box, or the program is too long: the interpreter kernel runs, and the line says so
                 spec["reason"] = str(e)[:300]
             spec.update({k: v for k, v in ctx.spec_info().items() if k in ("active", "rays_per_thread", "min_blocks", "compile_ms", "cubin_bytes")})
+            spec["tier"] = {0: "interpreter", 1: "structure (parameters as kernel arguments)", 2: "literal (parameters as immediates)"}[ctx.spec_tier]
         return spec
 
     def counters_of(self, count_step):
@@ -339,7 +340,7 @@ class Rig:
 
 def kernel_label(args, spec) -> str:
     if spec.get("active"):
-        return f"direct+specialised(rm_spec,R={spec.get('rays_per_thread')})"
+        return f"direct+specialised(rm_spec,R={spec.get('rays_per_thread')},{spec.get('tier', '?').split(' ')[0]} tier)"
     return args.kernel + ("+interpreter" if args.kernel == "direct" else "")
 
 
@@ -664,17 +665,22 @@ def parity_object(rig: Rig, args, W, H, uniforms, cmd, words, oracle_rows: dict,
                      "t_rel_note": "the north star states no percentile; applied as <= 1e-4 on >= 99.9 % of the samples hit by both (a flipped "
                                    "d < min_dist moves one sample by one march step); the observed max and fraction are printed with it"}}
     ctx.prepare(uniforms, cmd, words)
-    legs = ([("timed_kernel", True)] if spec.get("active") else []) + [("interpreter", False)]
-    for name, use_spec in legs:
+    legs = ([("timed_kernel", True), ("structure_tier", True)] if spec.get("active") else []) + [("interpreter", False)]
+
+    def select(name, use_spec):
+        ctx.set_spec_literal_after(0 if name == "structure_tier" else 8)
         if use_spec:
             ctx.specialize()
         else:
             ctx.set_specialize(False)
+
+    for name, use_spec in legs:
+        select(name, use_spec)
         img, cls, t, was_spec = aov_rows()
         st = parity_stats(img, ref_img, cls, ref_cls, t, ref_t)
-        st["kernel"] = kernel_label(args, spec) if use_spec else "direct+interpreter"
+        st["kernel"] = (kernel_label(args, spec) if name == "timed_kernel" else "direct+specialised(structure tier)") if use_spec else "direct+interpreter"
         st["aov_run_specialised"] = bool(was_spec)
-        if timed_frame is not None and (use_spec or not spec.get("active")):
+        if timed_frame is not None and (name == "timed_kernel" or not spec.get("active")):
             tf = timed_frame[rows]
             st["timed_frame_rows"] = parity_stats(tf, ref_img)
             st["aov_rgba_equals_timed_frame_rows"] = bool(np.array_equal(tf, img))
@@ -690,10 +696,7 @@ def parity_object(rig: Rig, args, W, H, uniforms, cmd, words, oracle_rows: dict,
     ident = {}
     for name, use_spec in legs:
         try:
-            if use_spec:
-                ctx.specialize()
-            else:
-                ctx.set_specialize(False)
+            select(name, use_spec)
             img, cls, t, _ = aov_rows()
             ident[name] = bool(np.array_equal(img, ref_img) and np.array_equal(cls, ref_cls)
                                and np.array_equal(t.view(np.uint32), ref_t.view(np.uint32)))
@@ -702,6 +705,7 @@ def parity_object(rig: Rig, args, W, H, uniforms, cmd, words, oracle_rows: dict,
     out["exact_mode_rows_identical"] = bool(all(v is True for v in ident.values()))
     out["exact_mode_rows_identical_detail"] = ident
     ctx.set_mode(mode0)
+    ctx.set_spec_literal_after(8)
     ctx.set_specialize(False)
     if spec.get("active"):
         ctx.specialize()
@@ -765,9 +769,11 @@ def b200_arm(args) -> int:
 
         spec = rig.specialise(args)
         if spec["requested"]:
-            spec["note"] = ("map_scene of this command stream compiled into the kernel at run time (NVRTC), once per program and outside the "
-                            "timed region, like the reference's shader compile at start-up; same arithmetic per ray, exact mode bit-identical "
-                            "to the oracle")
+            spec["note"] = ("map_scene of this command stream compiled into the kernel at run time (NVRTC) outside the timed region, like the "
+                            "reference's shader compile at start-up.  Two tiers: one kernel per program STRUCTURE with the values as kernel "
+                            "arguments (an edit of a value costs no compile), and, for words that stay put — this static scene — one with the "
+                            "values as immediates (the headline; value_structure_tier is the other).  Same arithmetic per ray, exact mode "
+                            "bit-identical to the oracle")
         counters = rig.counters_of(step)  # work counters of this rank's step (untimed) -> algorithmic FLOPs
 
         for _ in range(warm):
@@ -797,6 +803,15 @@ def b200_arm(args) -> int:
             interp = {"ms": interp_ms, "ms_local": interp_ms_local, "steps": n_i}
             spec["interpreter_ms_per_step_this_rank"] = interp_ms_local
             ctx.specialize()  # back on (a cache hit) for the end-to-end leg
+            # and through the structure-tier kernel: what paints right after an edit of a value
+            ctx.set_spec_literal_after(0)
+            step()
+            rig.barrier()
+            if ctx.spec_tier == 1:
+                st_ms_local = float(np.mean(rig.time_steps(step, n_i)))
+                (st_ms,) = rig.max_over_ranks(st_ms_local)
+                extra["_structure"] = {"ms": st_ms, "ms_local": st_ms_local}
+            ctx.set_spec_literal_after(8)
         elif args.kernel == "direct" and not args.early_out:
             interp = {"ms": None, "ms_local": ms_local, "steps": args.steps}
 
@@ -871,6 +886,9 @@ def b200_arm(args) -> int:
         if interp:
             roof["achieved_interpreter"] = flops / (interp["ms_local"] * 1e-3) / 1e12
             roof["frac_interpreter"] = roof["achieved_interpreter"] / peak["tflops"]
+        structure = extra.pop("_structure", None)
+        if structure:
+            roof["frac_structure_tier"] = flops / (structure["ms_local"] * 1e-3) / 1e12 / peak["tflops"]
         line = {"metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": warm,
                 "ms_per_step": ms, "fps": (n_poses if strong else world) * 1e3 / ms, "higher_is_better": True,
                 "scaling": "strong" if strong else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -882,6 +900,9 @@ def b200_arm(args) -> int:
             line["ms_per_step_interpreter"] = ims
             line["interpreter_note"] = ("the decoded-program interpreter kernel (k_direct) over the same steps in the same harness: what paints "
                                         "until a program has been compiled")
+        if structure:
+            line["value_structure_tier"] = rays_step_total / (structure["ms"] * 1e-3) / 1e6
+            line["ms_per_step_structure_tier"] = structure["ms"]
         line["e2e"] = e2e
         if cpu_base:
             line["cpu_baseline"] = cpu_base

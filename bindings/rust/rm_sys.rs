@@ -64,6 +64,11 @@ extern "C" {
                           buf: *mut c_char, cap: usize, needed: *mut usize) -> i32;
     pub fn rm_spec_compile_check(cmd_count: u32, words: *const u32, n_words: u32, mode: i32, rays_per_thread: i32,
                                  cubin_bytes: *mut u64, compile_ms: *mut f64, log: *mut c_char, log_cap: usize) -> i32;
+    pub fn rm_spec_params(cmd_count: u32, words: *const u32, n_words: u32, mode: i32, buf: *mut f32, cap_floats: usize,
+                          needed: *mut usize) -> i32;
+    pub fn rm_set_spec_literal_after(ctx: *mut RmCtx, n_paints: u32) -> i32;
+    pub fn rm_spec_tier(ctx: *mut RmCtx) -> i32;
+    pub fn rm_spec_cache(new_capacity: u64, entries: *mut u64, capacity: *mut u64, evictions: *mut u64) -> i32;
 
     // per frame — RayMarchingCallback::paint (renderer.rs:244-255)
     pub fn rm_paint(ctx: *mut RmCtx, w: u32, h: u32, row0: u32, nrows: u32, dst_rgba8_dev: *mut c_void,

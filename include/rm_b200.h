@@ -139,26 +139,40 @@ RM_API int rm_validate_program(uint32_t cmd_count, const uint32_t *words, uint32
 
 /* ---- program specialisation (optional; the reference compiles its shader once, RayMarchingResources::new
  *      renderer.rs:55-62 — here the SCENE can be compiled too) --------------------------------------------------- */
-/* By default the kernels interpret the decoded command stream: any program, no set-up cost.  A program that is painted
- * many times (a static scene, a turntable) can instead be compiled: map_scene is emitted as straight-line CUDA — every
- * constant an immediate, no fetch or dispatch — and built at run time (NVRTC, sm_100a) around the same kernel body.
- * Arithmetic per ray is operation for operation the interpreter's: exact mode stays bit-identical, fast mode may round
- * differently where the compiler contracts multiply-adds (within the parity gates).  Compiling takes of the order of a
- * second per (program, mode) and is cached process-wide (up to 512 programs; beyond that new programs stay on the
- * interpreter), so the contexts of a group share it.  Only RM_KERNEL_DIRECT
- * paints are affected; with rm_set_early_out on, the interpreter is used.
+/* By default the kernels interpret the decoded command stream: any program, no set-up cost.  A program can instead be
+ * compiled: map_scene is emitted as straight-line CUDA — no fetch, no dispatch — and built at run time (NVRTC, sm_100a)
+ * around the same kernel body.  The generated code depends on the program's STRUCTURE only: the opcode sequence, which
+ * parameters are exactly zero (those stay literals so that `p - 0` folds) and, in exact mode, which smooth-union k are
+ * powers of two.  Every other centre, radius, k, offset or matrix entry travels as a kernel argument (constant bank: an
+ * operand of the arithmetic instruction itself, no load, no register).  So the reference's per-frame re-flatten and
+ * re-upload (renderer.rs:224-239) and an editor dragging a value keep their compiled kernel: rm_prepare with new values
+ * of the same structure costs no compile.  Arithmetic per ray is operation for operation the interpreter's: exact mode
+ * stays bit-identical, fast mode may round differently where the compiler contracts multiply-adds (within the parity
+ * gates).  Compiling takes 0.2 - 1 s per (structure, mode) and is cached process-wide — shared by the contexts of a
+ * group, bounded LRU (512 structures by default, rm_spec_cache): the least recently used kernel no context is painting
+ * with is unloaded.  Only RM_KERNEL_DIRECT paints are affected; with rm_set_early_out on, the interpreter is used.
  * rm_specialize: compile the currently prepared program for the current mode now; paints use it until rm_prepare
- *   receives different words.  RM_E_JIT (reason in rm_last_error) when NVRTC cannot be loaded (libnvrtc.so.12; the
- *   environment variable RM_NVRTC_PATH names an exact file), the compile fails or the program is too long for the
- *   instruction cache — painting then simply continues through the interpreter.
+ *   receives words of a different structure.  RM_E_JIT (reason in rm_last_error) when NVRTC cannot be loaded
+ *   (libnvrtc.so.12; the environment variable RM_NVRTC_PATH names an exact file), the compile fails or the program is
+ *   too long for the instruction cache — painting then simply continues through the interpreter.
  * rm_set_specialize(1): do that automatically for every program at its first paint (a stall of one compile per new
- *   program: meant for batch rendering, not for interactive editing); failures are silent, see rm_spec_status.
- *   rm_set_specialize(2): the same without the stall — the program is compiled by a background thread of the context
- *   while paints keep going through the interpreter, and the first paint after the compile has finished switches over
- *   (a compile for words that have changed meanwhile is dropped): the setting for an interactive editor.
+ *   STRUCTURE: meant for batch rendering); failures are silent, see rm_spec_status.
+ *   rm_set_specialize(2): the same without the stall — a kernel already in the cache is adopted at once, a new
+ *   structure is compiled by a background thread of the context while paints keep going through the interpreter, and
+ *   the first paint after the compile has finished switches over: the setting for an interactive editor.
  *   rm_set_specialize(0) returns to the interpreter from the next paint on (also after rm_specialize). */
 RM_API int rm_specialize(rm_ctx *ctx);
 RM_API int rm_set_specialize(rm_ctx *ctx, int on);
+/* Second tier.  On sm_100 an arithmetic instruction takes an immediate for free but a kernel-argument value only through
+ * a uniform register (LDCU, one issue slot per 1-4 values): the deep scene's march loop is ~5 % longer with arguments.
+ * Words that STAY PUT are therefore compiled once more with every parameter an immediate (keyed by the whole word
+ * stream): after n_paints plain paints of unchanged words the context looks that kernel up, else compiles it on its
+ * background thread — never a stall, whatever the policy — and switches over when it is ready; rm_specialize compiles
+ * it at once.  New values of the same structure drop back to the structure kernel without a compile.
+ * n_paints: default 8; 0 = structure tier only.  rm_spec_tier: what the next plain paint runs — 0 the interpreter,
+ * 1 the structure kernel, 2 the literal kernel. */
+RM_API int rm_set_spec_literal_after(rm_ctx *ctx, uint32_t n_paints);
+RM_API int rm_spec_tier(rm_ctx *ctx);
 /* Whether the next RM_KERNEL_DIRECT paint (current mode, counters setting) runs specialised code, and what it is:
  * sample rays per thread (2, 4, 8: chosen from the code size), resident blocks asked of the compiler, compile + load
  * time, cubin size; number of compiles this context triggered and of specialised launches.  Any pointer may be NULL. */
@@ -166,12 +180,19 @@ RM_API int rm_spec_info(rm_ctx *ctx, int *active, int *rays_per_thread, int *min
                         uint64_t *cubin_bytes, uint64_t *compiles, uint64_t *launches);
 RM_API const char *rm_spec_status(rm_ctx *ctx);
 /* No device needed: the generated CUDA source of a command stream (rays_per_thread 0 = automatic), and a trial
- * compile of it (NVRTC cross-compiles for sm_100a without a GPU). */
+ * compile of it (NVRTC cross-compiles for sm_100a without a GPU).  mode | RM_SPEC_LITERAL_TIER: the literal tier's. */
+#define RM_SPEC_LITERAL_TIER 0x100
 RM_API int rm_spec_source(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, int mode, int rays_per_thread,
                           char *buf, size_t cap, size_t *needed);
 RM_API int rm_spec_compile_check(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, int mode,
                                  int rays_per_thread, uint64_t *cubin_bytes, double *compile_ms, char *log,
                                  size_t log_cap);
+/* The parameter block the generated kernel of these words reads (its SpecParams argument): *needed floats. */
+RM_API int rm_spec_params(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, int mode, float *buf,
+                          size_t cap_floats, size_t *needed);
+/* Process-wide kernel cache: new_capacity > 0 sets the LRU bound (evicting down to it); reports entries, bound and
+ * evictions so far.  Any pointer may be NULL. */
+RM_API int rm_spec_cache(uint64_t new_capacity, uint64_t *entries, uint64_t *capacity, uint64_t *evictions);
 
 /* ---- per frame: replaces RayMarchingCallback::paint, renderer.rs:244-255 -------------------- */
 /* Shades rows [row0,row0+nrows) of a W×H frame (row 0 = top) as RGBA8 (R,G,B,A bytes; A=255).

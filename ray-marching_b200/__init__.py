@@ -25,6 +25,7 @@ E_PROGRAM_TOO_LARGE, E_BAD_OPCODE, E_STACK_OVERFLOW, E_STACK_UNBALANCED, E_BAD_P
 OP_SPHERE, OP_BOX, OP_PLANE, OP_UNION, OP_SUBTRACTION, OP_INTERSECTION, OP_SMOOTH_UNION = 0, 1, 2, 100, 101, 102, 103
 OP_TRANSLATION_PUSH, OP_TRANSLATION_POP, OP_ROTATION_PUSH, OP_ROTATION_POP, OP_SCALE_PUSH, OP_SCALE_POP = 200, 201, 202, 203, 204, 205
 MODE_EXACT, MODE_FAST = 0, 1
+SPEC_LITERAL_TIER = 0x100  # or-ed into the mode of spec_source / spec_compile_check: the literal tier's kernel
 KERNEL_WAVEFRONT, KERNEL_SIMPLE, KERNEL_WAVEFRONT2, KERNEL_DIRECT = 0, 1, 2, 3
 UNIFORMS_BYTES, LIMITS_BYTES = 144, 12
 
@@ -37,7 +38,7 @@ ABI_SYMBOLS = [
     "rm_flush_l2", "rm_fp32_peak", "rm_launch_count", "rm_host_alloc", "rm_host_free", "rm_last_error",
     "rm_strerror", "rm_version",
     "rm_group_create", "rm_group_destroy", "rm_group_size", "rm_group_ctx", "rm_group_set_mode", "rm_group_set_limits",
-    "rm_specialize", "rm_set_specialize", "rm_spec_info", "rm_spec_status", "rm_spec_source", "rm_spec_compile_check",
+    "rm_specialize", "rm_set_specialize", "rm_spec_info", "rm_spec_status", "rm_spec_source", "rm_spec_compile_check", "rm_spec_params", "rm_spec_cache", "rm_set_spec_literal_after", "rm_spec_tier",
     "rm_group_specialize", "rm_group_prepare", "rm_group_paint_bands", "rm_group_frame", "rm_group_paint_poses", "rm_group_last_error",
 ]
 
@@ -120,6 +121,10 @@ def lib() -> C.CDLL:
             "rm_spec_status": (C.c_char_p, [vp]),
             "rm_spec_source": (i, [u32, vp, u32, i, i, C.c_char_p, sz, C.POINTER(sz)]),
             "rm_spec_compile_check": (i, [u32, vp, u32, i, i, C.POINTER(u64), C.POINTER(C.c_double), C.c_char_p, sz]),
+            "rm_spec_params": (i, [u32, vp, u32, i, vp, sz, C.POINTER(sz)]),
+            "rm_set_spec_literal_after": (i, [vp, u32]),
+            "rm_spec_tier": (i, [vp]),
+            "rm_spec_cache": (i, [u64, C.POINTER(u64), C.POINTER(u64), C.POINTER(u64)]),
             "rm_group_specialize": (i, [vp]),
             "rm_group_create": (i, [C.POINTER(i), i, C.POINTER(vp)]),
             "rm_group_destroy": (None, [vp]),
@@ -160,6 +165,25 @@ def spec_source(cmd_count: int, words, mode: int = MODE_FAST, rays_per_thread: i
     buf = C.create_string_buffer(need.value)
     lib().rm_spec_source(cmd_count, w.ctypes.data if w.size else None, w.size, mode, rays_per_thread, buf, need.value, None)
     return buf.value.decode()
+
+
+def spec_params(cmd_count: int, words, mode: int = MODE_FAST) -> np.ndarray:
+    """The parameter block (float32) the generated kernel of these words reads: its non-zero parameters in stream order."""
+    w = _words_arr(words)
+    need = C.c_size_t()
+    rc = lib().rm_spec_params(cmd_count, w.ctypes.data if w.size else None, w.size, mode, None, 0, C.byref(need))
+    if rc != RM_OK:
+        raise RmError(rc, lib().rm_strerror(rc).decode())
+    out = np.zeros(max(1, need.value), np.float32)
+    lib().rm_spec_params(cmd_count, w.ctypes.data if w.size else None, w.size, mode, out.ctypes.data, out.size, None)
+    return out[:need.value]
+
+
+def spec_cache(new_capacity: int = 0) -> dict:
+    """Process-wide specialised-kernel cache: optionally sets the LRU bound; -> {entries, capacity, evictions}."""
+    n, cap, ev = C.c_uint64(), C.c_uint64(), C.c_uint64()
+    lib().rm_spec_cache(new_capacity, C.byref(n), C.byref(cap), C.byref(ev))
+    return {"entries": int(n.value), "capacity": int(cap.value), "evictions": int(ev.value)}
 
 
 def spec_compile_check(cmd_count: int, words, mode: int = MODE_FAST, rays_per_thread: int = 0) -> dict:
@@ -257,6 +281,15 @@ class Context:
     def set_specialize(self, on):
         """0 / False: interpreter; 1 / True: compile every program at its first paint; 2: compile in the background."""
         self._chk(self._L.rm_set_specialize(self._h, int(on)))
+
+    def set_spec_literal_after(self, n_paints: int):
+        """Literal tier: adopted after n_paints plain paints of unchanged words (0 = structure tier only; default 8)."""
+        self._chk(self._L.rm_set_spec_literal_after(self._h, n_paints))
+
+    @property
+    def spec_tier(self) -> int:
+        """What the next plain paint runs: 0 interpreter, 1 structure-specialised kernel, 2 literal-specialised kernel."""
+        return int(self._L.rm_spec_tier(self._h))
 
     def spec_info(self) -> dict:
         a, r, mb, ms = C.c_int(), C.c_int(), C.c_int(), C.c_double()

@@ -25,16 +25,6 @@ namespace {
 constexpr uint32_t kMaxWordsCap = 3072;  // decoded program must fit in shared memory (48 B/insn)
 constexpr int kEventSlots = 16;
 constexpr size_t kFlushBytes = 256ull << 20;
-// EXPERIMENTAL, off unless RM_N4_COLLAPSE=1 is in the environment: programs with N4 commands prepared in fast mode are
-// decoded with one similarity per primitive instead of one instruction per transform step (rm_program.h).  Exact mode is
-// never affected; without the variable every code path below is what it was.
-bool n4_collapse_enabled() {
-    static const bool on = [] {
-        const char *s = std::getenv("RM_N4_COLLAPSE");
-        return s && s[0] == '1';
-    }();
-    return on;
-}
 }  // namespace
 
 struct rm_ctx {
@@ -60,21 +50,32 @@ struct rm_ctx {
     std::atomic<int> spec_bg_state{0};  // 0 idle, 1 compiling, 2 result ready
     uint64_t spec_bg_generation = 0;    // prog_uploads of the words being compiled: a result for older words is dropped
     int spec_bg_ex = 0, spec_bg_variant = 0, spec_bg_rc = 0;
-    const SpecKernel *spec_bg_kernel = nullptr;
+    bool spec_bg_compiled = false, spec_bg_literals = false;
     std::string spec_bg_err;
-    bool spec_requested = false;  // rm_specialize: the current program only
-    const SpecKernel *spec_cur[2][3] = {};  // [exact][SPEC_PLAIN / SPEC_COUNT / SPEC_AOV] for the current words
+    bool spec_requested = false;  // rm_specialize: the current program and every later one of the same STRUCTURE
+    SpecHandle spec_cur[2][3];    // [exact][SPEC_PLAIN / SPEC_COUNT / SPEC_AOV] for the current words
     bool spec_failed[2][3] = {};
+    // the kernels are compiled per program structure (rm_jit.h): the values travel as a kernel argument
+    std::vector<float> spec_params;      // parameter block of the current words (the same for both modes and all variants)
+    // LITERAL tier (rm_jit.h): the current words with every parameter an immediate — adopted once the same words have
+    // been painted spec_lit_after times (compiled in the background, never a stall) or at once by rm_specialize
+    SpecHandle spec_lit[2][3];
+    bool spec_lit_failed[2][3] = {};
+    uint32_t spec_lit_after = 8;         // rm_set_spec_literal_after: 0 = structure tier only
+    uint64_t paints_same_words = 0;      // plain paints since the words last changed
+    std::vector<uint32_t> spec_sig[2];   // structure signature the explicit request (rm_specialize) was made for, per mode
     std::string spec_status;      // why the last specialisation failed
     uint64_t spec_compiles = 0, spec_launches = 0;
     float limits_f[2] = {0.01f, 100.0f};  // renderer.rs:133-137
     uint32_t max_iter = 100;
     float uniforms[36] = {};
-    Program prog;
-    bool prog_collapsed = false;  // prog was decoded with collapse_chains (RM_N4_COLLAPSE experiment, fast mode only)
+    // The command stream decoded twice (rm_program.h): `prog` keeps the oracle's sequential operation order (RM_MODE_EXACT),
+    // `prog_fast` is the algebraically equal form RM_MODE_FAST paints (smooth unions as min(a,b) - e*e; the transform chains
+    // of extended programs composed into one similarity per primitive).  Both live in d_prog: exact at 0, fast at prog_cap.
+    Program prog, prog_fast;
     RmInsn *d_prog = nullptr;
     RmInsn *h_prog = nullptr;  // pinned staging
-    size_t prog_cap = 0;       // instructions
+    size_t prog_cap = 0;       // instructions per form
     uint8_t *d_fb = nullptr;
     size_t fb_cap = 0, fb_bytes = 0;
     float *d_codes = nullptr;
@@ -130,8 +131,12 @@ int ensure(rm_ctx *c, void **p, size_t *cap, size_t need) {
     return RM_OK;
 }
 
+// the decoded form the current arithmetic mode paints, on the host and on the device
+const Program &cur_prog(const rm_ctx *c) { return c->mode == RM_MODE_EXACT ? c->prog : c->prog_fast; }
+const RmInsn *cur_dprog(const rm_ctx *c) { return c->mode == RM_MODE_EXACT ? c->d_prog : c->d_prog + c->prog_cap; }
+
 FrameParams make_params(const rm_ctx *c, const float *u, uint32_t W, uint32_t H, uint32_t row0, uint32_t nrows) {
-    return make_frame_params(u, c->limits_f[0], c->limits_f[1], c->max_iter, (uint32_t)c->prog.insns.size(), W, H, row0, nrows);
+    return make_frame_params(u, c->limits_f[0], c->limits_f[1], c->max_iter, (uint32_t)cur_prog(c).insns.size(), W, H, row0, nrows);
 }
 
 int check_band(rm_ctx *c, uint32_t W, uint32_t H, uint32_t row0, uint32_t nrows) {
@@ -186,8 +191,8 @@ int rm_create_ex(int cuda_device, uint32_t max_words, rm_ctx **out) {
     ok = ok && cudaEventCreateWithFlags(&c->upload_done, cudaEventDisableTiming) == cudaSuccess;
     ok = ok && cudaEventCreateWithFlags(&c->paint_done, cudaEventDisableTiming) == cudaSuccess;
     c->prog_cap = max_words;
-    ok = ok && cudaMalloc(&c->d_prog, c->prog_cap * sizeof(RmInsn)) == cudaSuccess;
-    ok = ok && cudaMallocHost(&c->h_prog, c->prog_cap * sizeof(RmInsn)) == cudaSuccess;
+    ok = ok && cudaMalloc(&c->d_prog, 2 * c->prog_cap * sizeof(RmInsn)) == cudaSuccess;
+    ok = ok && cudaMallocHost(&c->h_prog, 2 * c->prog_cap * sizeof(RmInsn)) == cudaSuccess;
     ok = ok && cudaMalloc(&c->d_counters, 4 * sizeof(unsigned long long)) == cudaSuccess;
     ok = ok && cudaMemset(c->d_counters, 0, 4 * sizeof(unsigned long long)) == cudaSuccess;
     ok = ok && wavefront_init(&c->wf, cuda_device) == cudaSuccess;
@@ -241,14 +246,7 @@ int rm_set_limits(rm_ctx *c, const void *limits12) {
 
 int rm_set_mode(rm_ctx *c, int mode) {
     if (!c || (mode != RM_MODE_EXACT && mode != RM_MODE_FAST)) return RM_E_INVALID_ARG;
-    c->mode = mode;
-    // RM_N4_COLLAPSE experiment: the decoded form of an extended program depends on the arithmetic mode
-    if (n4_collapse_enabled() && c->prepared && c->prog.extended && c->prog_collapsed != (mode == RM_MODE_FAST)) {
-        float u[36];
-        std::memcpy(u, c->uniforms, sizeof u);
-        const std::vector<uint32_t> words = c->last_words;
-        return rm_prepare(c, u, c->last_cmd_count, words.data(), (uint32_t)words.size());
-    }
+    c->mode = mode;  // both decoded forms of the program are on the device (rm_prepare): nothing to redo
     return RM_OK;
 }
 int rm_get_mode(rm_ctx *c) { return c ? c->mode : RM_E_INVALID_ARG; }
@@ -268,25 +266,24 @@ int rm_prepare(rm_ctx *c, const void *uniforms144, uint32_t cmd_count, const uin
     if (n_words && !words) return fail(c, RM_E_INVALID_ARG, "null words");
     // Same command stream as the one already on the device (the reference re-flattens and re-uploads the tree every
     // frame, renderer.rs:224-239; an editor frame usually changes only the camera): only the uniforms change.
-    const bool want_collapse = n4_collapse_enabled() && c->mode == RM_MODE_FAST;  // false unless RM_N4_COLLAPSE=1
     if (c->prepared && cmd_count == c->last_cmd_count && n_words == c->last_words.size() &&
-        (n_words == 0 || std::memcmp(words, c->last_words.data(), (size_t)n_words * sizeof(uint32_t)) == 0) &&
-        (!c->prog.extended || c->prog_collapsed == want_collapse)) {
+        (n_words == 0 || std::memcmp(words, c->last_words.data(), (size_t)n_words * sizeof(uint32_t)) == 0)) {
         std::memcpy(c->uniforms, uniforms144, RM_UNIFORMS_BYTES);
         return RM_OK;
     }
-    Program p;
-    int rc = decode_program(cmd_count, words, n_words, c->max_words, &p, want_collapse);
+    Program p, pf;
+    int rc = decode_program(cmd_count, words, n_words, c->max_words, &p);
+    if (rc == RM_OK) rc = decode_program(cmd_count, words, n_words, c->max_words, &pf, /*fast_form=*/true, /*collapse_chains=*/true);
     if (rc != RM_OK) return fail(c, rc, rm_strerror(rc));
     // an extended program (N4) re-establishes the evaluation point whenever the chain of transforms in force changes, so
     // its instruction stream can be longer than its word stream; the device buffer holds max_words instructions
-    if (p.insns.size() > c->prog_cap) return fail(c, RM_E_PROGRAM_TOO_LARGE, "decoded program is longer than the instruction capacity (rm_create_ex max_words)");
+    if (p.insns.size() > c->prog_cap || pf.insns.size() > c->prog_cap) return fail(c, RM_E_PROGRAM_TOO_LARGE, "decoded program is longer than the instruction capacity (rm_create_ex max_words)");
     RM_CUDA(c, cudaSetDevice(c->device));
     // the staging buffer may still be in flight from the previous prepare
     RM_CUDA(c, cudaEventSynchronize(c->upload_done));
     c->prog = std::move(p);
-    c->prog_collapsed = want_collapse && c->prog.extended;
-    const size_t n = c->prog.insns.size();
+    c->prog_fast = std::move(pf);
+    const size_t n = c->prog.insns.size(), nf = c->prog_fast.insns.size();
     // paints still running on a caller-supplied stream read d_prog until they finish: the upload goes behind them
     if (c->paint_pending) {
         RM_CUDA(c, cudaStreamWaitEvent(c->stream, c->paint_done, 0));
@@ -296,14 +293,31 @@ int rm_prepare(rm_ctx *c, const void *uniforms144, uint32_t cmd_count, const uin
         std::memcpy(c->h_prog, c->prog.insns.data(), n * sizeof(RmInsn));
         RM_CUDA(c, cudaMemcpyAsync(c->d_prog, c->h_prog, n * sizeof(RmInsn), cudaMemcpyHostToDevice, c->stream));
     }
+    if (nf) {
+        std::memcpy(c->h_prog + c->prog_cap, c->prog_fast.insns.data(), nf * sizeof(RmInsn));
+        RM_CUDA(c, cudaMemcpyAsync(c->d_prog + c->prog_cap, c->h_prog + c->prog_cap, nf * sizeof(RmInsn), cudaMemcpyHostToDevice, c->stream));
+    }
     RM_CUDA(c, cudaEventRecord(c->upload_done, c->stream));
     std::memcpy(c->uniforms, uniforms144, RM_UNIFORMS_BYTES);
     c->last_words.assign(words, words + n_words);
     c->last_cmd_count = cmd_count;
-    // a specialised kernel belongs to one command stream: back to the interpreter (or, with the policy on, the new
-    // program is compiled at its first paint)
-    c->spec_requested = false;
-    for (int a = 0; a < 2; ++a) for (int b = 0; b < 3; ++b) { c->spec_cur[a][b] = nullptr; c->spec_failed[a][b] = false; }
+    // A specialised kernel belongs to one program STRUCTURE (opcode sequence; rm_jit.h): new words of the same structure —
+    // an editor dragging a radius — find their kernel in the cache at the next paint and only the parameter block changes.
+    // An explicit rm_specialize (no policy) holds for that structure only: other words go back to the interpreter.
+    if (c->spec_requested && !c->spec_policy) {
+        const int ex = c->mode == RM_MODE_EXACT ? 1 : 0;
+        std::vector<uint32_t> sig;
+        if (c->spec_sig[ex].empty() ||
+            spec_generate_source(cmd_count, words, n_words, ex != 0, SPEC_PLAIN, 0, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, &sig) != RM_OK ||
+            sig != c->spec_sig[ex])
+            c->spec_requested = false;
+    }
+    for (int a = 0; a < 2; ++a) for (int b = 0; b < 3; ++b) {
+        c->spec_cur[a][b].reset(); c->spec_failed[a][b] = false;
+        c->spec_lit[a][b].reset(); c->spec_lit_failed[a][b] = false;
+    }
+    c->paints_same_words = 0;
+    if (!c->spec_requested) { c->spec_sig[0].clear(); c->spec_sig[1].clear(); }
     ++c->prog_uploads;
     c->prepared = true;
     return RM_OK;

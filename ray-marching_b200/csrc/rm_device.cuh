@@ -66,6 +66,12 @@ struct FrameParams {
     float ro4[4];        // inv_view * (0,0,0,1)                        wgsl:39-40
     float sample_ax[4];  // ((i + 0.5)/4 - 0.5) / extent.x * 2, i = 0..3   wgsl:52-53
     float sample_ay[4];  // ((j + 0.5)/4 - 0.5) / extent.y * 2, j = 0..3
+    // FAST mode only: wgsl:52-61 is affine in the sample position, so the un-normalised direction of sample (i, j) of pixel
+    // (px, py) is  ray_c0 + X * ray_cx + Y * ray_cy  with  X = px + ray_bx + i * ray_gx,  Y = py + ray_by + j * ray_gy
+    // (for extent == (W, H): X = px + (2i+1)/8).  The three 4-vectors are inv_view * inv_proj composed in double on the host
+    // (rm_frame.h): 8 FFMA per sample instead of two 4x4 matrix-vector products and the pixel -> pt_screen divisions.
+    float ray_c0[4], ray_cx[4], ray_cy[4];
+    float ray_gx, ray_gy, ray_bx, ray_by;
 };
 
 __device__ __forceinline__ uint32_t frame_row(const FrameParams &fp, uint32_t ry) {
@@ -182,18 +188,21 @@ __device__ __forceinline__ void xf_scale(float bx, float by, float bz, float s, 
 
 // ---- binary operators: a = left operand (deeper stack entry), b = right (top) ----------------
 // X2: h = max(k-|a-b|,0)/k ; min(a,b) - h*h*k*0.25
-// Fast mode uses the algebraically equal h*h*k*0.25 = e*e/(4k) with c4k = 1/(4k) precomputed per
-// instruction: one multiply fewer per blend (exact mode keeps the literal operation order).
+// Exact mode evaluates that literally (inv_k = 1/k, used when k is a power of two).  Fast mode uses the algebraically
+// equal  min(a,b) - e*e,  e = max(k*s - |a-b|*s, 0),  s = sqrt(1/(4k)):  the FAST form of the program carries
+// (k*s, s) in the (inv_k, c4k) positions (rm_program.h smooth_constants_fast), and the blend is FADD, FFMA, 2 FMNMX, FFMA.
 template <bool EX>
 __device__ __forceinline__ float op_smooth(float a, float b, float k, float inv_k, float c4k, bool k_pow2) {
     using A = Arith<EX>;
-    float e = fmaxf(A::sub(k, fabsf(A::sub(a, b))), 0.0f);
-    float m = fminf(a, b);
     if (EX) {
+        float e = fmaxf(A::sub(k, fabsf(A::sub(a, b))), 0.0f);
+        float m = fminf(a, b);
         float h = k_pow2 ? __fmul_rn(e, inv_k) : __fdiv_rn(e, k);
         return __fsub_rn(m, __fmul_rn(__fmul_rn(__fmul_rn(h, h), k), 0.25f));
     } else {
-        return fmaf(-(e * e), c4k, m);
+        const float ks = inv_k, s = c4k;
+        const float e = fmaxf(fmaf(-fabsf(a - b), s, ks), 0.0f);
+        return fmaf(-e, e, fminf(a, b));
     }
 }
 // acc = smooth-min(acc, b), same operations, with the result tied to acc's register so that the
@@ -201,15 +210,18 @@ __device__ __forceinline__ float op_smooth(float a, float b, float k, float inv_
 template <bool EX>
 __device__ __forceinline__ void op_smooth_acc(float &acc, float b, float k, float inv_k, float c4k, bool k_pow2) {
     using A = Arith<EX>;
-    const float e = fmaxf(A::sub(k, fabsf(A::sub(acc, b))), 0.0f);
-    RM_PTX_MIN_ACC(acc, b);
     if (EX) {
+        const float e = fmaxf(A::sub(k, fabsf(A::sub(acc, b))), 0.0f);
+        RM_PTX_MIN_ACC(acc, b);
         const float h = k_pow2 ? __fmul_rn(e, inv_k) : __fdiv_rn(e, k);
         const float t = __fmul_rn(__fmul_rn(__fmul_rn(h, h), k), 0.25f);
         RM_PTX_SUB_ACC(acc, t);
     } else {
-        const float t = -(e * e);
-        RM_PTX_FMA_ACC(acc, t, c4k);
+        const float ks = inv_k, s = c4k;
+        const float e = fmaxf(fmaf(-fabsf(acc - b), s, ks), 0.0f);
+        RM_PTX_MIN_ACC(acc, b);
+        const float t = -e;
+        RM_PTX_FMA_ACC(acc, t, e);
     }
 }
 template <bool EX>
@@ -324,6 +336,18 @@ __device__ __forceinline__ void gen_ray(const FrameParams &fp, uint32_t px, uint
     ro[0] = fp.ro4[0]; ro[1] = fp.ro4[1]; ro[2] = fp.ro4[2];
 }
 
+// Fast-mode ray generation from the per-frame affine form (FrameParams::ray_c0 / ray_cx / ray_cy): same rays as gen_ray<false>
+// up to float rounding (the composition is done in double on the host), a third of the instructions.
+__device__ __forceinline__ void gen_ray_affine(const FrameParams &fp, float fpx, float fpy, uint32_t sample, float rd[3]) {
+    const float X = fmaf((float)(sample >> 2), fp.ray_gx, fpx), Y = fmaf((float)(sample & 3u), fp.ray_gy, fpy);  // wgsl:44-45: i -> x, j -> y
+    const float dx = fmaf(Y, fp.ray_cy[0], fmaf(X, fp.ray_cx[0], fp.ray_c0[0]));
+    const float dy = fmaf(Y, fp.ray_cy[1], fmaf(X, fp.ray_cx[1], fp.ray_c0[1]));
+    const float dz = fmaf(Y, fp.ray_cy[2], fmaf(X, fp.ray_cx[2], fp.ray_c0[2]));
+    const float dw = fmaf(Y, fp.ray_cy[3], fmaf(X, fp.ray_cx[3], fp.ray_c0[3]));
+    const float inv = rsqrtf(fmaf(dw, dw, fmaf(dz, dz, fmaf(dy, dy, dx * dx))));  // vec4 normalise, wgsl:62
+    rd[0] = dx * inv; rd[1] = dy * inv; rd[2] = dz * inv;
+}
+
 // ---- hit shading wgsl:100-105 given the un-normalised tetrahedron sum n (wgsl:138-143) --------
 template <bool EX>
 __device__ __forceinline__ float shade_diffuse(float nx, float ny, float nz, float px, float py, float pz) {
@@ -391,6 +415,25 @@ __device__ __forceinline__ void code_to_gamma(float code, float g[3]) {
         const float rg = __fadd_rn(0.1f, __fmul_rn(0.2f, col)), b = __fadd_rn(0.2f, __fmul_rn(0.2f, col));
         g[0] = g[1] = __fsqrt_rn(rg);
         g[2] = __fsqrt_rn(b);
+    }
+}
+
+// The same in fast mode: sqrt(albedo * v) as sqrt(albedo) * sqrt(v) — one MUFU and three multiplies instead of three IEEE
+// square roots (a relative difference of ~1e-7 per sample before the 8-bit quantisation).  Floor and sky samples are the
+// exact constants in both modes.
+#define RM_SQRT_ALBEDO_R 0.632455532f   /* sqrt(0.4) */
+#define RM_SQRT_ALBEDO_G 0.836660027f   /* sqrt(0.7) */
+#define RM_SQRT_ALBEDO_B 0.316227766f   /* sqrt(0.1) */
+template <bool EX>
+__device__ __forceinline__ void code_to_gamma_t(float code, float g[3]) {
+    if (EX) {
+        code_to_gamma(code, g);
+    } else if (code >= 0.0f) {
+        float r;
+        RM_PTX_SQRT_APPROX(r, code);
+        g[0] = RM_SQRT_ALBEDO_R * r; g[1] = RM_SQRT_ALBEDO_G * r; g[2] = RM_SQRT_ALBEDO_B * r;
+    } else {
+        code_to_gamma(code, g);
     }
 }
 

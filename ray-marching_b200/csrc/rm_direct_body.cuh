@@ -43,23 +43,27 @@ __device__ __forceinline__ void direct_body(const FrameParams &fp, uint8_t *__re
     const uint32_t grp = (uint32_t)lane % TPP;  // this thread holds samples grp*R .. grp*R+R-1 (sample = 4*i + j)
     const bool inside = px < fp.W && ry < fp.nrows;
 
-    float ro[3] = {0.f, 0.f, 0.f};
-    float rdx[R], rdy[R], rdz[R], dist[R], code[R];
+    // The ray origin is the same for every ray of the frame (wgsl:39-40): read where it is used, it stays a uniform operand.
+    const float ox = fp.ro4[0], oy = fp.ro4[1], oz = fp.ro4[2];
+    float rdx[R], rdy[R], rdz[R], dist[R];
     uint32_t live = 0, hit = 0;  // bit r: ray r still marching / ray r hit the scene
     uint32_t c_step = 0, c_hit = 0, c_floor = 0, c_sample = 0;
-    float t_miss[AOV ? R : 1];
-    int cls_miss[AOV ? R : 1];
-    RM_FOR_R { rdx[r] = rdy[r] = rdz[r] = 0.f; dist[r] = 0.f; code[r] = RM_CODE_SKY; }
+    RM_FOR_R { rdx[r] = rdy[r] = rdz[r] = 0.f; dist[r] = 0.f; }
     if (inside) {
         const uint32_t fy = frame_row(fp, ry);
-        RM_FOR_R {
-            float o[3], d[3], c[3], t;
-            gen_ray<EX>(fp, px, fy, grp * R + (uint32_t)r, o, d);  // wgsl:39-62
-            ro[0] = o[0]; ro[1] = o[1]; ro[2] = o[2];
-            rdx[r] = d[0]; rdy[r] = d[1]; rdz[r] = d[2];
-            const int cls = shade_miss(o, d, c, t);  // wgsl:117-130: what the ray gets if it never hits
-            code[r] = cls == 0 ? RM_CODE_SKY : (c[0] > 0.2f ? RM_CODE_FLOOR_LIGHT : RM_CODE_FLOOR_DARK);
-            if constexpr (AOV) { t_miss[r] = t; cls_miss[r] = cls; }
+        if constexpr (EX) {
+            RM_FOR_R {
+                float o[3], d[3];
+                gen_ray<EX>(fp, px, fy, grp * R + (uint32_t)r, o, d);  // wgsl:39-62, one rounding per operation
+                rdx[r] = d[0]; rdy[r] = d[1]; rdz[r] = d[2];
+            }
+        } else {
+            const float fpx = (float)px + fp.ray_bx, fpy = (float)fy + fp.ray_by;
+            RM_FOR_R {
+                float d[3];
+                gen_ray_affine(fp, fpx, fpy, grp * R + (uint32_t)r, d);  // the same rays from the per-frame affine form
+                rdx[r] = d[0]; rdy[r] = d[1]; rdz[r] = d[2];
+            }
         }
         if (COUNT) c_sample = R;
         if (fp.max_iter > 0) live = (1u << R) - 1u;
@@ -69,9 +73,9 @@ __device__ __forceinline__ void direct_body(const FrameParams &fp, uint8_t *__re
     // ---------------- march: all live rays of the thread take one step per trip (wgsl:88-115) ----------------
     for (uint32_t it = 0; live != 0; ++it) {
         RM_FOR_R {  // pos = origin + direction * dist   wgsl:91
-            px_[r] = A::mad(rdx[r], dist[r], ro[0]);
-            py_[r] = A::mad(rdy[r], dist[r], ro[1]);
-            pz_[r] = A::mad(rdz[r], dist[r], ro[2]);
+            px_[r] = A::mad(rdx[r], dist[r], ox);
+            py_[r] = A::mad(rdy[r], dist[r], oy);
+            pz_[r] = A::mad(rdz[r], dist[r], oz);
         }
         RM_FOR_R RM_OPAQUE_F3(px_[r], py_[r], pz_[r]);
         map(px_, py_, pz_, s);
@@ -92,6 +96,23 @@ __device__ __forceinline__ void direct_body(const FrameParams &fp, uint8_t *__re
             }
         }
     }
+    // ---------------- what the rays that never hit get: floor or sky (wgsl:117-130), after the march so that nothing of it
+    // is live across the loop; always with exact roundings (one division per missed ray) ----------------
+    float code[R];
+    float t_miss[AOV ? R : 1];
+    int cls_miss[AOV ? R : 1];
+    RM_FOR_R {
+        code[r] = RM_CODE_SKY;
+        if constexpr (AOV) { t_miss[r] = 0.f; cls_miss[r] = 0; }
+        if (inside && !((hit >> r) & 1u)) {
+            const float o[3] = {ox, oy, oz}, d[3] = {rdx[r], rdy[r], rdz[r]};
+            float c[3], t;
+            const int cls = shade_miss(o, d, c, t);
+            code[r] = cls == 0 ? RM_CODE_SKY : (c[0] > 0.2f ? RM_CODE_FLOOR_LIGHT : RM_CODE_FLOOR_DARK);
+            if (COUNT && cls != 0) ++c_floor;
+            if constexpr (AOV) { t_miss[r] = t; cls_miss[r] = cls; }
+        }
+    }
     // ---------------- normals + diffuse term of the rays that hit (wgsl:98-105,138-143) ----------------
     const uint32_t hit0 = hit;
     const float ep = RM_NORMAL_EPS, en = -RM_NORMAL_EPS;
@@ -101,7 +122,7 @@ __device__ __forceinline__ void direct_body(const FrameParams &fp, uint8_t *__re
             hit &= hit - 1u;
             const float dx = rr ? rdx[1] : rdx[0], dy = rr ? rdy[1] : rdy[0], dz = rr ? rdz[1] : rdz[0];
             const float dd = rr ? dist[1] : dist[0];
-            const float hx = A::mad(dx, dd, ro[0]), hy = A::mad(dy, dd, ro[1]), hz = A::mad(dz, dd, ro[2]);
+            const float hx = A::mad(dx, dd, ox), hy = A::mad(dy, dd, oy), hz = A::mad(dz, dd, oz);
             float a[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll 1
             for (int pass = 0; pass < 2; ++pass) {  // taps wgsl:138-142: (+,-,-) (-,-,+) | (-,+,-) (+,+,+)
@@ -124,7 +145,7 @@ __device__ __forceinline__ void direct_body(const FrameParams &fp, uint8_t *__re
                 hit &= hit - 1u;  // 0 stays 0
                 float dx = 0.f, dy = 0.f, dz = 0.f, dd = 0.f;
                 RM_FOR_R if (r == rr[j]) { dx = rdx[r]; dy = rdy[r]; dz = rdz[r]; dd = dist[r]; }
-                hx[j] = A::mad(dx, dd, ro[0]); hy[j] = A::mad(dy, dd, ro[1]); hz[j] = A::mad(dz, dd, ro[2]);
+                hx[j] = A::mad(dx, dd, ox); hy[j] = A::mad(dy, dd, oy); hz[j] = A::mad(dz, dd, oz);
                 // tetrahedron taps wgsl:138-142: (+,-,-) (-,-,+) (-,+,-) (+,+,+), eps = 1e-4
                 px_[4 * j + 0] = __fadd_rn(hx[j], ep); py_[4 * j + 0] = __fadd_rn(hy[j], en); pz_[4 * j + 0] = __fadd_rn(hz[j], en);
                 px_[4 * j + 1] = __fadd_rn(hx[j], en); py_[4 * j + 1] = __fadd_rn(hy[j], en); pz_[4 * j + 1] = __fadd_rn(hz[j], ep);
@@ -143,7 +164,6 @@ __device__ __forceinline__ void direct_body(const FrameParams &fp, uint8_t *__re
             }
         }
     }
-    if (COUNT && inside) RM_FOR_R if (!(hit0 & (1u << r)) && code[r] != RM_CODE_SKY) ++c_floor;
     if constexpr (AOV) if (inside) {
         const size_t base = ((size_t)ry * fp.W + px) * 16 + grp * R;
         RM_FOR_R {
@@ -156,7 +176,7 @@ __device__ __forceinline__ void direct_body(const FrameParams &fp, uint8_t *__re
     // ---------------- resolve: 16-sample mean in shader order (wgsl:44-45,68-75) ----------------
     // a pixel's threads hold consecutive sample ranges, so the running sum visits them in lane order
     float gm[R][3];
-    RM_FOR_R code_to_gamma(code[r], gm[r]);
+    RM_FOR_R code_to_gamma_t<EX>(code[r], gm[r]);
     float sr = 0.0f, sg = 0.0f, sb = 0.0f;
 #pragma unroll
     for (int g = 0; g < TPP; ++g) {

@@ -37,6 +37,27 @@ inline FrameParams make_frame_params(const float *uniforms36, float min_dist, fl
         fp.sample_ax[i] = qx * 2.0f;
         fp.sample_ay[i] = qy * 2.0f;
     }
+    // fast mode: the affine form of wgsl:52-61.  p.x = (2/W) X - 1 with X = px + 0.5 + (i - 1.5) * W / (4 extent.x);
+    // p.y = 1 - (2/H) Y with Y = py + 0.5 - (j - 1.5) * H / (4 extent.y); pt_world - ro = M (p.x, p.y, -1, 1) - ro with M = inv_view * inv_proj (column-major).
+    {
+        double M[16];
+        for (int c = 0; c < 4; ++c)
+            for (int r = 0; r < 4; ++r) {
+                double a = 0.0;
+                for (int k = 0; k < 4; ++k) a += (double)fp.inv_view[4 * k + r] * (double)fp.inv_proj[4 * c + k];
+                M[4 * c + r] = a;
+            }
+        const double w2 = 2.0 / (double)W, h2 = 2.0 / (double)H;
+        for (int r = 0; r < 4; ++r) {
+            fp.ray_cx[r] = (float)(M[r] * w2);
+            fp.ray_cy[r] = (float)(-M[4 + r] * h2);
+            fp.ray_c0[r] = (float)(-M[r] + M[4 + r] - M[8 + r] + M[12 + r] - (double)fp.ro4[r]);
+        }
+        const double gx = (double)W / (4.0 * (double)fp.extent[0]), gy = (double)H / (4.0 * (double)fp.extent[1]);
+        // a larger j moves the sample UP (larger p.y), i.e. towards smaller Y
+        fp.ray_gx = (float)gx; fp.ray_gy = (float)-gy;
+        fp.ray_bx = (float)(0.5 - 1.5 * gx); fp.ray_by = (float)(0.5 + 1.5 * gy);
+    }
     return fp;
 }
 

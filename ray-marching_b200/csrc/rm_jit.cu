@@ -7,6 +7,7 @@
 #include <dlfcn.h>
 
 #include <chrono>
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -35,11 +36,12 @@ constexpr int kNumHeaders = (int)(sizeof(kHeaders) / sizeof(kHeaders[0]));
 // ---- code-size model (SASS instructions per ray of one map_scene evaluation, fast mode; counted in the generated
 // code of the S0/S1/S2 scenes: sphere 3 FADD + FMUL + 2 FFMA + MUFU + FADD, box 6 FADD + 5 FMNMX + FMUL + 2 FFMA + MUFU
 // + FADD, smooth union 2 FADD + 2 FMNMX + FMUL + FFMA) and the instruction-cache budget it is checked against ----
-constexpr uint32_t kInsnSphere = 8, kInsnBox = 17, kInsnMinMax = 1, kInsnSmooth = 6;
+constexpr uint32_t kInsnSphere = 8, kInsnBox = 17, kInsnMinMax = 1, kInsnSmooth = 5;
 // N4 commands, counted from their device functions (not yet measured): plane 3 FFMA + FMUL-free, translation 3 FADD,
 // rotation 3 FMUL + 6 FFMA, scale 3 FMUL (push) + 1 FMUL (pop)
 constexpr uint32_t kInsnPlane = 3, kInsnTranslate = 3, kInsnRotate = 9, kInsnScalePush = 3, kInsnScalePop = 1;
 constexpr uint32_t kBytesPerInsn = 16;
+constexpr size_t kMaxParamBytes = 3584;  // SpecParams + FrameParams + pointers stay inside the classic 4-KB kernel-argument space
 constexpr uint32_t kLoopBudget4 = 24u << 10;  // 4 rays per thread while the march loop's map code stays under this
 constexpr uint32_t kLoopBudget2 = 40u << 10;  // 2 rays per thread up to here; beyond it the interpreter is the better kernel
 
@@ -116,33 +118,122 @@ const Nvrtc &nvrtc() {
     return n;
 }
 
+// Where a command parameter of the generated code comes from.  Default: the kernel's SpecParams argument (constant
+// bank; FADD / FFMA / FMNMX take a c[0x0][off] operand directly, so it costs no instruction and no register) — the code
+// then depends on the program's STRUCTURE only and one cubin serves every edit of a radius, a centre or a k.  Exception:
+// a parameter that is exactly +0 or -0 stays a literal (and its zero-ness is part of the structure signature), so that
+// `p - 0` and friends still fold; an editor drag leaves 0 once, not per frame.  The LITERAL tier emits every parameter
+// as an immediate by its bits and is keyed by the whole word stream: sm_100 arithmetic takes immediates for free, but a
+// kernel-argument value has to be loaded into a uniform register first (LDCU: one issue slot per 1-4 values; S2's march
+// loop is 1165 instructions with arguments against 1105 with immediates), so words that stay put are worth a second
+// compile (rm_abi_paint.inc current_spec promotes them in the background).
+struct ParamSink {
+    bool literals;
+    std::vector<float> *params;      // may be null (source only)
+    std::vector<uint32_t> *sig;      // may be null
+    uint32_t n = 0;
+    // The parameters of one command are read together: start them on a 16-byte (3 or more values) or 8-byte (2 values)
+    // boundary of the block, so that they arrive in the uniform registers as one LDCU.128 / LDCU.64 instead of one load
+    // each (sm_100 arithmetic takes uniform-register operands, not c[bank][offset] ones: every value costs a load slot)
+    void group(const uint32_t *bits, uint32_t count) {
+        if (literals) return;
+        uint32_t nz = 0;
+        for (uint32_t j = 0; j < count; ++j) nz += (bits[j] & 0x7fffffffu) != 0u;
+        const uint32_t al = nz >= 3 ? 4u : (nz == 2 ? 2u : 1u);
+        while (n % al) {
+            if (params) params->push_back(0.0f);
+            ++n;
+        }
+    }
+    std::string operator()(uint32_t bits) {
+        if (literals) return lit(bits);
+        if ((bits & 0x7fffffffu) == 0u) {           // +-0: structural
+            if (sig) sig->push_back(0xF0000000u | (bits >> 31));
+            return bits ? "(-0.0f)" : "0.0f";
+        }
+        if (sig) sig->push_back(0xF0000002u);
+        if (params) params->push_back(as_f32(bits));
+        return "P.f[" + std::to_string(n++) + "]";
+    }
+};
+
 // ---- process-wide cache ------------------------------------------------------------------------
+// Keyed by the structure signature of spec_generate_source (+ mode, variant); LRU-bounded.  Entries are shared_ptrs:
+// a context keeps the kernels of its current program alive, eviction only drops the cache's reference, and the cubin is
+// unloaded (SpecKernel's destructor) when the last holder lets go.
 struct Key {
-    std::vector<uint32_t> words;
-    uint32_t cmd_count;
+    std::vector<uint32_t> sig;
     bool exact;
     int variant;
     bool operator<(const Key &o) const {
-        if (cmd_count != o.cmd_count) return cmd_count < o.cmd_count;
         if (exact != o.exact) return exact < o.exact;
         if (variant != o.variant) return variant < o.variant;
-        return words < o.words;
+        return sig < o.sig;
     }
 };
 struct Entry {
     int rc = RM_OK;
     std::string err;
-    SpecKernel k;
+    std::shared_ptr<SpecKernel> k;
+    uint64_t last_use = 0;
 };
-constexpr size_t kMaxCacheEntries = 512;
+size_t g_cache_cap = 512;
+uint64_t g_tick = 0, g_evictions = 0;
 std::mutex g_mu;
-std::map<Key, std::unique_ptr<Entry>> g_cache;
+std::map<Key, Entry> g_cache;
+
+// with g_mu held: make room for one more entry by dropping the least recently used one nobody else holds
+bool evict_one() {
+    auto victim = g_cache.end();
+    for (auto it = g_cache.begin(); it != g_cache.end(); ++it) {
+        if (it->second.k && it->second.k.use_count() > 1) continue;  // painted by some context right now
+        if (victim == g_cache.end() || it->second.last_use < victim->second.last_use) victim = it;
+    }
+    if (victim == g_cache.end()) return false;
+    g_cache.erase(victim);  // ~SpecKernel unloads the cubin
+    ++g_evictions;
+    return true;
+}
 
 }  // namespace
 
+SpecKernel::~SpecKernel() {
+    if (!lib) return;
+    // kernels of this cubin may still be running on the devices that launched it
+    int cur = 0;
+    cudaGetDevice(&cur);
+    const uint64_t m = dev_mask.load();
+    for (int d = 0; d < 64; ++d)
+        if (m & (1ull << d)) { cudaSetDevice(d); cudaDeviceSynchronize(); }
+    cudaSetDevice(cur);
+    cudaLibraryUnload(lib);
+}
+
+void spec_cache_set_capacity(size_t n) {
+    std::lock_guard<std::mutex> lock(g_mu);
+    g_cache_cap = n ? n : 1;
+    while (g_cache.size() > g_cache_cap && evict_one()) {}
+}
+void spec_cache_stats(size_t *entries, size_t *capacity, uint64_t *evictions) {
+    std::lock_guard<std::mutex> lock(g_mu);
+    if (entries) *entries = g_cache.size();
+    if (capacity) *capacity = g_cache_cap;
+    if (evictions) *evictions = g_evictions;
+}
+
 int spec_generate_source(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, bool exact, int variant, int R,
-                         std::string *src, int *r_out, int *minb_out, uint32_t *est_out, std::string *err) {
-    // walk the postfix stream (builder.rs:26-62) with a stack of SSA value numbers: command i defines v<i>
+                         std::string *src, int *r_out, int *minb_out, uint32_t *est_out, std::string *err,
+                         std::vector<float> *params, std::vector<uint32_t> *sig, bool literals) {
+    // walk the postfix stream (builder.rs:26-62) with a stack of SSA value numbers: command i defines v<i>.
+    // The stream has been validated by decode_program (rm_prepare / rm_spec_source); the checks here only keep the walk
+    // itself in bounds and accept exactly what the decoder accepts.
+    ParamSink par{literals, params, sig};
+    if (params) params->clear();
+    if (sig) {
+        sig->clear();
+        if (literals) { sig->push_back(0xFFFFFFFFu); sig->push_back(cmd_count); sig->insert(sig->end(), words, words + n_words); }
+    }
+    auto sig_op = [&](uint32_t op) { if (sig && !literals) sig->push_back(op); };
     std::string body;
     std::vector<uint32_t> stack;
     // N4: the evaluation point is an SSA value too — a Push defines q<i>x/y/z from the point in force, the Pop goes back
@@ -155,24 +246,29 @@ int spec_generate_source(uint32_t cmd_count, const uint32_t *words, uint32_t n_w
     for (uint32_t i = 0; i < cmd_count; ++i) {
         if (!need(1)) { if (err) *err = "truncated command stream"; return RM_E_STACK_UNBALANCED; }
         const uint32_t op = words[ptr++];
+        sig_op(op);
         std::string e;
         if (op == RM_OP_SPHERE) {
             if (!need(4)) { if (err) *err = "truncated sphere"; return RM_E_STACK_UNBALANCED; }
-            e = "sd_sphere<EX>(" + at() + ", " + lit(words[ptr]) + ", " + lit(words[ptr + 1]) + ", " + lit(words[ptr + 2]) +
-                ", " + lit(words[ptr + 3]) + ")";
+            par.group(words + ptr, 4);
+            e = "sd_sphere<EX>(" + at();
+            for (int j = 0; j < 4; ++j) e += ", " + par(words[ptr + j]);
+            e += ")";
             ptr += 4; est += kInsnSphere;
             stack.push_back(i);
         } else if (op == RM_OP_BOX) {
             if (!need(6)) { if (err) *err = "truncated box"; return RM_E_STACK_UNBALANCED; }
+            par.group(words + ptr, 6);
             e = "sd_box<EX>(" + at();
-            for (int j = 0; j < 6; ++j) e += ", " + lit(words[ptr + j]);
+            for (int j = 0; j < 6; ++j) e += ", " + par(words[ptr + j]);
             e += ")";
             ptr += 6; est += kInsnBox;
             stack.push_back(i);
         } else if (op == RM_OP_PLANE) {
             if (!need(4)) { if (err) *err = "truncated plane"; return RM_E_STACK_UNBALANCED; }
+            par.group(words + ptr, 4);
             e = "sd_plane<EX>(" + at();
-            for (int j = 0; j < 4; ++j) e += ", " + lit(words[ptr + j]);
+            for (int j = 0; j < 4; ++j) e += ", " + par(words[ptr + j]);
             e += ")";
             ptr += 4; est += kInsnPlane;
             stack.push_back(i);
@@ -186,11 +282,16 @@ int spec_generate_source(uint32_t cmd_count, const uint32_t *words, uint32_t n_w
             else if (op == RM_OP_ROTATION_PUSH) { call = "xf_rotate<EX>(" + at(); est += kInsnRotate; }
             else {
                 const float sc = as_f32(words[ptr]);
-                if (!(sc > 0.0f) || sc > 3.0e38f) { if (err) *err = "scale must be finite and > 0"; return RM_E_BAD_PARAM; }
-                call = "xf_scale<EX>(" + at() + ", " + lit(words[ptr]) + ", " + lit(as_u32(1.0f / sc));
+                if (!(sc > 0.0f) || !std::isfinite(sc)) { if (err) *err = "scale must be finite and > 0"; return RM_E_BAD_PARAM; }
+                const uint32_t sb[2] = {words[ptr], as_u32(1.0f / sc)};
+                par.group(sb, 2);
+                call = "xf_scale<EX>(" + at() + ", " + par(sb[0]) + ", " + par(sb[1]);
                 est += kInsnScalePush;
             }
-            if (op != RM_OP_SCALE_PUSH) for (uint32_t j = 0; j < np; ++j) call += ", " + lit(words[ptr + j]);
+            if (op != RM_OP_SCALE_PUSH) {
+                par.group(words + ptr, np);
+                for (uint32_t j = 0; j < np; ++j) call += ", " + par(words[ptr + j]);
+            }
             call += ", " + q + "x[r], " + q + "y[r], " + q + "z[r])";
             body += "        float " + q + "x[R], " + q + "y[R], " + q + "z[R];\n        RM_FOR_R " + call + ";\n";
             pos.push_back(Pos{q + "x", q + "y", q + "z", op, words[ptr], stack.size()});
@@ -206,7 +307,7 @@ int spec_generate_source(uint32_t cmd_count, const uint32_t *words, uint32_t n_w
                 if (words[ptr] != pos.back().s_bits) { if (err) *err = "ScalePop factor differs from its push"; return RM_E_BAD_PARAM; }
                 // the child's distance back in the parent's units: a new SSA value replaces the top of the stack
                 const std::string top = var(stack.back()) + "[r]";
-                body += "        float " + var(i) + "[R];\n        RM_FOR_R " + var(i) + "[r] = Arith<EX>::mul(" + top + ", " + lit(words[ptr]) + ");\n";
+                body += "        float " + var(i) + "[R];\n        RM_FOR_R " + var(i) + "[r] = Arith<EX>::mul(" + top + ", " + par(words[ptr]) + ");\n";
                 stack.back() = i;
                 ptr += 1; est += kInsnScalePop;
             }
@@ -224,12 +325,28 @@ int spec_generate_source(uint32_t cmd_count, const uint32_t *words, uint32_t n_w
             else {
                 if (!need(1)) { if (err) *err = "truncated smooth union"; return RM_E_STACK_UNBALANCED; }
                 const float k = as_f32(words[ptr++]);
-                if (!(k > 0.0f) || k != k || k > 3.0e38f) { if (err) *err = "smooth-union k must be finite and > 0"; return RM_E_BAD_PARAM; }
+                if (!(k > 0.0f) || !std::isfinite(k)) { if (err) *err = "smooth-union k must be finite and > 0"; return RM_E_BAD_PARAM; }
                 float inv_k, c4k;
                 bool pow2;
                 smooth_constants(k, &inv_k, &c4k, &pow2);
-                e = "op_smooth<EX>(" + a + ", " + b + ", " + lit(as_u32(k)) + ", " + lit(as_u32(inv_k)) + ", " + lit(as_u32(c4k)) + ", " +
-                    (pow2 ? "true" : "false") + ")";
+                if (literals && exact) {
+                    e = "op_smooth<EX>(" + a + ", " + b + ", " + lit(as_u32(k)) + ", " + lit(as_u32(inv_k)) + ", " + lit(as_u32(c4k)) + ", " +
+                        (pow2 ? "true" : "false") + ")";
+                } else if (exact) {
+                    // whether 1/k is exact decides multiply-or-divide: structural.  1/k is only read when it is.
+                    if (sig && !literals) sig->push_back(0xF0000010u | (pow2 ? 1u : 0u));
+                    const uint32_t kb[2] = {as_u32(k), as_u32(inv_k)};
+                    par.group(kb, pow2 ? 2 : 1);
+                    e = "op_smooth<EX>(" + a + ", " + b + ", " + par(kb[0]) + ", " + (pow2 ? par(kb[1]) : std::string("0.0f")) + ", 0.0f, " +
+                        (pow2 ? "true" : "false") + ")";
+                } else {
+                    // fast mode reads (k*s, s) only (rm_program.h smooth_constants_fast)
+                    float ks, sk;
+                    smooth_constants_fast(k, &ks, &sk);
+                    const uint32_t kb[2] = {as_u32(ks), as_u32(sk)};
+                    par.group(kb, 2);
+                    e = "op_smooth<EX>(" + a + ", " + b + ", 0.0f, " + par(kb[0]) + ", " + par(kb[1]) + ", false)";
+                }
                 est += kInsnSmooth;
             }
             stack.push_back(i);
@@ -240,7 +357,12 @@ int spec_generate_source(uint32_t cmd_count, const uint32_t *words, uint32_t n_w
         if (stack.size() > RM_STACK_MAX) { if (err) *err = "value stack deeper than 32"; return RM_E_STACK_OVERFLOW; }
         body += "        float " + var(i) + "[R];\n        RM_FOR_R " + var(i) + "[r] = " + e + ";\n";
     }
-    if (cmd_count != 0 && (stack.size() != 1 || pos.size() != 1)) { if (err) *err = "value stack does not end with one value"; return RM_E_STACK_UNBALANCED; }
+    // same acceptance as decode_program: at least one value left (the shader's final pop_value takes the top), all groups closed
+    if (cmd_count != 0 && (stack.empty() || pos.size() != 1)) { if (err) *err = "value stack ends empty or a transform group is open"; return RM_E_STACK_UNBALANCED; }
+    if ((size_t)par.n * sizeof(float) > kMaxParamBytes) {
+        if (err) *err = "too many parameters for the kernel-argument block (" + std::to_string(par.n) + "): the interpreter is used";
+        return RM_E_JIT;
+    }
 
     // rays per thread from the code-size estimate: the march loop's copy of map_scene has to stay in the instruction cache
     if (R == 0) R = env_int("RM_SPEC_R");
@@ -254,23 +376,27 @@ int spec_generate_source(uint32_t cmd_count, const uint32_t *words, uint32_t n_w
     }
     int minb = env_int("RM_SPEC_MINB");
     if (minb <= 0) minb = R == 2 ? 12 : (R == 4 ? 10 : 7);  // measured on B200, profiles/r1_s14_NOTES.md
+    if (sig && !literals) { sig->push_back(0xF0000020u | (uint32_t)R); sig->push_back(0xF0000040u | (uint32_t)minb); }
     if (r_out) *r_out = R;
     if (minb_out) *minb_out = minb;
     if (est_out) *est_out = est;
+    if (params) while (params->size() < 4 || params->size() % 4) params->push_back(0.0f);  // = sizeof(SpecParams): the launch copies all of it
     if (!src) return RM_OK;
 
     std::string s;
     s += "// generated by rm_jit.cu: map_scene of one " + std::to_string(cmd_count) + "-command stream as straight-line code\n";
     s += "#include \"rm_direct_body.cuh\"\n";
     s += "namespace rm {\n";
-    s += "template <bool EX, int R>\nstruct SpecMap {\n    float max_dist;\n";
+    s += "struct alignas(16) SpecParams { float f[" + std::to_string(par.n ? ((par.n + 3u) & ~3u) : 4u) + "]; };  // the stream's non-zero parameters, in stream order\n";
+    s += "template <bool EX, int R>\nstruct SpecMap {\n    float max_dist;\n    const SpecParams &P;  // the kernel's __grid_constant__ argument: every use is a constant-bank operand\n";
+    s += "    __device__ __forceinline__ SpecMap(float md, const SpecParams &p) : max_dist(md), P(p) {}\n";
     s += "    __device__ __forceinline__ void operator()(const float (&px)[R], const float (&py)[R], const float (&pz)[R], float (&out)[R]) {\n";
     if (cmd_count == 0) s += "        RM_FOR_R out[r] = max_dist;  // wgsl:189-191\n";
     else s += body + "        RM_FOR_R out[r] = " + var(stack.back()) + "[r];\n";
     s += "    }\n};\n}  // namespace rm\n";
     s += "extern \"C\" __global__ void __launch_bounds__(RM_DIRECT_THREADS, " + std::to_string(minb) + ")\n";
-    s += "rm_spec(const __grid_constant__ rm::FrameParams fp, uint8_t *__restrict__ dst, size_t pitch, unsigned long long *__restrict__ counters,\n        uint8_t *__restrict__ aov_cls, float *__restrict__ aov_t) {\n";
-    s += "    rm::SpecMap<" + std::string(exact ? "true" : "false") + ", " + std::to_string(R) + "> map;\n    map.max_dist = fp.max_dist;\n";
+    s += "rm_spec(const __grid_constant__ rm::FrameParams fp, const __grid_constant__ rm::SpecParams P, uint8_t *__restrict__ dst, size_t pitch,\n        unsigned long long *__restrict__ counters, uint8_t *__restrict__ aov_cls, float *__restrict__ aov_t) {\n";
+    s += "    rm::SpecMap<" + std::string(exact ? "true" : "false") + ", " + std::to_string(R) + "> map(fp.max_dist, P);\n";
     s += "    rm::direct_body<" + std::string(exact ? "true" : "false") + ", " + std::to_string(R) + ", " + (variant == SPEC_COUNT ? "true" : "false") + ", " +
          (variant == SPEC_AOV ? "true" : "false") + ">(fp, dst, pitch, counters, aov_cls, aov_t, map);\n}\n";
     *src = std::move(s);
@@ -308,56 +434,74 @@ int spec_compile(const std::string &src, std::string *cubin, std::string *err) {
     return RM_OK;
 }
 
-int spec_get(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, bool exact, int variant, const SpecKernel **out,
-             bool *compiled_now, std::string *err) {
-    Key key{std::vector<uint32_t>(words, words + n_words), cmd_count, exact, variant};
-    std::lock_guard<std::mutex> lock(g_mu);  // one compile at a time; the other members of a group then hit the cache
+int spec_get(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, bool exact, int variant, bool literals, SpecHandle *out,
+             std::vector<float> *params, bool *compiled_now, std::string *err, bool lookup_only) {
     if (compiled_now) *compiled_now = false;
-    auto it = g_cache.find(key);
-    if (it == g_cache.end() && g_cache.size() >= kMaxCacheEntries) {
-        // kernels are never unloaded (contexts hold pointers into the cache), so the cache is bounded instead: a host that
-        // streams thousands of distinct programs with the policy on falls back to the interpreter for the new ones
-        if (err) *err = "specialisation cache is full (" + std::to_string(kMaxCacheEntries) + " programs): the interpreter is used";
-        return RM_E_JIT;
+    Key key{{}, exact, variant};
+    std::string src, gen_err;
+    SpecKernel meta;
+    // generation is cheap (string building); it yields the structure signature = the cache key, and the parameter block
+    int rc = spec_generate_source(cmd_count, words, n_words, exact, variant, 0, &src, &meta.rays_per_thread, &meta.min_blocks,
+                                  &meta.est_insn_per_ray, &gen_err, params, &key.sig, literals);
+    if (rc != RM_OK) {
+        if (err) *err = gen_err;
+        return rc;
     }
+    std::lock_guard<std::mutex> lock(g_mu);  // one compile at a time; the other members of a group then hit the cache
+    auto it = g_cache.find(key);
     if (it == g_cache.end()) {
+        if (lookup_only) return RM_E_JIT;
+        while (g_cache.size() >= g_cache_cap) {
+            if (!evict_one()) {
+                if (err) *err = "specialisation cache is full (" + std::to_string(g_cache_cap) + " programs, all in use): the interpreter is used";
+                return RM_E_JIT;
+            }
+        }
         if (compiled_now) *compiled_now = true;
-        auto e = std::make_unique<Entry>();
+        Entry e;
         const auto t0 = std::chrono::steady_clock::now();
-        std::string src, cubin;
-        e->k.exact = exact; e->k.variant = variant;
-        e->rc = spec_generate_source(cmd_count, words, n_words, exact, variant, 0, &src, &e->k.rays_per_thread, &e->k.min_blocks,
-                                     &e->k.est_insn_per_ray, &e->err);
-        if (e->rc == RM_OK) e->rc = spec_compile(src, &cubin, &e->err);
-        if (e->rc == RM_OK) {
-            cudaError_t ce = cudaLibraryLoadData(&e->k.lib, cubin.data(), nullptr, nullptr, 0, nullptr, nullptr, 0);
-            if (ce == cudaSuccess) ce = cudaLibraryGetKernel(&e->k.fn, e->k.lib, "rm_spec");
+        std::string cubin;
+        auto k = std::make_shared<SpecKernel>();
+        k->exact = exact; k->variant = variant; k->literals = literals;
+        k->rays_per_thread = meta.rays_per_thread; k->min_blocks = meta.min_blocks; k->est_insn_per_ray = meta.est_insn_per_ray;
+        k->n_params = params ? (uint32_t)params->size() : 0;
+        e.rc = spec_compile(src, &cubin, &e.err);
+        if (e.rc == RM_OK) {
+            cudaError_t ce = cudaLibraryLoadData(&k->lib, cubin.data(), nullptr, nullptr, 0, nullptr, nullptr, 0);
+            if (ce == cudaSuccess) ce = cudaLibraryGetKernel(&k->fn, k->lib, "rm_spec");
             if (ce != cudaSuccess) {
-                e->rc = RM_E_JIT;
-                e->err = std::string("loading the specialised kernel: ") + cudaGetErrorString(ce);
+                e.rc = RM_E_JIT;
+                e.err = std::string("loading the specialised kernel: ") + cudaGetErrorString(ce);
                 cudaGetLastError();
             }
-            e->k.cubin_bytes = cubin.size();
+            k->cubin_bytes = cubin.size();
         }
-        e->k.compile_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        k->compile_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        if (e.rc == RM_OK) e.k = std::move(k);
         it = g_cache.emplace(std::move(key), std::move(e)).first;  // failures are cached too: no retry storm per frame
     }
-    const Entry &e = *it->second;
+    Entry &e = it->second;
+    e.last_use = ++g_tick;
     if (e.rc != RM_OK) {
         if (err) *err = e.err;
         return e.rc;
     }
-    *out = &e.k;
+    *out = e.k;
     return RM_OK;
 }
 
-cudaError_t launch_spec(const SpecKernel &k, const FrameParams &fp, uint8_t *dst, size_t pitch, unsigned long long *counters,
-                        uint8_t *aov_cls, float *aov_t, cudaStream_t st) {
+cudaError_t launch_spec(const SpecKernel &k, const FrameParams &fp, const float *params, uint8_t *dst, size_t pitch,
+                        unsigned long long *counters, uint8_t *aov_cls, float *aov_t, cudaStream_t st) {
     if (fp.nrows == 0 || fp.W == 0) return cudaSuccess;
     const uint32_t tile_h = direct_tile_rows(k.rays_per_thread);
     const unsigned grid = ((fp.W + RM_DIRECT_TILE_W - 1) / RM_DIRECT_TILE_W) * ((fp.nrows + tile_h - 1) / tile_h);
     FrameParams p = fp;
-    void *args[] = {&p, &dst, &pitch, &counters, &aov_cls, &aov_t};
+    static const float kNoParams[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+    const float *pp = params ? params : kNoParams;  // the launch copies sizeof(SpecParams) bytes from here
+    int dev = 0;
+    cudaGetDevice(&dev);
+    k.dev_mask.fetch_or(1ull << (dev & 63));
+    void *args[] = {&p, (void *)pp, &dst, &pitch, &counters, &aov_cls, &aov_t};
     return cudaLaunchKernel((const void *)k.fn, dim3(grid), dim3(RM_DIRECT_THREADS), args, 0, st);
 }
 

@@ -34,13 +34,20 @@ inline uint32_t combine_of(uint32_t t) {
         default: return CB_SMOOTH;
     }
 }
-inline void set_k(RmInsn &in, float k) {
+inline void set_k(RmInsn &in, float k, bool fast_form) {
     in.k = k;
     bool pow2 = false;
     smooth_constants(k, &in.inv_k, &in.c4k, &pow2);
     if (pow2) in.flags |= FLAG_K_POW2;
+    if (fast_form) smooth_constants_fast(k, &in.inv_k, &in.c4k);  // (k*s, s) in the slots of (1/k, 1/(4k))
 }
 }  // namespace
+
+void smooth_constants_fast(float k, float *ks, float *s) {
+    const double sd = std::sqrt(0.25 / (double)k);
+    *s = (float)sd;
+    *ks = (float)((double)k * sd);
+}
 
 void smooth_constants(float k, float *inv_k, float *c4k, bool *k_pow2) {
     *inv_k = 1.0f / k;
@@ -94,7 +101,7 @@ Frame compose_chain(const std::vector<Cmd> &cmds, const std::vector<uint32_t> &c
 // collapse_chains (fast arithmetic only; exact mode has to keep the sequential roundings): each primitive's chain is
 // composed on the host into one similarity q = A*p + b; A becomes ONE "q = transpose(M)*p" instruction (none when the
 // chain only translates), b is folded into the primitive's centre (sphere, box) or offset (plane).
-int lower_extended(const std::vector<Cmd> &cmds, Program &prog, Program *out, bool collapse_chains) {
+int lower_extended(const std::vector<Cmd> &cmds, Program &prog, Program *out, bool fast_form, bool collapse_chains) {
     const uint32_t n = (uint32_t)cmds.size();
     // pass 2a: value-stack and group discipline, command by command as the sequential semantics would run
     // (same rules as oracle/rm_oracle.c validate_program)
@@ -217,7 +224,7 @@ int lower_extended(const std::vector<Cmd> &cmds, Program &prog, Program *out, bo
             if (depth >= 1 && i + 1 < nv && !v[i + 1].accmul && is_binary(cmds[v[i + 1].cmd].type)) {
                 const Cmd &o = cmds[v[i + 1].cmd];  // fused: acc = op(acc, prim); T/R pops in between change nothing
                 in.op = opcode(src, combine_of(o.type));
-                if (o.type == RM_OP_SMOOTH_UNION) set_k(in, o.p[0]);
+                if (o.type == RM_OP_SMOOTH_UNION) set_k(in, o.p[0], fast_form);
                 ++i;
             } else if (depth == 0) {
                 in.op = opcode(src, CB_FIRST);
@@ -230,7 +237,7 @@ int lower_extended(const std::vector<Cmd> &cmds, Program &prog, Program *out, bo
         } else {
             in.op = opcode(SRC_POP, combine_of(c.type));
             in.slot = depth - 2;
-            if (c.type == RM_OP_SMOOTH_UNION) set_k(in, c.p[0]);
+            if (c.type == RM_OP_SMOOTH_UNION) set_k(in, c.p[0], fast_form);
             depth -= 1;
         }
         finish_flags(in);
@@ -246,7 +253,7 @@ int lower_extended(const std::vector<Cmd> &cmds, Program &prog, Program *out, bo
 }  // namespace
 
 int decode_program(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, uint32_t max_words,
-                   Program *out, bool collapse_chains) {
+                   Program *out, bool fast_form, bool collapse_chains) {
     if (out) *out = Program();
     if (cmd_count == 0) return RM_OK;  // empty scene: map_scene == max_dist (wgsl:188-191)
     if (!words) return RM_E_INVALID_ARG;
@@ -289,7 +296,7 @@ int decode_program(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, 
         for (uint32_t j = 0; j < np; ++j) if (c.p[j] != c.p[j]) return RM_E_BAD_PARAM;
         cmds.push_back(c);
     }
-    if (prog.extended) return lower_extended(cmds, prog, out, collapse_chains);
+    if (prog.extended) return lower_extended(cmds, prog, out, fast_form, collapse_chains);
 
     // pass 2: stack discipline + emission with top-of-stack caching and prim/op fusion
     uint32_t depth = 0, max_depth = 0;
@@ -305,7 +312,7 @@ int decode_program(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, 
             if (depth >= 1 && i + 1 < cmd_count && is_binary(cmds[i + 1].type)) {
                 const Cmd &o = cmds[i + 1];  // fused: acc = op(acc, prim)
                 in.op = opcode(src, combine_of(o.type));
-                if (o.type == RM_OP_SMOOTH_UNION) set_k(in, o.p[0]);
+                if (o.type == RM_OP_SMOOTH_UNION) set_k(in, o.p[0], fast_form);
                 ++i;  // the operator is consumed; depth unchanged (push 1, pop 2, push 1)
             } else if (depth == 0) {
                 in.op = opcode(src, CB_FIRST);
@@ -319,7 +326,7 @@ int decode_program(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, 
             if (depth < 2) return RM_E_STACK_UNBALANCED;
             in.op = opcode(SRC_POP, combine_of(c.type));
             in.slot = depth - 2;
-            if (c.type == RM_OP_SMOOTH_UNION) set_k(in, c.p[0]);
+            if (c.type == RM_OP_SMOOTH_UNION) set_k(in, c.p[0], fast_form);
             depth -= 1;
         }
         {

@@ -99,8 +99,8 @@ RM_HD constexpr uint32_t opcode_cb_ext(uint32_t op) { return op < 16u ? opcode_c
 // One decoded instruction = 3 x 16 bytes (three broadcast LDS.128).
 struct alignas(16) RmInsn {
     float cx, cy, cz, r0;      // centre, sphere radius / box radius x
-    float r1, r2, k, inv_k;    // box radius y,z; smooth-union k and 1/k
-    float c4k;                 // 1/(4k): fast mode evaluates min(a,b) - e*e*c4k (exact mode does not read it)
+    float r1, r2, k, inv_k;    // box radius y,z; smooth-union k and 1/k.  FAST form of the program: inv_k holds k*s instead,
+    float c4k;                 // and c4k holds s = sqrt(1/(4k)) (smooth_constants_fast); exact form: c4k = 1/(4k), unread
     uint32_t op;               // dense fused opcode, see opcode()
     uint32_t slot;             // spill slot read (SRC_POP) or written (CB_PUSH)
     uint32_t flags;
@@ -128,16 +128,22 @@ struct Program {
 // Per-instruction constants of the smooth union (X2) — one definition for the interpreter's decoder and the
 // specialised-kernel generator (rm_jit.cu), so that both evaluate the blend with the same numbers.
 void smooth_constants(float k, float *inv_k, float *c4k, bool *k_pow2);
+// Fast mode evaluates  min(a,b) - h*h*k/4  (h = max(k-|a-b|,0)/k)  as  min(a,b) - e*e  with
+// e = max(ks - |a-b|*s, 0),  s = sqrt(1/(4k)),  ks = k*s:  FADD, FFMA, 2 FMNMX, FFMA — one instruction fewer than
+// min(a,b) - (max(k-|a-b|,0))^2 * (1/(4k)).  For k a power of four (k = 0.25: s = 1) the two are the same numbers.
+void smooth_constants_fast(float k, float *ks, float *s);
 
 // Returns an RM_* code (rm_b200.h).  `out` may be null for validation only.
-// collapse_chains (EXPERIMENTAL, only meaningful for extended programs painted in fast mode; off everywhere unless the
-// environment variable RM_N4_COLLAPSE=1 is set, see rm_abi.cu): instead of one instruction per transform step, each
-// primitive's chain of groups is composed on the host (double precision) into one similarity q = A*p + b — A is one
-// "q = transpose(M)*p" instruction, shared by consecutive primitives with the same A and absent for translation-only
-// chains, and b moves into the primitive's centre / the plane's offset.  Not the sequential roundings of the oracle:
-// never used in exact mode.  Not yet measured on a GPU.
+// A prepared program is decoded twice (rm_abi.cu): the EXACT form keeps the sequential operation order and roundings of
+// the oracle; the FAST form (what RM_MODE_FAST paints) differs in two ways, both algebraically equal to it:
+//   fast_form:        smooth unions carry (k*s, s) in place of (1/k, 1/(4k)) — see smooth_constants_fast;
+//   collapse_chains:  (extended programs) instead of one instruction per transform step, each primitive's chain of
+//                     groups is composed on the host (double precision) into one similarity q = A*p + b — A is one
+//                     "q = transpose(M)*p" instruction, shared by consecutive primitives with the same A and absent for
+//                     translation-only chains, and b moves into the primitive's centre / the plane's offset.
+//                     Measured on B200: S3 through the EXT interpreter 20.74 -> 16.76 ms (profiles/r2_s1_n4_collapse_timing.jsonl).
 int decode_program(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, uint32_t max_words,
-                   Program *out, bool collapse_chains = false);
+                   Program *out, bool fast_form = false, bool collapse_chains = false);
 #endif  // !__CUDACC_RTC__
 
 }  // namespace rm

@@ -62,7 +62,7 @@ int hc_paint(int exact, int rays_per_thread, uint32_t cmd_count, const uint32_t 
              int dst_frame_rows, uint8_t *dst, size_t pitch, uint64_t *counters4, uint8_t *aov_cls, float *aov_t) {
     Program p;
     // exact < 0: fast mode with the experimental collapsed lowering of extended programs (RM_N4_COLLAPSE)
-    const int rc = decode_program(cmd_count, words, n_words, 3072, &p, exact < 0);
+    const int rc = decode_program(cmd_count, words, n_words, 3072, &p, /*fast_form=*/exact <= 0, /*collapse_chains=*/exact < 0);
     if (exact < 0) exact = 0;
     if (rc != RM_OK) return rc;
     float u[36], lim[2];
@@ -95,7 +95,7 @@ int hc_paint(int exact, int rays_per_thread, uint32_t cmd_count, const uint32_t 
 int hc_decode(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, uint32_t max_words, void *insns, uint32_t cap,
               uint32_t *n_insn, int *extended, uint32_t *flops_per_eval, int collapse_chains) {
     Program p;
-    const int rc = decode_program(cmd_count, words, n_words, max_words, &p, collapse_chains != 0);
+    const int rc = decode_program(cmd_count, words, n_words, max_words, &p, /*fast_form=*/collapse_chains != 0, collapse_chains != 0);
     if (rc != RM_OK) return rc;
     if (n_insn) *n_insn = (uint32_t)p.insns.size();
     if (extended) *extended = p.extended ? 1 : 0;
@@ -110,7 +110,7 @@ int hc_decode(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, uint3
 int hc_map(int exact, int rays_per_thread, int force_ext, uint32_t cmd_count, const uint32_t *words, uint32_t n_words, float max_dist,
            const float *pts, uint64_t n, float *out, int collapse_chains) {
     Program p;
-    const int rc = decode_program(cmd_count, words, n_words, 3072, &p, collapse_chains != 0);
+    const int rc = decode_program(cmd_count, words, n_words, 3072, &p, /*fast_form=*/!exact, collapse_chains != 0);
     if (rc != RM_OK) return rc;
     const bool ext = p.extended || force_ext;
 #define HC_RUN(EXV, EXTV)                                                            \

@@ -280,26 +280,150 @@ def test_background_policy_never_stalls_and_switches_over(rm, ctx):
     import time
     W, H = 96, 64
     u = h.orbit_uniforms(W, H, yaw=0.3, pitch=0.2)
-    # a program nobody has compiled in this process yet (the cache is process-wide)
-    words = h.sphere((0.123, 0.2, -0.1), 0.9) + h.box((0.4, 0.1, 0.0), (0.5, 0.6, 0.7)) + [103, h.fbits(0.37)]
-    ref = h.oracle_render(u, 3, words, W, H)["rgba"]
+    # a program STRUCTURE nobody has compiled in this process yet (the cache is process-wide and keyed by structure: the
+    # zero pattern of the parameters is part of it)
+    words = (h.sphere((0.123, 0.0, -0.1), 0.9) + h.box((0.4, 0.1, 0.0), (0.5, 0.6, 0.7)) + [103, h.fbits(0.37)]
+             + h.sphere((0.0, 0.0, 0.3), 0.4) + [102] + h.box((0.0, 0.2, 0.0), (0.3, 0.3, 0.9)) + [101])
+    ncmd = 7
+    ref = h.oracle_render(u, ncmd, words, W, H)["rgba"]
     ctx.set_mode(rm.MODE_EXACT)
     ctx.set_specialize(2)
     t0 = time.perf_counter()
-    img = ctx.render(u, 3, words, W, H)
+    img = ctx.render(u, ncmd, words, W, H)
     first_ms = (time.perf_counter() - t0) * 1e3
     assert np.array_equal(img, ref)
     assert ctx.spec_info()["launches"] == 0           # painted by the interpreter, the compile had only just started
     assert first_ms < 100, first_ms                   # no compile in the paint path (a compile is 150-600 ms)
     deadline = time.time() + 30
     while ctx.spec_info()["launches"] == 0 and time.time() < deadline:
-        assert np.array_equal(ctx.render(u, 3, words, W, H), ref)
+        assert np.array_equal(ctx.render(u, ncmd, words, W, H), ref)
         time.sleep(0.02)
     info = ctx.spec_info()
-    assert info["active"] and info["launches"] >= 1 and info["compiles"] == 1
+    assert info["active"] and info["launches"] >= 1 and info["compiles"] == 1 and ctx.spec_tier == 1
+    # other VALUES of the same structure: adopted from the cache at once, no compile, no interpreter frame
+    w2 = list(words)
+    w2[4] = h.fbits(0.55)
+    n0 = info["launches"]
+    assert np.array_equal(ctx.render(u, ncmd, w2, W, H), h.oracle_render(u, ncmd, w2, W, H)["rgba"])
+    assert ctx.spec_info()["launches"] == n0 + 1 and ctx.spec_info()["compiles"] == 1
     # words that change while a compile is in flight: its result is dropped, nothing crashes, frames stay right
     for i in range(4):
         w2 = h.sphere((0.01 * i, 0.2, -0.1), 0.8 + 0.01 * i)
         assert np.array_equal(ctx.render(u, 1, w2, W, H), h.oracle_render(u, 1, w2, W, H)["rgba"])
     with pytest.raises(rm.RmError):
         ctx.set_specialize(3)
+
+
+
+# ---- round 2: kernels are compiled per program STRUCTURE; values travel as kernel arguments ------------
+def test_dragging_a_radius_for_1000_frames_compiles_once(rm, ctx):
+    """The reference re-flattens and re-uploads the program every frame (renderer.rs:224-239) and an editor drags values:
+    1000 frames, one radius changing per frame -> ONE compile, every frame specialised and byte-identical to the oracle."""
+    W, H = 48, 27
+    u = h.orbit_uniforms(W, H, yaw=0.6, pitch=0.4)
+    ctx.set_mode(rm.MODE_EXACT)
+    ctx.set_specialize(1)
+    c0 = None
+    for f in range(1000):
+        r = 0.4 + 0.0005 * f
+        words = h.box((0.05, 0.0, 0.0), (1, 1, 1)) + h.sphere((0.0, 1.0, 0.0), 1.0) + [h.OP_UNION] + h.sphere((0.6, 0.3, 1.0), r) + [h.OP_SUBTRACTION]
+        img = ctx.render(u, 5, words, W, H)
+        info = ctx.spec_info()
+        if c0 is None:
+            c0 = info["compiles"]            # 1, or 0 if an earlier test compiled this structure
+            assert c0 <= 1
+        assert info["active"] and info["launches"] == f + 1 and info["compiles"] == c0, (f, info)
+        assert ctx.spec_tier == 1            # the words never stay put: no literal-tier compile either
+        if f % 7 == 0 or f == 999:
+            assert np.array_equal(img, h.oracle_render(u, 5, words, W, H)["rgba"]), f
+    assert ctx.program_uploads >= 1000
+
+
+def test_streaming_more_structures_than_the_cache_holds_keeps_specialising(rm, ctx):
+    """LRU eviction instead of a permanent cap: with room for 6 kernels, 20 distinct structures are all painted
+    specialised and right; evicted kernels are unloaded (cudaLibraryUnload) once no context paints with them."""
+    W, H = 64, 36
+    u = h.orbit_uniforms(W, H, yaw=0.6, pitch=0.4)
+    ctx.set_mode(rm.MODE_EXACT)
+    ctx.set_specialize(1)
+    ctx.set_spec_literal_after(0)
+    before = rm.spec_cache()
+    try:
+        rm.spec_cache(6)
+        ev0 = rm.spec_cache()["evictions"]
+        rng = np.random.default_rng(77)
+        seen = []
+        for i in range(20):
+            words, cmd = h.random_program(rng, 2 + i % 5, ext=(i % 3 == 0))
+            words = list(words)
+            for j in range(i + 1):   # i + 1 more leaves: every structure of the stream has its own length
+                words += h.sphere((0.1 * i, 0.05 * j, 0), 0.3) + [h.OP_UNION]
+            cmd += 2 * (i + 1)
+            img = ctx.render(u, cmd, words, W, H)
+            info = ctx.spec_info()
+            assert info["active"], (i, info["status"])
+            assert np.array_equal(img, h.oracle_render(u, cmd, words, W, H)["rgba"]), i
+            seen.append((cmd, words))
+        st = rm.spec_cache()
+        assert st["entries"] <= 6 and st["evictions"] - ev0 >= 10, st
+        # an evicted structure comes back with a fresh compile and still paints right
+        cmd, words = seen[0]
+        n0 = ctx.spec_info()["compiles"]
+        assert np.array_equal(ctx.render(u, cmd, words, W, H), h.oracle_render(u, cmd, words, W, H)["rgba"])
+        assert ctx.spec_info()["compiles"] == n0 + 1 and ctx.spec_info()["active"]
+    finally:
+        rm.spec_cache(before["capacity"])
+
+
+def test_words_that_stay_put_are_promoted_to_the_literal_tier_in_the_background(rm, ctx):
+    import time
+    W, H = 96, 54
+    u = h.orbit_uniforms(W, H, yaw=0.6, pitch=0.4)
+    words = h.box((0.07, 0.0, 0.0), (0.9, 1, 1)) + h.sphere((0.0, 1.0, 0.0), 1.0) + [h.OP_SMOOTH_UNION, h.fbits(0.31)]
+    ref = h.oracle_render(u, 3, words, W, H)["rgba"]
+    ctx.set_mode(rm.MODE_EXACT)
+    ctx.set_specialize(1)
+    ctx.set_spec_literal_after(4)
+    tiers = []
+    deadline = time.time() + 60
+    while time.time() < deadline:
+        t0 = time.perf_counter()
+        img = ctx.render(u, 3, words, W, H)
+        ms = (time.perf_counter() - t0) * 1e3
+        assert np.array_equal(img, ref)
+        tiers.append(ctx.spec_tier)
+        if len(tiers) > 1:
+            assert ms < 100, (len(tiers), ms)       # only the very first paint may wait for a compile (policy 1)
+        if tiers[-1] == 2:
+            break
+        time.sleep(0.01)
+    assert tiers[0] == 1 and tiers[-1] == 2 and tiers[:4] == [1, 1, 1, 1], tiers
+    assert np.array_equal(ctx.render(u, 3, words, W, H), ref)     # painted by the literal kernel
+    c0 = ctx.spec_info()["compiles"]
+    w2 = list(words)
+    w2[4] = h.fbits(0.8)                                           # a value changes: structure kernel again, no compile
+    assert np.array_equal(ctx.render(u, 3, w2, W, H), h.oracle_render(u, 3, w2, W, H)["rgba"])
+    assert ctx.spec_tier == 1 and ctx.spec_info()["compiles"] == c0
+    ctx.set_spec_literal_after(0)                                   # structure tier only
+    for _ in range(6):
+        assert np.array_equal(ctx.render(u, 3, words, W, H), ref)
+    assert ctx.spec_tier == 1
+
+
+def test_specialize_compiles_both_tiers_at_once_and_fast_mode_tiers_agree(rm, ctx):
+    W, H = 384, 216
+    cmd, words = h.scene_s2()
+    u = h.orbit_uniforms(W, H, yaw=0.6, pitch=0.4)
+    ctx.set_mode(rm.MODE_FAST)
+    ctx.prepare(u, cmd, words)
+    ctx.specialize()
+    assert ctx.spec_tier == 2
+    lit = ctx.render(u, cmd, words, W, H)
+    ctx.set_spec_literal_after(0)
+    assert ctx.spec_tier == 1
+    par = ctx.render(u, cmd, words, W, H)
+    ctx.set_specialize(False)
+    interp = ctx.render(u, cmd, words, W, H)
+    for a, b in ((lit, par), (par, interp)):
+        d = np.abs(a.astype(np.int16) - b.astype(np.int16)).max(-1)
+        assert d.max() <= 1 and (d > 0).mean() <= 2e-3, (int(d.max()), float((d > 0).mean()))

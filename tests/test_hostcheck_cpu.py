@@ -278,6 +278,18 @@ def test_validation_agrees_with_the_oracle_on_random_extended_streams(hc):
 
 
 # ---- run-time generated map_scene code (rm_jit.cu) ------------------------------------------------------------------
+def _spec_params(rm_lib, cmd, w, mode_exact):
+    """The parameter block the generated structure-tier kernel reads (rm_spec_params), padded like the kernel argument."""
+    rm_lib.rm_spec_params.restype = C.c_int
+    rm_lib.rm_spec_params.argtypes = [C.c_uint32, u32p, C.c_uint32, C.c_int, f32p, C.c_size_t, C.POINTER(C.c_size_t)]
+    need = C.c_size_t()
+    rc = rm_lib.rm_spec_params(cmd, w.ctypes.data_as(u32p), w.size, 0 if mode_exact else 1, None, 0, C.byref(need))
+    assert rc == 0, rc
+    out = np.zeros(max(4, need.value), np.float32)
+    rm_lib.rm_spec_params(cmd, w.ctypes.data_as(u32p), w.size, 0 if mode_exact else 1, out.ctypes.data_as(f32p), out.size, None)
+    return out
+
+
 def _spec_map_on_host(tmp_path, rm_lib, cmd, words, mode_exact, R, pts):
     """Compiles the generated SpecMap functor for the host (kernel wrapper cut off) and evaluates it at pts."""
     w = np.ascontiguousarray(np.asarray(words, np.uint32))
@@ -286,13 +298,15 @@ def _spec_map_on_host(tmp_path, rm_lib, cmd, words, mode_exact, R, pts):
     rc = rm_lib.rm_spec_source(cmd, w.ctypes.data_as(u32p), w.size, 0 if mode_exact else 1, R, buf, 1 << 20, C.byref(need))
     assert rc == 0, rc
     src = buf.value.decode()
-    m = re.search(r"rm::SpecMap<(true|false), (\d)> map;", src)
+    m = re.search(r"rm::SpecMap<(true|false), (\d)> map\(", src)
     ex, r = m.group(1), int(m.group(2))
     src = src[:src.index('extern "C" __global__')]
+    params = _spec_params(rm_lib, cmd, w, mode_exact)
     src = '#include "cuda_runtime.h"\n' + src + f"""
-extern "C" void hc_spec(const float *pts, unsigned long long n, float max_dist, float *out) {{
-    rm::SpecMap<{ex}, {r}> map;
-    map.max_dist = max_dist;
+extern "C" void hc_spec(const float *pts, unsigned long long n, float max_dist, const float *params, float *out) {{
+    rm::SpecParams P;
+    memcpy(&P, params, sizeof P);
+    rm::SpecMap<{ex}, {r}> map(max_dist, P);
     for (unsigned long long i = 0; i < n; i += {r}) {{
         float px[{r}], py[{r}], pz[{r}], s[{r}];
         for (int k = 0; k < {r}; ++k) {{ unsigned long long j = i + k < n ? i + k : n - 1; px[k] = pts[3 * j]; py[k] = pts[3 * j + 1]; pz[k] = pts[3 * j + 2]; }}
@@ -301,15 +315,17 @@ extern "C" void hc_spec(const float *pts, unsigned long long n, float max_dist, 
     }}
 }}
 """
-    cu = tmp_path / "spec.cpp"
+    # a fresh file name per build: dlopen of a path it has already loaded would hand back the OLD code
+    tag = f"{abs(hash((cmd, bytes(w), mode_exact, R)))}"
+    cu = tmp_path / f"spec_{tag}.cpp"
     cu.write_text(src)
-    so = tmp_path / "libspec.so"
+    so = tmp_path / f"libspec_{tag}.so"
     subprocess.run(CXX + ["-o", str(so), str(cu)], check=True, capture_output=True)
     lib = C.CDLL(str(so))
-    lib.hc_spec.argtypes = [f32p, C.c_uint64, C.c_float, f32p]
+    lib.hc_spec.argtypes = [f32p, C.c_uint64, C.c_float, f32p, f32p]
     pts = np.ascontiguousarray(pts, np.float32)
     out = np.zeros(len(pts), np.float32)
-    lib.hc_spec(pts.ctypes.data_as(f32p), len(pts), 100.0, out.ctypes.data_as(f32p))
+    lib.hc_spec(pts.ctypes.data_as(f32p), len(pts), 100.0, params.ctypes.data_as(f32p), out.ctypes.data_as(f32p))
     return out, r
 
 

@@ -194,6 +194,8 @@ SPEC_DRIVER = """
 extern "C" int hc_spec_paint(const void *uniforms144, const void *limits12, uint32_t W, uint32_t H, uint32_t row0, uint32_t nrows,
                              uint32_t strip_rows, uint32_t strip_pitch, int dst_frame_rows, uint8_t *dst, size_t pitch,
                              uint64_t *counters4, uint8_t *aov_cls, float *aov_t) {
+    rm::SpecParams P;
+    memcpy(&P, hc_spec_params, sizeof P);
     float u[36], lim[2];
     uint32_t max_iter;
     memcpy(u, uniforms144, 144); memcpy(lim, limits12, 8); memcpy(&max_iter, (const char *)limits12 + 8, 4);
@@ -201,7 +203,7 @@ extern "C" int hc_spec_paint(const void *uniforms144, const void *limits12, uint
     fp.strip_rows = strip_rows; fp.strip_pitch = strip_pitch; fp.dst_frame_rows = dst_frame_rows ? 1u : 0u;
     const uint32_t tile_h = rm::direct_tile_rows(HC_R);
     const unsigned grid = ((W + RM_DIRECT_TILE_W - 1) / RM_DIRECT_TILE_W) * ((nrows + tile_h - 1) / tile_h);
-    hc_run_grid(grid, RM_DIRECT_THREADS, [&] { rm_spec(fp, dst, pitch, (unsigned long long *)counters4, aov_cls, aov_t); });
+    hc_run_grid(grid, RM_DIRECT_THREADS, [&] { rm_spec(fp, P, dst, pitch, (unsigned long long *)counters4, aov_cls, aov_t); });
     return 0;
 }
 """
@@ -214,10 +216,15 @@ def spec_paint(tmp_path, rm_lib, cmd, words, u, W, H, exact=True, R=0, **kw):
     rc = rm_lib.rm_spec_source(cmd, w.ctypes.data_as(u32p), w.size, 0 if exact else 1, R, buf, 1 << 20, C.byref(need))
     assert rc == 0, rc
     src = buf.value.decode()
-    r = int(re.search(r"rm::SpecMap<(?:true|false), (\d)> map;", src).group(1))
+    r = int(re.search(r"rm::SpecMap<(?:true|false), (\d)> map\(", src).group(1))
     cu = tmp_path / "spec_kernel.cpp"
-    cu.write_text('#include "hc_grid.h"\n' + src + f"\n#define HC_R {r}\n" + SPEC_DRIVER)
-    so = tmp_path / f"libspec_kernel_{abs(hash((cmd, bytes(w), exact, R)))}.so"
+    import test_hostcheck_cpu as thc
+    params = thc._spec_params(rm_lib, cmd, w, exact)
+    table = "static const float hc_spec_params[] = {" + ", ".join("%sf" % repr(float(x)) if np.isfinite(x) else "0.0f" for x in params) + "};\n"
+    table = "static const unsigned hc_spec_params_bits[] = {" + ", ".join("0x%08xu" % int(x) for x in params.view(np.uint32)) + "};\n" \
+            "#define hc_spec_params ((const float *)hc_spec_params_bits)\n"
+    cu.write_text('#include "hc_grid.h"\n' + src + f"\n#define HC_R {r}\n" + table + SPEC_DRIVER)
+    so = tmp_path / f"libspec_kernel_{abs(hash((cmd, bytes(w), exact, R)))}.so"  # params are baked into the driver: one .so per word stream
     subprocess.run(CXX + ["-pthread", f"-I{HC_DIR}", "-o", str(so), str(cu)], check=True, capture_output=True)
     lib = C.CDLL(str(so))
     lib.hc_spec_paint.restype = C.c_int

@@ -32,14 +32,16 @@ def test_source_is_one_ssa_value_per_command_in_stream_order(rm):
     assert "direct_body<true, 4, false, false>" in rm.spec_source(cmd, words, rm.MODE_EXACT)
 
 
-def test_constants_are_emitted_by_their_bits(rm):
+def test_literal_tier_emits_constants_by_their_bits(rm):
+    lit = rm.MODE_FAST | rm.SPEC_LITERAL_TIER
     words = h.sphere((0.1, -2.5, 3.0e-7), 1.25)
-    src = rm.spec_source(1, words, rm.MODE_FAST)
+    src = rm.spec_source(1, words, lit)
     for w in words[1:]:
         assert "__uint_as_float(0x%08xu)" % w in src
     k = 0.3
     words = h.sphere((0, 0, 0), 1) + h.sphere((1, 0, 0), 1) + [103, h.fbits(k)]
-    src = rm.spec_source(3, words, rm.MODE_FAST)
+    # exact mode reads k (and 1/k when it is exact); fast mode reads k*s and s with s = sqrt(1/(4k))
+    src = rm.spec_source(3, words, rm.MODE_EXACT | rm.SPEC_LITERAL_TIER)
     inv = np.float32(1.0) / np.float32(k)
     c4k = np.float32(0.25) / np.float32(k)
     m = re.search(r"op_smooth<EX>\(v0\[r\], v1\[r\], (\S+), (\S+), (\S+), (true|false)\)", src)
@@ -47,8 +49,37 @@ def test_constants_are_emitted_by_their_bits(rm):
     assert m.group(2) == "__uint_as_float(0x%08xu)" % int(inv.view(np.uint32))
     assert m.group(3) == "__uint_as_float(0x%08xu)" % int(c4k.view(np.uint32))
     assert m.group(4) == "false"
+    src = rm.spec_source(3, words, lit)
+    s = np.float32(np.sqrt(0.25 / np.float64(np.float32(k))))
+    ks = np.float32(np.float64(np.float32(k)) * np.sqrt(0.25 / np.float64(np.float32(k))))
+    m = re.search(r"op_smooth<EX>\(v0\[r\], v1\[r\], 0.0f, (\S+), (\S+), false\)", src)
+    assert m and m.group(1) == "__uint_as_float(0x%08xu)" % int(ks.view(np.uint32)) and m.group(2) == "__uint_as_float(0x%08xu)" % int(s.view(np.uint32))
     words[-1] = h.fbits(0.25)  # power of two: the exact-mode divide becomes a multiply by the exact reciprocal
-    assert ", true)" in rm.spec_source(3, words, rm.MODE_FAST)
+    assert ", true)" in rm.spec_source(3, words, rm.MODE_EXACT | rm.SPEC_LITERAL_TIER)
+
+
+def test_structure_tier_reads_parameters_from_the_kernel_argument(rm):
+    """The default kernel depends on the STRUCTURE only: parameters are P.f[i] (a __grid_constant__ kernel argument), except
+    exact zeros, which stay literals (and are part of the structure)."""
+    a = h.sphere((0.1, -2.5, 0.0), 1.25) + h.box((0, 0, 0), (1, 2, 3)) + [103, h.fbits(0.3)]
+    b = h.sphere((0.7, 9.5, 0.0), 0.25) + h.box((0, 0, 0), (3, 1, 2)) + [103, h.fbits(0.7)]
+    sa, sb = rm.spec_source(3, a), rm.spec_source(3, b)
+    assert sa == sb                                     # same structure, other values: the same code
+    assert "__uint_as_float" not in sa and "const __grid_constant__ rm::SpecParams P" in sa
+    assert re.search(r"sd_sphere<EX>\(px\[r\], py\[r\], pz\[r\], P.f\[0\], P.f\[1\], 0.0f, P.f\[2\]\)", sa)
+    assert re.search(r"sd_box<EX>\(px\[r\], py\[r\], pz\[r\], 0.0f, 0.0f, 0.0f, P.f\[4\], P.f\[5\], P.f\[6\]\)", sa)   # 16-byte aligned group
+    pa, pb = rm.spec_params(3, a), rm.spec_params(3, b)
+    assert pa.size == pb.size and pa.size % 4 == 0
+    np.testing.assert_array_equal(pa[:3], np.float32([0.1, -2.5, 1.25]))
+    np.testing.assert_array_equal(pa[4:7], np.float32([1, 2, 3]))
+    np.testing.assert_array_equal(pb[:3], np.float32([0.7, 9.5, 0.25]))
+    c = h.sphere((0.1, -2.5, 0.5), 1.25) + h.box((0, 0, 0), (1, 2, 3)) + [103, h.fbits(0.3)]
+    assert rm.spec_source(3, c) != sa                   # a zero became non-zero: another structure
+    # exact mode: whether k is a power of two is structural (multiply by 1/k instead of dividing)
+    e1 = rm.spec_source(3, a, rm.MODE_EXACT)
+    a2 = list(a)
+    a2[-1] = h.fbits(0.25)
+    assert rm.spec_source(3, a2, rm.MODE_EXACT) != e1 and rm.spec_source(3, a2, rm.MODE_FAST) == sa
 
 
 def test_rays_per_thread_follow_the_code_size(rm):
@@ -78,15 +109,24 @@ def test_deep_stacks_and_empty_program(rm):
     assert "out[r] = max_dist" in src
 
 
-@pytest.mark.parametrize("bad,code", [([5], -3), ([100], -5), (h.sphere((0, 0, 0), 1) * 2, -5)])
+@pytest.mark.parametrize("bad,code", [([5], -3), ([100], -5), (h.sphere((0, 0, 0), 1)[:3], -5)])
 def test_invalid_streams_are_rejected_with_the_validation_codes(rm, bad, code):
     with pytest.raises(rm.RmError) as e:
-        rm.spec_source(len(bad) if bad[0] != 0 else 2, bad)
+        rm.spec_source(1, bad)
     assert e.value.code == code
 
 
+def test_generator_accepts_what_the_decoder_accepts(rm):
+    """ADVICE r1: a stream that leaves MORE than one value is valid — the shader's final pop_value takes the top
+    (wgsl:200-202) — for rm_prepare and for the specialiser alike."""
+    two = h.sphere((0, 0, 0), 1) + h.sphere((2, 0, 0), 0.5)
+    assert rm.validate_program(2, two) == 0
+    src = rm.spec_source(2, two)
+    assert "RM_FOR_R out[r] = v1[r];" in src
+
+
 @pytest.mark.parametrize("scene", ["s0", "s1", "s2"])
-@pytest.mark.parametrize("mode", [0, 1])
+@pytest.mark.parametrize("mode", [0, 1, 0x100, 0x101])
 def test_generated_source_compiles_for_sm_100a(rm, scene, mode):
     cmd, words = getattr(h, "scene_" + scene)()
     r = rm.spec_compile_check(cmd, words, mode)
