@@ -69,100 +69,112 @@ __device__ __forceinline__ void direct_body(const FrameParams &fp, uint8_t *__re
         if (fp.max_iter > 0) live = (1u << R) - 1u;
     }
 
-    float px_[R], py_[R], pz_[R], s[R];
-    // ---------------- march: all live rays of the thread take one step per trip (wgsl:88-115) ----------------
-    for (uint32_t it = 0; live != 0; ++it) {
-        RM_FOR_R {  // pos = origin + direction * dist   wgsl:91
-            px_[r] = A::mad(rdx[r], dist[r], ox);
-            py_[r] = A::mad(rdy[r], dist[r], oy);
-            pz_[r] = A::mad(rdz[r], dist[r], oz);
-        }
-        RM_FOR_R RM_OPAQUE_F3(px_[r], py_[r], pz_[r]);
-        map(px_, py_, pz_, s);
-        const bool last = it + 1 >= fp.max_iter;  // loop bound wgsl:90
-        RM_FOR_R {
-            const uint32_t bit = 1u << r;
-            if (live & bit) {
-                if (COUNT) ++c_step;
-                if (s[r] < fp.min_dist) {  // wgsl:97: hit, dist stays at the hit distance
-                    hit |= bit;
-                    live &= ~bit;
-                } else if (s[r] > fp.max_dist) {  // wgsl:109-111
-                    live &= ~bit;
-                } else {
-                    dist[r] = A::add(dist[r], s[r]);  // wgsl:114
-                    if (last) live &= ~bit;
-                }
-            }
-        }
-    }
-    // ---------------- what the rays that never hit get: floor or sky (wgsl:117-130), after the march so that nothing of it
-    // is live across the loop; always with exact roundings (one division per missed ray) ----------------
     float code[R];
     float t_miss[AOV ? R : 1];
     int cls_miss[AOV ? R : 1];
-    RM_FOR_R {
-        code[r] = RM_CODE_SKY;
-        if constexpr (AOV) { t_miss[r] = 0.f; cls_miss[r] = 0; }
-        if (inside && !((hit >> r) & 1u)) {
-            const float o[3] = {ox, oy, oz}, d[3] = {rdx[r], rdy[r], rdz[r]};
-            float c[3], t;
-            const int cls = shade_miss(o, d, c, t);
-            code[r] = cls == 0 ? RM_CODE_SKY : (c[0] > 0.2f ? RM_CODE_FLOOR_LIGHT : RM_CODE_FLOOR_DARK);
-            if (COUNT && cls != 0) ++c_floor;
-            if constexpr (AOV) { t_miss[r] = t; cls_miss[r] = cls; }
-        }
-    }
-    // ---------------- normals + diffuse term of the rays that hit (wgsl:98-105,138-143) ----------------
-    const uint32_t hit0 = hit;
-    const float ep = RM_NORMAL_EPS, en = -RM_NORMAL_EPS;
-    if constexpr (R == 2) {  // a hit ray's 4 taps take two passes of the 2-wide map: taps 0,1 then taps 2,3
-        while (hit != 0) {
-            const int rr = __ffs((int)hit) - 1;
-            hit &= hit - 1u;
-            const float dx = rr ? rdx[1] : rdx[0], dy = rr ? rdy[1] : rdy[0], dz = rr ? rdz[1] : rdz[0];
-            const float dd = rr ? dist[1] : dist[0];
-            const float hx = A::mad(dx, dd, ox), hy = A::mad(dy, dd, oy), hz = A::mad(dz, dd, oz);
-            float a[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll 1
-            for (int pass = 0; pass < 2; ++pass) {  // taps wgsl:138-142: (+,-,-) (-,-,+) | (-,+,-) (+,+,+)
-                px_[0] = __fadd_rn(hx, pass ? en : ep); py_[0] = __fadd_rn(hy, pass ? ep : en); pz_[0] = __fadd_rn(hz, en);
-                px_[1] = __fadd_rn(hx, pass ? ep : en); py_[1] = __fadd_rn(hy, pass ? ep : en); pz_[1] = __fadd_rn(hz, ep);
-                map(px_, py_, pz_, s);
-                if (pass == 0) { a[0] = s[0]; a[1] = s[1]; } else { a[2] = s[0]; a[3] = s[1]; }
-            }
-            const float c = wf_shade<EX>(a[0], a[1], a[2], a[3], hx, hy, hz);
-            if (rr) code[1] = c; else code[0] = c;
-            if (COUNT) ++c_hit;
-        }
-    } else {
-        while (hit != 0) {
-            int rr[(R + 3) / 4];
-            float hx[(R + 3) / 4], hy[(R + 3) / 4], hz[(R + 3) / 4];
-#pragma unroll
-            for (int j = 0; j < R / 4; ++j) {  // R/4 hit rays per trip: ray j's 4 taps fill slots 4j..4j+3
-                rr[j] = hit ? __ffs((int)hit) - 1 : -1;
-                hit &= hit - 1u;  // 0 stays 0
-                float dx = 0.f, dy = 0.f, dz = 0.f, dd = 0.f;
-                RM_FOR_R if (r == rr[j]) { dx = rdx[r]; dy = rdy[r]; dz = rdz[r]; dd = dist[r]; }
-                hx[j] = A::mad(dx, dd, ox); hy[j] = A::mad(dy, dd, oy); hz[j] = A::mad(dz, dd, oz);
-                // tetrahedron taps wgsl:138-142: (+,-,-) (-,-,+) (-,+,-) (+,+,+), eps = 1e-4
-                px_[4 * j + 0] = __fadd_rn(hx[j], ep); py_[4 * j + 0] = __fadd_rn(hy[j], en); pz_[4 * j + 0] = __fadd_rn(hz[j], en);
-                px_[4 * j + 1] = __fadd_rn(hx[j], en); py_[4 * j + 1] = __fadd_rn(hy[j], en); pz_[4 * j + 1] = __fadd_rn(hz[j], ep);
-                px_[4 * j + 2] = __fadd_rn(hx[j], en); py_[4 * j + 2] = __fadd_rn(hy[j], ep); pz_[4 * j + 2] = __fadd_rn(hz[j], en);
-                px_[4 * j + 3] = __fadd_rn(hx[j], ep); py_[4 * j + 3] = __fadd_rn(hy[j], ep); pz_[4 * j + 3] = __fadd_rn(hz[j], ep);
+    uint32_t hit0 = 0;
+    {
+        float px_[R], py_[R], pz_[R], s[R];
+        // ---------------- march: all live rays of the thread take one step per trip (wgsl:88-115) ----------------
+        for (uint32_t it = 0; live != 0; ++it) {
+            RM_FOR_R {  // pos = origin + direction * dist   wgsl:91
+                px_[r] = A::mad(rdx[r], dist[r], ox);
+                py_[r] = A::mad(rdy[r], dist[r], oy);
+                pz_[r] = A::mad(rdz[r], dist[r], oz);
             }
             RM_FOR_R RM_OPAQUE_F3(px_[r], py_[r], pz_[r]);
             map(px_, py_, pz_, s);
-#pragma unroll
-            for (int j = 0; j < R / 4; ++j) {
-                if (rr[j] >= 0) {
-                    const float c = wf_shade<EX>(s[4 * j], s[4 * j + 1], s[4 * j + 2], s[4 * j + 3], hx[j], hy[j], hz[j]);
-                    RM_FOR_R if (r == rr[j]) code[r] = c;
-                    if (COUNT) ++c_hit;
+            const bool last = it + 1 >= fp.max_iter;  // loop bound wgsl:90
+            RM_FOR_R {
+                const uint32_t bit = 1u << r;
+                if (live & bit) {
+                    if (COUNT) ++c_step;
+                    if (s[r] < fp.min_dist) {  // wgsl:97: hit, dist stays at the hit distance
+                        hit |= bit;
+                        live &= ~bit;
+                    } else if (s[r] > fp.max_dist) {  // wgsl:109-111
+                        live &= ~bit;
+                    } else {
+                        dist[r] = A::add(dist[r], s[r]);  // wgsl:114
+                        if (last) live &= ~bit;
+                    }
                 }
             }
         }
+        // ---------------- normals + diffuse term of the rays that hit (wgsl:98-105,138-143) ----------------
+        hit0 = hit;
+        RM_FOR_R code[r] = RM_CODE_SKY;
+        // floor or sky for the rays that never hit (wgsl:117-130): after the march so that nothing of it is live across the
+        // loop; always with exact roundings (one division per missed ray).  With 2 rays per thread it runs BEFORE the taps
+        // (the ray directions are then dead while MAP runs again), else after them.
+        auto shade_missed = [&]() {
+            RM_FOR_R {
+                if constexpr (AOV) { t_miss[r] = 0.f; cls_miss[r] = 0; }
+                if (inside && !((hit0 >> r) & 1u)) {
+                    const float o[3] = {ox, oy, oz}, d[3] = {rdx[r], rdy[r], rdz[r]};
+                    float c[3], t;
+                    const int cls = shade_miss(o, d, c, t);
+                    code[r] = cls == 0 ? RM_CODE_SKY : (c[0] > 0.2f ? RM_CODE_FLOOR_LIGHT : RM_CODE_FLOOR_DARK);
+                    if (COUNT && cls != 0) ++c_floor;
+                    if constexpr (AOV) { t_miss[r] = t; cls_miss[r] = cls; }
+                }
+            }
+        };
+        if constexpr (R == 2) shade_missed();
+        const float ep = RM_NORMAL_EPS, en = -RM_NORMAL_EPS;
+        if constexpr (R == 2) {
+            // Both rays' hit positions first: the directions and distances are then dead, and the tap loop below carries
+            // only what it needs across its two inlined evaluations of MAP.  A hit ray's 4 taps take two passes of the
+            // 2-wide map: taps 0,1 then taps 2,3.
+            const float h0x = A::mad(rdx[0], dist[0], ox), h0y = A::mad(rdy[0], dist[0], oy), h0z = A::mad(rdz[0], dist[0], oz);
+            const float h1x = A::mad(rdx[1], dist[1], ox), h1y = A::mad(rdy[1], dist[1], oy), h1z = A::mad(rdz[1], dist[1], oz);
+            while (hit != 0) {
+                const int rr = __ffs((int)hit) - 1;
+                hit &= hit - 1u;
+                const float hx = rr ? h1x : h0x, hy = rr ? h1y : h0y, hz = rr ? h1z : h0z;
+                float a0 = 0.f, a1 = 0.f;
+                float c = 0.f;
+    #pragma unroll 1
+                for (int pass = 0; pass < 2; ++pass) {  // taps wgsl:138-142: (+,-,-) (-,-,+) | (-,+,-) (+,+,+)
+                    px_[0] = __fadd_rn(hx, pass ? en : ep); py_[0] = __fadd_rn(hy, pass ? ep : en); pz_[0] = __fadd_rn(hz, en);
+                    px_[1] = __fadd_rn(hx, pass ? ep : en); py_[1] = __fadd_rn(hy, pass ? ep : en); pz_[1] = __fadd_rn(hz, ep);
+                    map(px_, py_, pz_, s);
+                    if (pass == 0) { a0 = s[0]; a1 = s[1]; }
+                    else c = wf_shade<EX>(a0, a1, s[0], s[1], hx, hy, hz);
+                }
+                if (rr) code[1] = c; else code[0] = c;
+                if (COUNT) ++c_hit;
+            }
+        } else {
+            while (hit != 0) {
+                int rr[(R + 3) / 4];
+                float hx[(R + 3) / 4], hy[(R + 3) / 4], hz[(R + 3) / 4];
+    #pragma unroll
+                for (int j = 0; j < R / 4; ++j) {  // R/4 hit rays per trip: ray j's 4 taps fill slots 4j..4j+3
+                    rr[j] = hit ? __ffs((int)hit) - 1 : -1;
+                    hit &= hit - 1u;  // 0 stays 0
+                    float dx = 0.f, dy = 0.f, dz = 0.f, dd = 0.f;
+                    RM_FOR_R if (r == rr[j]) { dx = rdx[r]; dy = rdy[r]; dz = rdz[r]; dd = dist[r]; }
+                    hx[j] = A::mad(dx, dd, ox); hy[j] = A::mad(dy, dd, oy); hz[j] = A::mad(dz, dd, oz);
+                    // tetrahedron taps wgsl:138-142: (+,-,-) (-,-,+) (-,+,-) (+,+,+), eps = 1e-4
+                    px_[4 * j + 0] = __fadd_rn(hx[j], ep); py_[4 * j + 0] = __fadd_rn(hy[j], en); pz_[4 * j + 0] = __fadd_rn(hz[j], en);
+                    px_[4 * j + 1] = __fadd_rn(hx[j], en); py_[4 * j + 1] = __fadd_rn(hy[j], en); pz_[4 * j + 1] = __fadd_rn(hz[j], ep);
+                    px_[4 * j + 2] = __fadd_rn(hx[j], en); py_[4 * j + 2] = __fadd_rn(hy[j], ep); pz_[4 * j + 2] = __fadd_rn(hz[j], en);
+                    px_[4 * j + 3] = __fadd_rn(hx[j], ep); py_[4 * j + 3] = __fadd_rn(hy[j], ep); pz_[4 * j + 3] = __fadd_rn(hz[j], ep);
+                }
+                RM_FOR_R RM_OPAQUE_F3(px_[r], py_[r], pz_[r]);
+                map(px_, py_, pz_, s);
+    #pragma unroll
+                for (int j = 0; j < R / 4; ++j) {
+                    if (rr[j] >= 0) {
+                        const float c = wf_shade<EX>(s[4 * j], s[4 * j + 1], s[4 * j + 2], s[4 * j + 3], hx[j], hy[j], hz[j]);
+                        RM_FOR_R if (r == rr[j]) code[r] = c;
+                        if (COUNT) ++c_hit;
+                    }
+                }
+            }
+        }
+        if constexpr (R != 2) shade_missed();
     }
     if constexpr (AOV) if (inside) {
         const size_t base = ((size_t)ry * fp.W + px) * 16 + grp * R;

@@ -376,7 +376,7 @@ int spec_generate_source(uint32_t cmd_count, const uint32_t *words, uint32_t n_w
     }
     int minb = env_int("RM_SPEC_MINB");
     if (minb <= 0) minb = R == 2 ? 12 : (R == 4 ? 10 : 7);  // measured on B200, profiles/r1_s14_NOTES.md
-    if (sig && !literals) { sig->push_back(0xF0000020u | (uint32_t)R); sig->push_back(0xF0000040u | (uint32_t)minb); }
+    if (sig) { sig->push_back(0xF0000020u | (uint32_t)R); sig->push_back(0xF0000040u | (uint32_t)minb); }
     if (r_out) *r_out = R;
     if (minb_out) *minb_out = minb;
     if (est_out) *est_out = est;

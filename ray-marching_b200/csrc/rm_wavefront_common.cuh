@@ -66,6 +66,80 @@ __device__ __forceinline__ void acc_max(float &acc, float v) { RM_PTX_MAX_ACC(ac
 #define RM_EO_SLACK 1e-4f
 // EXT (N4, rm_program.h): the program may hold Plane primitives and the XOP_* instructions that maintain the
 // evaluation point q of the R rays; primitives then read q.  EXT = false is the reference-set interpreter, unchanged.
+// ---- the fast-mode interpreter of the reference instruction set (map_evalR_tail) --------------------------------------
+// COMMON TAIL: every dispatch path leaves (m, e) per ray and ONE tail writes acc = m - e*e (e = 0 for union / subtraction /
+// intersection / first / push: the value is unchanged bit for bit).  The accumulators then have a single definition per
+// trip and ptxas keeps them in place; in map_evalR below the results of the taken path are copied back to the loop's
+// accumulator registers at the back-edge (8 MOV per instruction with 8 rays).  The smooth union needs the FFMA anyway.
+// Measured on B200 (profiles/r2_interp_NOTES.md): cfg3 with 8 rays 42.8 -> 41.2 ms; with 4 rays (short programs) it
+// loses (cfg2 1.07 -> 1.20 ms), so only the 8-ray kernels use it.  Dispatching PAIRS of instructions at once (decoder-
+// marked, 8 templated pair bodies) and 16 rays per thread were measured too and lost: 44.4 and 42.0 ms.
+template <int R, bool BOX>
+__device__ __forceinline__ void tail_prim(const float4 &q0, const float4 &q1, const float (&px)[R], const float (&py)[R],
+                                          const float (&pz)[R], float (&v)[R]) {
+    if (BOX) { RM_FOR_R v[r] = sd_box<false>(px[r], py[r], pz[r], q0.x, q0.y, q0.z, q0.w, q1.x, q1.y); }
+    else { RM_FOR_R v[r] = sd_sphere<false>(px[r], py[r], pz[r], q0.x, q0.y, q0.z, q0.w); }
+}
+
+template <int R>
+__device__ __forceinline__ void map_evalR_tail(const float4 *__restrict__ prog, uint32_t n_insn, float max_dist,
+                                               const float (&px)[R], const float (&py)[R], const float (&pz)[R],
+                                               float (&acc)[R], float (*spill)[R]) {
+    if (n_insn == 0) {  // wgsl:189-191
+        RM_FOR_R acc[r] = max_dist;
+        return;
+    }
+    RM_FOR_R acc[r] = 0.0f;
+#pragma unroll 1
+    for (uint32_t i = 0; i < n_insn; ++i) {
+        const float4 q0 = prog[3 * i], q1 = prog[3 * i + 1], q2 = prog[3 * i + 2];
+        const uint32_t fl = __float_as_uint(q2.w);
+        float m[R], e[R];
+        if (!(fl & FLAG_POP)) {
+            float v[R];
+            if (fl & FLAG_BOX) tail_prim<R, true>(q0, q1, px, py, pz, v);
+            else tail_prim<R, false>(q0, q1, px, py, pz, v);
+            if (fl & FLAG_SMOOTH) {
+                RM_FOR_R { e[r] = fmaxf(fmaf(-fabsf(acc[r] - v[r]), q2.x, q1.w), 0.0f); m[r] = fminf(acc[r], v[r]); }
+            } else {
+                if (fl & FLAG_UNION) {
+                    RM_FOR_R m[r] = fminf(acc[r], v[r]);
+                } else if (fl & FLAG_SUB) {
+                    RM_FOR_R m[r] = fmaxf(acc[r], -v[r]);
+                } else if (fl & FLAG_INTER) {
+                    RM_FOR_R m[r] = fmaxf(acc[r], v[r]);
+                } else {
+                    if (fl & FLAG_PUSH) {
+                        const uint32_t slot = __float_as_uint(q2.z);
+                        RM_FOR_R spill[slot][r] = acc[r];
+                    }
+                    RM_FOR_R m[r] = v[r];
+                }
+                RM_FOR_R e[r] = 0.0f;
+            }
+        } else {
+            const uint32_t slot = __float_as_uint(q2.z);
+            if (fl & FLAG_SMOOTH) {
+                RM_FOR_R {
+                    const float a = spill[slot][r];
+                    e[r] = fmaxf(fmaf(-fabsf(a - acc[r]), q2.x, q1.w), 0.0f);
+                    m[r] = fminf(a, acc[r]);
+                }
+            } else {
+                if (fl & FLAG_UNION) {
+                    RM_FOR_R m[r] = fminf(spill[slot][r], acc[r]);
+                } else if (fl & FLAG_SUB) {
+                    RM_FOR_R m[r] = fmaxf(spill[slot][r], -acc[r]);
+                } else {
+                    RM_FOR_R m[r] = fmaxf(spill[slot][r], acc[r]);
+                }
+                RM_FOR_R e[r] = 0.0f;
+            }
+        }
+        RM_FOR_R acc[r] = fmaf(-e[r], e[r], m[r]);
+    }
+}
+
 template <bool EX, int R, bool EO = false, bool EXT = false>
 __device__ __forceinline__ void map_evalR(const float4 *__restrict__ prog, uint32_t n_insn, float max_dist,
                                           const float (&px)[R], const float (&py)[R], const float (&pz)[R],
@@ -174,6 +248,8 @@ __device__ __forceinline__ void map_evalR(const float4 *__restrict__ prog, uint3
 }
 
 // map_scene through the decoded-program interpreter (program in shared memory, spill slots in the thread's frame)
+// The 8-ray fast-mode kernels of reference-set programs run map_evalR_tail; exact mode, the early-out, extended programs
+// and the 4-ray kernels run map_evalR.
 template <bool EX, int R, bool EO, bool EXT>
 struct InterpMap {
     const float4 *prog;
@@ -181,7 +257,8 @@ struct InterpMap {
     float max_dist;
     float spill[RM_STACK_MAX - 1][R];
     __device__ __forceinline__ void operator()(const float (&px)[R], const float (&py)[R], const float (&pz)[R], float (&s)[R]) {
-        map_evalR<EX, R, EO, EXT>(prog, n_insn, max_dist, px, py, pz, s, spill);
+        if constexpr (R == 8 && !EX && !EO && !EXT) map_evalR_tail<R>(prog, n_insn, max_dist, px, py, pz, s, spill);
+        else map_evalR<EX, R, EO, EXT>(prog, n_insn, max_dist, px, py, pz, s, spill);
     }
 };
 

@@ -33,11 +33,15 @@ def digest(a: np.ndarray) -> str:
 
 @pytest.mark.parametrize("mode", ["exact", "fast"])
 def test_cfg3_all_kernels_same_bytes_at_3840x2160(rm, ctx, mode):
+    """Exact mode: the four kernels produce the same bytes and the same work counters.  Fast mode: the three that share the
+    round-1 arithmetic (both wavefront generations, one thread per sample) still do; the production kernel generates its rays
+    from the per-frame affine form and blends with min(a,b) - e*e, so it may differ from them by an LSB on a
+    few pixels and by a few flipped threshold decisions — never by more."""
     W, H = 3840, 2160
     cmd, words = h.scene_s2()
     u = h.orbit_uniforms(W, H, yaw=0.6, pitch=0.4)
     ctx.set_mode(rm.MODE_EXACT if mode == "exact" else rm.MODE_FAST)
-    got = {}
+    got, imgs = {}, {}
     for name in ("DIRECT", "WAVEFRONT2", "WAVEFRONT", "SIMPLE"):
         ctx.set_kernel(getattr(rm, "KERNEL_" + name))
         ctx.set_counters(True)
@@ -45,7 +49,16 @@ def test_cfg3_all_kernels_same_bytes_at_3840x2160(rm, ctx, mode):
         got[name] = (digest(img), tuple(int(x) for x in ctx.get_counters()))
         ctx.set_counters(False)
         assert img[..., 3].min() == 255 and img[..., :3].max() > 0
-    assert len({v for v in got.values()}) == 1, got
+        if name in ("DIRECT", "SIMPLE"):
+            imgs[name] = img
+    if mode == "exact":
+        assert len({v for v in got.values()}) == 1, got
+    else:
+        assert len({got[k] for k in ("WAVEFRONT2", "WAVEFRONT", "SIMPLE")}) == 1, got
+        d = np.abs(imgs["DIRECT"].astype(np.int16) - imgs["SIMPLE"].astype(np.int16)).max(-1)
+        assert (d > 2).mean() <= 1e-3 and (d > 0).mean() <= 2e-2, (int(d.max()), float((d > 2).mean()), float((d > 0).mean()))
+        for a, b in zip(got["DIRECT"][1], got["SIMPLE"][1]):
+            assert abs(a - b) <= 1e-4 * max(a, b, 1), (got["DIRECT"][1], got["SIMPLE"][1])
     n_step, n_hit, n_floor, n_sample = got["DIRECT"][1]
     assert n_sample == W * H * 16 and 0 < n_hit < n_sample and n_step > n_sample
 

@@ -32,6 +32,20 @@ def ctx(rm):
     c.close()
 
 
+def same_frames(rm, kut, mode, a, ca, b, cb):
+    """Bit-identity with the first-generation kernel — except the production kernel in FAST mode, which since round 2
+    generates its rays from the per-frame affine form and resolves hit samples as sqrt(albedo)*sqrt(v): there
+    the two may differ by an LSB on a few pixels and by a handful of flipped threshold decisions."""
+    if kut == "direct" and mode == rm.MODE_FAST:
+        d = np.abs(a.astype(np.int16) - b.astype(np.int16)).max(-1)
+        assert (d > 2).mean() <= 2e-3 and (d > 0).mean() <= 5e-2, (int(d.max()), float((d > 2).mean()), float((d > 0).mean()))
+        for x, y in zip(ca, cb):
+            assert abs(int(x) - int(y)) <= max(4, 2e-3 * max(int(x), int(y))), (ca, cb)
+    else:
+        assert np.array_equal(a, b), int((a != b).any(-1).sum())
+        assert np.array_equal(ca, cb), (ca, cb)
+
+
 def both_kernels(rm, ctx, kut, mode, u, cmd, words, W, H, **kw):
     out = []
     ctx.set_mode(mode)
@@ -51,9 +65,9 @@ def both_kernels(rm, ctx, kut, mode, u, cmd, words, W, H, **kw):
 def test_matches_first_generation_kernel_bit_for_bit(rm, ctx, name, W, H, yaw, pitch, mode, kut):
     cmd, words = h.SCENES[name]()
     u = h.orbit_uniforms(W, H, yaw=yaw, pitch=pitch)
-    (a, ca), (b, cb) = both_kernels(rm, ctx, kut, rm.MODE_EXACT if mode == "exact" else rm.MODE_FAST, u, cmd, words, W, H)
-    assert np.array_equal(a, b), int((a != b).any(-1).sum())
-    assert np.array_equal(ca, cb), (ca, cb)
+    m = rm.MODE_EXACT if mode == "exact" else rm.MODE_FAST
+    (a, ca), (b, cb) = both_kernels(rm, ctx, kut, m, u, cmd, words, W, H)
+    same_frames(rm, kut, m, a, ca, b, cb)
 
 
 @pytest.mark.parametrize("W,H", [(37, 23), (8, 4), (1, 1), (9, 5), (130, 3)])
@@ -109,8 +123,7 @@ def test_hit_dense_view_overflows_the_hit_queue(rm, ctx, kut):
     u = h.orbit_uniforms(W, H, yaw=0.0, pitch=0.0, radius=1.6)
     for mode in (rm.MODE_EXACT, rm.MODE_FAST):
         (a, ca), (b, cb) = both_kernels(rm, ctx, kut, mode, u, cmd, words, W, H)
-        assert np.array_equal(a, b)
-        assert np.array_equal(ca, cb), (ca, cb)
+        same_frames(rm, kut, mode, a, ca, b, cb)
     ctx.set_mode(rm.MODE_EXACT)
     ctx.set_kernel(kid(rm, kut))
     assert np.array_equal(ctx.render(u, cmd, words, W, H), h.oracle_render(u, cmd, words, W, H)["rgba"])

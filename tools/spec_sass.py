@@ -27,12 +27,15 @@ def main():
     ap.add_argument("--minb", type=int, default=0)
     ap.add_argument("--dump", default=None)
     ap.add_argument("--src", default=None, help="write the generated source here")
+    ap.add_argument("--lib", default=None, help="another build of librm_b200.so (its generator)")
     a = ap.parse_args()
     if a.minb:
         os.environ["RM_SPEC_MINB"] = str(a.minb)
     import helpers as h
     import rm_import
     rm = rm_import.load()
+    if a.lib:
+        rm.LIB_PATH = Path(a.lib).resolve()
     cmd, words = h.SCENES[a.scene]()
     src = rm.spec_source(cmd, words, (rm.MODE_FAST if a.mode == "fast" else rm.MODE_EXACT) | (rm.SPEC_LITERAL_TIER if a.literals else 0), a.rays)
     if a.src:
