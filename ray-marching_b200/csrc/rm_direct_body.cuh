@@ -66,7 +66,7 @@ __device__ __forceinline__ void direct_body(const FrameParams &fp, uint8_t *__re
             }
         }
         if (COUNT) c_sample = R;
-        if (fp.max_iter > 0) live = (1u << R) - 1u;
+        live = (1u << R) - 1u;
     }
 
     float code[R];
@@ -76,7 +76,9 @@ __device__ __forceinline__ void direct_body(const FrameParams &fp, uint8_t *__re
     {
         float px_[R], py_[R], pz_[R], s[R];
         // ---------------- march: all live rays of the thread take one step per trip (wgsl:88-115) ----------------
-        for (uint32_t it = 0; live != 0; ++it) {
+        // (the loop bound of wgsl:90 is the same for every ray — they all start at trip 0 — so it bounds the loop itself:
+        // rays still live when it runs out fall through to the floor / sky code exactly like aborted ones, Q5)
+        for (uint32_t it = 0; live != 0 && it < fp.max_iter; ++it) {
             RM_FOR_R {  // pos = origin + direction * dist   wgsl:91
                 px_[r] = A::mad(rdx[r], dist[r], ox);
                 py_[r] = A::mad(rdy[r], dist[r], oy);
@@ -84,7 +86,6 @@ __device__ __forceinline__ void direct_body(const FrameParams &fp, uint8_t *__re
             }
             RM_FOR_R RM_OPAQUE_F3(px_[r], py_[r], pz_[r]);
             map(px_, py_, pz_, s);
-            const bool last = it + 1 >= fp.max_iter;  // loop bound wgsl:90
             RM_FOR_R {
                 const uint32_t bit = 1u << r;
                 if (live & bit) {
@@ -96,7 +97,6 @@ __device__ __forceinline__ void direct_body(const FrameParams &fp, uint8_t *__re
                         live &= ~bit;
                     } else {
                         dist[r] = A::add(dist[r], s[r]);  // wgsl:114
-                        if (last) live &= ~bit;
                     }
                 }
             }

@@ -374,9 +374,16 @@ int spec_generate_source(uint32_t cmd_count, const uint32_t *words, uint32_t n_w
             return RM_E_JIT;
         }
     }
+    // Deep programs (2 rays per thread) get ONE out-of-line copy of the scene code, called by the march loop and by the
+    // tap loop, instead of an inlined copy in each: half the code (the instruction cache holds it with room to spare), no
+    // spill at all, half the compile time, and specialisation keeps paying up to 64 leaves instead of 48 (measured on B200,
+    // profiles/r2_s9_crossover.txt: 32 / 48 / 64 leaves x1.26 / 1.21 / 1.18 over the interpreter against x1.25 / 1.13 / 1.03
+    // inlined).  Shallow programs (4 rays) stay inlined: the call costs more than it saves there (cfg2 0.708 vs 0.680 ms).
+    bool noinline = R == 2;
+    if (const char *ns = std::getenv("RM_SPEC_NOINLINE")) noinline = ns[0] == '1';
     int minb = env_int("RM_SPEC_MINB");
-    if (minb <= 0) minb = R == 2 ? 12 : (R == 4 ? 10 : 7);  // measured on B200, profiles/r1_s14_NOTES.md
-    if (sig) { sig->push_back(0xF0000020u | (uint32_t)R); sig->push_back(0xF0000040u | (uint32_t)minb); }
+    if (minb <= 0) minb = R == 2 ? (noinline ? 10 : 12) : (R == 4 ? 10 : 7);  // measured on B200: profiles/r1_s14_NOTES.md, r2_s8_noinline_sweep.jsonl
+    if (sig) { sig->push_back(0xF0000020u | (uint32_t)R); sig->push_back(0xF0000040u | (uint32_t)minb); sig->push_back(0xF0000080u | (noinline ? 1u : 0u)); }
     if (r_out) *r_out = R;
     if (minb_out) *minb_out = minb;
     if (est_out) *est_out = est;
@@ -390,9 +397,23 @@ int spec_generate_source(uint32_t cmd_count, const uint32_t *words, uint32_t n_w
     s += "struct alignas(16) SpecParams { float f[" + std::to_string(par.n ? ((par.n + 3u) & ~3u) : 4u) + "]; };  // the stream's non-zero parameters, in stream order\n";
     s += "template <bool EX, int R>\nstruct SpecMap {\n    float max_dist;\n    const SpecParams &P;  // the kernel's __grid_constant__ argument: every use is a constant-bank operand\n";
     s += "    __device__ __forceinline__ SpecMap(float md, const SpecParams &p) : max_dist(md), P(p) {}\n";
+    if (noinline) {  // scalar arguments and a by-value result: nothing of the call goes through memory
+        s += "    struct Out { float v[R]; };\n";
+        s += "    __device__ __noinline__ Out eval(";
+        for (int r = 0; r < R; ++r) s += std::string(r ? ", " : "") + "float x" + std::to_string(r) + ", float y" + std::to_string(r) + ", float z" + std::to_string(r);
+        s += ") const {\n        float px[R], py[R], pz[R], out[R];\n";
+        for (int r = 0; r < R; ++r) s += "        px[" + std::to_string(r) + "] = x" + std::to_string(r) + "; py[" + std::to_string(r) + "] = y" + std::to_string(r) + "; pz[" + std::to_string(r) + "] = z" + std::to_string(r) + ";\n";
+        if (cmd_count == 0) s += "        RM_FOR_R out[r] = max_dist;\n";
+        else s += body + "        RM_FOR_R out[r] = " + var(stack.back()) + "[r];\n";
+        s += "        Out o;\n        RM_FOR_R o.v[r] = out[r];\n        return o;\n    }\n";
+        s += "    __device__ __forceinline__ void operator()(const float (&px)[R], const float (&py)[R], const float (&pz)[R], float (&out)[R]) {\n        const Out o = eval(";
+        for (int r = 0; r < R; ++r) s += std::string(r ? ", " : "") + "px[" + std::to_string(r) + "], py[" + std::to_string(r) + "], pz[" + std::to_string(r) + "]";
+        s += ");\n        RM_FOR_R out[r] = o.v[r];\n";
+    } else {
     s += "    __device__ __forceinline__ void operator()(const float (&px)[R], const float (&py)[R], const float (&pz)[R], float (&out)[R]) {\n";
     if (cmd_count == 0) s += "        RM_FOR_R out[r] = max_dist;  // wgsl:189-191\n";
     else s += body + "        RM_FOR_R out[r] = " + var(stack.back()) + "[r];\n";
+    }
     s += "    }\n};\n}  // namespace rm\n";
     s += "extern \"C\" __global__ void __launch_bounds__(RM_DIRECT_THREADS, " + std::to_string(minb) + ")\n";
     s += "rm_spec(const __grid_constant__ rm::FrameParams fp, const __grid_constant__ rm::SpecParams P, uint8_t *__restrict__ dst, size_t pitch,\n        unsigned long long *__restrict__ counters, uint8_t *__restrict__ aov_cls, float *__restrict__ aov_t) {\n";

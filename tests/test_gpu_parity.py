@@ -89,14 +89,16 @@ def test_fast_mode_meets_north_star_gates(rm, ctx, name, W, H, yaw, pitch):
     u = h.orbit_uniforms(W, H, yaw=yaw, pitch=pitch)
     ref = h.oracle_render(u, cmd, words, W, H, aov=True)
     ctx.set_mode(rm.MODE_FAST)
-    img = ctx.render(u, cmd, words, W, H)
-    dbg = ctx.paint_debug(W, H)
-    assert np.array_equal(dbg["rgba"], img)  # wavefront and simple kernels agree bit for bit
-    g = gates(img, ref["rgba"], dbg["cls"], ref["cls"], dbg["t"], ref["t"])
-    print(name, g)
-    assert g["hitmask_pix"] <= GATE_HITMASK, g
-    assert g["rgba_frac"] <= GATE_RGBA_FRAC, g
-    assert g["t_frac"] <= GATE_T_FRAC, g
+    # the production kernel (default) from its own AOVs, and the one-thread-per-sample verification kernel from its own
+    # (since round 2 the two generate their fast-mode rays differently: DESIGN.md §4)
+    ctx.prepare(u, cmd, words)
+    for what, out in (("production", ctx.paint_aov(W, H)), ("verification", ctx.paint_debug(W, H))):
+        g = gates(out["rgba"], ref["rgba"], out["cls"], ref["cls"], out["t"], ref["t"])
+        print(name, what, g)
+        assert g["hitmask_pix"] <= GATE_HITMASK, (what, g)
+        assert g["rgba_frac"] <= GATE_RGBA_FRAC, (what, g)
+        assert g["t_frac"] <= GATE_T_FRAC, (what, g)
+    assert np.array_equal(ctx.render(u, cmd, words, W, H), ctx.paint_aov(W, H)["rgba"])  # the plain build paints the same bytes
 
 
 def random_program(rng, n_leaves, right_bias=0.3):

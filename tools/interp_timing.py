@@ -62,7 +62,7 @@ def main():
         flops = bench.frame_flops(cnt, fmap, W * H)
         m = float(np.mean(ms))
         out = {"workload": a.workload, "tier": a.tier, "spec_tier": ctx.spec_tier, "fused": os.environ.get("RM_SPEC_FUSED", ""),
-               "minb": os.environ.get("RM_SPEC_MINB", ""), "variant": os.environ.get("RM_INTERP_VARIANT", ""), "direct_r": os.environ.get("RM_DIRECT_R", ""),
+               "minb": os.environ.get("RM_SPEC_MINB", ""), "noinline": os.environ.get("RM_SPEC_NOINLINE", ""), "spec_r": os.environ.get("RM_SPEC_R", ""), "variant": os.environ.get("RM_INTERP_VARIANT", ""), "direct_r": os.environ.get("RM_DIRECT_R", ""),
                "lib": str(rm.LIB_PATH.name), "ms": m, "ms_min": float(np.min(ms)), "frac": flops / (m * 1e-3) / 1e12 / peak["tflops"],
                "sum": int(img.astype(np.uint64).sum())}
         print(json.dumps(out))
