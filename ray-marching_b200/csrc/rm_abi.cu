@@ -65,7 +65,8 @@ struct rm_ctx {
     uint64_t paints_same_words = 0;      // plain paints since the words last changed
     std::vector<uint32_t> spec_sig[2];   // structure signature the explicit request (rm_specialize) was made for, per mode
     std::string spec_status;      // why the last specialisation failed
-    uint64_t spec_compiles = 0, spec_launches = 0;
+    std::atomic<uint64_t> spec_compiles{0};  // also counted by the background worker, when its compile finishes
+    uint64_t spec_launches = 0;
     float limits_f[2] = {0.01f, 100.0f};  // renderer.rs:133-137
     uint32_t max_iter = 100;
     float uniforms[36] = {};

@@ -7,6 +7,7 @@
 #include <dlfcn.h>
 
 #include <chrono>
+#include <condition_variable>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -176,16 +177,19 @@ struct Entry {
     std::string err;
     std::shared_ptr<SpecKernel> k;
     uint64_t last_use = 0;
+    bool ready = false;  // false while its compile is in flight (the mutex is not held meanwhile)
 };
 size_t g_cache_cap = 512;
 uint64_t g_tick = 0, g_evictions = 0;
 std::mutex g_mu;
+std::condition_variable g_cv;
 std::map<Key, Entry> g_cache;
 
 // with g_mu held: make room for one more entry by dropping the least recently used one nobody else holds
 bool evict_one() {
     auto victim = g_cache.end();
     for (auto it = g_cache.begin(); it != g_cache.end(); ++it) {
+        if (!it->second.ready) continue;                               // being compiled
         if (it->second.k && it->second.k.use_count() > 1) continue;  // painted by some context right now
         if (victim == g_cache.end() || it->second.last_use < victim->second.last_use) victim = it;
     }
@@ -359,10 +363,6 @@ int spec_generate_source(uint32_t cmd_count, const uint32_t *words, uint32_t n_w
     }
     // same acceptance as decode_program: at least one value left (the shader's final pop_value takes the top), all groups closed
     if (cmd_count != 0 && (stack.empty() || pos.size() != 1)) { if (err) *err = "value stack ends empty or a transform group is open"; return RM_E_STACK_UNBALANCED; }
-    if ((size_t)par.n * sizeof(float) > kMaxParamBytes) {
-        if (err) *err = "too many parameters for the kernel-argument block (" + std::to_string(par.n) + "): the interpreter is used";
-        return RM_E_JIT;
-    }
 
     // rays per thread from the code-size estimate: the march loop's copy of map_scene has to stay in the instruction cache
     if (R == 0) R = env_int("RM_SPEC_R");
@@ -374,12 +374,18 @@ int spec_generate_source(uint32_t cmd_count, const uint32_t *words, uint32_t n_w
             return RM_E_JIT;
         }
     }
+    if ((size_t)par.n * sizeof(float) > kMaxParamBytes) {
+        if (err) *err = "too many parameters for the kernel-argument block (" + std::to_string(par.n) + "): the interpreter is used";
+        return RM_E_JIT;
+    }
     // Deep programs (2 rays per thread) get ONE out-of-line copy of the scene code, called by the march loop and by the
     // tap loop, instead of an inlined copy in each: half the code (the instruction cache holds it with room to spare), no
     // spill at all, half the compile time, and specialisation keeps paying up to 64 leaves instead of 48 (measured on B200,
     // profiles/r2_s9_crossover.txt: 32 / 48 / 64 leaves x1.26 / 1.21 / 1.18 over the interpreter against x1.25 / 1.13 / 1.03
-    // inlined).  Shallow programs (4 rays) stay inlined: the call costs more than it saves there (cfg2 0.708 vs 0.680 ms).
-    bool noinline = R == 2;
+    // inlined).  Shallow programs (4 rays) stay inlined: the call costs more than it saves there (cfg2 0.708 vs 0.680 ms),
+    // and so does the structure tier: inlined, ptxas hoists part of the argument loads out of the march loop, out of line
+    // every LDCU is paid per evaluation (cfg3 structure tier 38.9 ms out of line, 37.4 inlined).
+    bool noinline = R == 2 && literals;
     if (const char *ns = std::getenv("RM_SPEC_NOINLINE")) noinline = ns[0] == '1';
     int minb = env_int("RM_SPEC_MINB");
     if (minb <= 0) minb = R == 2 ? (noinline ? 10 : 12) : (R == 4 ? 10 : 7);  // measured on B200: profiles/r1_s14_NOTES.md, r2_s8_noinline_sweep.jsonl
@@ -468,8 +474,16 @@ int spec_get(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, bool e
         if (err) *err = gen_err;
         return rc;
     }
-    std::lock_guard<std::mutex> lock(g_mu);  // one compile at a time; the other members of a group then hit the cache
+    // The cache mutex is NOT held while compiling (a paint that only looks a kernel up must never wait for somebody else's
+    // compile): a miss inserts a placeholder, compiles outside the lock and fills it in; requests for the same key wait
+    // for it (blocking callers) or report a miss (lookup_only).
+    std::unique_lock<std::mutex> lock(g_mu);
     auto it = g_cache.find(key);
+    if (it != g_cache.end() && !it->second.ready) {
+        if (lookup_only) return RM_E_JIT;
+        g_cv.wait(lock, [&] { auto i2 = g_cache.find(key); return i2 == g_cache.end() || i2->second.ready; });
+        it = g_cache.find(key);
+    }
     if (it == g_cache.end()) {
         if (lookup_only) return RM_E_JIT;
         while (g_cache.size() >= g_cache_cap) {
@@ -479,6 +493,8 @@ int spec_get(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, bool e
             }
         }
         if (compiled_now) *compiled_now = true;
+        g_cache.emplace(key, Entry{});  // placeholder: ready = false
+        lock.unlock();
         Entry e;
         const auto t0 = std::chrono::steady_clock::now();
         std::string cubin;
@@ -499,7 +515,12 @@ int spec_get(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, bool e
         }
         k->compile_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
         if (e.rc == RM_OK) e.k = std::move(k);
-        it = g_cache.emplace(std::move(key), std::move(e)).first;  // failures are cached too: no retry storm per frame
+        e.ready = true;
+        lock.lock();
+        it = g_cache.find(key);
+        if (it == g_cache.end()) it = g_cache.emplace(key, Entry{}).first;  // (evicted meanwhile: cannot happen to a placeholder, kept for safety)
+        it->second = std::move(e);  // failures are cached too: no retry storm per frame
+        g_cv.notify_all();
     }
     Entry &e = it->second;
     e.last_use = ++g_tick;

@@ -87,8 +87,10 @@ def test_rays_per_thread_follow_the_code_size(rm):
     assert "direct_body<false, 4," in rm.spec_source(cmd, words)
     cmd, words = h.scene_s2()  # 63 commands: ~9 KB of code per ray -> 2 rays keep the march loop in the instruction cache
     src = rm.spec_source(cmd, words)
-    assert "direct_body<false, 2," in src and "__launch_bounds__(RM_DIRECT_THREADS, 10)" in src
-    assert "__noinline__ Out eval(float x0, float y0, float z0, float x1, float y1, float z1)" in src   # ONE out-of-line copy of the scene code
+    assert "direct_body<false, 2," in src and "__launch_bounds__(RM_DIRECT_THREADS, 12)" in src and "__noinline__" not in src
+    lit = rm.spec_source(cmd, words, rm.MODE_FAST | rm.SPEC_LITERAL_TIER)   # the literal tier of a deep program: ONE out-of-line copy of the scene code
+    assert "direct_body<false, 2," in lit and "__launch_bounds__(RM_DIRECT_THREADS, 10)" in lit
+    assert "__noinline__ Out eval(float x0, float y0, float z0, float x1, float y1, float z1)" in lit
     assert "direct_body<false, 8," in rm.spec_source(cmd, words, rm.MODE_FAST, 8)  # explicit request is honoured
     # a chain far beyond the instruction-cache budget is refused (the interpreter is the better kernel there)
     n = 120
