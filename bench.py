@@ -269,6 +269,8 @@ class Rig:
                              "direct": rm.KERNEL_DIRECT}[args.kernel])
         if args.early_out:
             self.ctx.set_early_out(True)
+        if args.cull == "on":
+            self.ctx.set_cull(True)
         self.stream = torch.cuda.Stream(self.dev)
         torch.cuda.set_stream(self.stream)
         self.sp = self.stream.cuda_stream
@@ -320,7 +322,7 @@ class Rig:
     def specialise(self, args) -> dict:
         """Program specialisation of the prepared command stream (once, untimed; cached process-wide)."""
         rm, ctx = self.rm, self.ctx
-        spec = {"requested": args.specialize == "on" and args.kernel == "direct" and not args.early_out, "active": False}
+        spec = {"requested": args.specialize == "on" and args.kernel == "direct" and not args.early_out and args.cull != "on", "active": False}
         if spec["requested"]:
             try:
                 ctx.specialize()
@@ -331,10 +333,12 @@ class Rig:
         return spec
 
     def counters_of(self, count_step):
+        self.ctx.cull_stats()
         self.ctx.set_counters(True)
         count_step()
         c = self.ctx.get_counters()
         self.ctx.set_counters(False)
+        self.cull_stats = self.ctx.cull_stats()   # executed map_scene flops of that step when culling is on
         return c
 
 
@@ -727,6 +731,11 @@ def b200_arm(args) -> int:
               "l2": "flushed between timed steps (256 MiB memset, untimed)"}
     if args.early_out:
         config["early_out"] = "ON: executed work per map_scene evaluation is less than the algorithmic FLOPs the roofline fraction counts"
+    if args.cull == "on":
+        config["cull"] = ("ON (opt-in, never the headline): every block interprets only the instructions its tile's cone can be changed by "
+                          "(csrc/rm_cull.cu); frames and work counters are identical to the unculled paint, the work per evaluation is not "
+                          "the shader's literal arithmetic: roofline.frac counts ALGORITHMIC flops and overstates, frac_executed counts the "
+                          "flops of the instructions actually run")
     peaks = measured_peaks()
     hbm_gbs = float(peaks.get("hbm_gbs", 0.0)) or None
     extra = {}
@@ -812,7 +821,7 @@ def b200_arm(args) -> int:
                 (st_ms,) = rig.max_over_ranks(st_ms_local)
                 extra["_structure"] = {"ms": st_ms, "ms_local": st_ms_local}
             ctx.set_spec_literal_after(8)
-        elif args.kernel == "direct" and not args.early_out:
+        elif args.kernel == "direct" and not args.early_out and args.cull != "on":
             interp = {"ms": None, "ms_local": ms_local, "steps": args.steps}
 
         # ---- e2e: host buffers in, host result out, through the public C-ABI calls (prepare + paint + download)
@@ -883,6 +892,13 @@ def b200_arm(args) -> int:
                 "framebuffer_gbs": fb_bytes / (ms_local * 1e-3) / 1e9,
                 "hbm_peak_gbs": hbm_gbs, "hbm_peak_source": "MEASURED_PEAKS.json hbm_gbs" if hbm_gbs else "MEASURED_PEAKS.json absent",
                 "framebuffer_frac_of_hbm_peak": (fb_bytes / (ms_local * 1e-3) / 1e9 / hbm_gbs) if hbm_gbs else None}
+        if args.cull == "on" and getattr(rig, "cull_stats", {}).get("culled_paints"):
+            n_eval = float(counters[0]) + 4.0 * float(counters[1])
+            executed = flops - n_eval * fmap + float(rig.cull_stats["executed_map_flops"])
+            roof.update(executed_flops_per_step=executed, frac_executed=executed / (ms_local * 1e-3) / 1e12 / peak["tflops"],
+                        executed_map_flops_per_eval=float(rig.cull_stats["executed_map_flops"]) / max(n_eval, 1.0),
+                        cull_note="frac counts the algorithmic flops of the FULL program per evaluation (overstates); frac_executed counts "
+                                  "the instructions the tiles kept; the culling pre-pass (one thread per tile) is inside the timed step")
         if interp:
             roof["achieved_interpreter"] = flops / (interp["ms_local"] * 1e-3) / 1e12
             roof["frac_interpreter"] = roof["achieved_interpreter"] / peak["tflops"]
@@ -932,6 +948,9 @@ def main():
     ap.add_argument("--early-out", action="store_true",
                     help="opt-in exact early-out of the interpreter (bit-identical output, but NOT the shader's literal arithmetic "
                          "per evaluation: reported separately, never the headline)")
+    ap.add_argument("--cull", default="off", choices=["on", "off"],
+                    help="opt-in per-tile culling of the program (exact: identical frames and counters; reported with executed flops, "
+                         "never the headline); paints through the interpreter")
     ap.add_argument("--e2e", default="serial", choices=["serial", "pipelined"],
                     help="end-to-end leg of the single-frame workloads.  serial (default): rm_prepare + rm_paint + rm_download per step, "
                          "each step waits for its frame.  pipelined: the steps go through rm_paint_poses_host, which copies frame k to "

@@ -66,6 +66,8 @@ extern "C" {
                                  cubin_bytes: *mut u64, compile_ms: *mut f64, log: *mut c_char, log_cap: usize) -> i32;
     pub fn rm_spec_params(cmd_count: u32, words: *const u32, n_words: u32, mode: i32, buf: *mut f32, cap_floats: usize,
                           needed: *mut usize) -> i32;
+    pub fn rm_set_cull(ctx: *mut RmCtx, on: i32) -> i32;
+    pub fn rm_get_cull_stats(ctx: *mut RmCtx, executed_map_flops: *mut u64, culled_paints: *mut u64, reset: i32) -> i32;
     pub fn rm_set_spec_literal_after(ctx: *mut RmCtx, n_paints: u32) -> i32;
     pub fn rm_spec_tier(ctx: *mut RmCtx) -> i32;
     pub fn rm_spec_cache(new_capacity: u64, entries: *mut u64, capacity: *mut u64, evictions: *mut u64) -> i32;

@@ -137,6 +137,20 @@ RM_API uint64_t rm_program_uploads(rm_ctx *ctx);
 RM_API int rm_validate_program(uint32_t cmd_count, const uint32_t *words, uint32_t n_words,
                                uint32_t max_words);
 
+/* Opt-in, never the headline: per-tile conservative culling of the program (csrc/rm_cull.cu).  Before the paint, one
+ * thread per 8-wide block tile walks the tile's centre ray over every ray parameter a ray of the frame can reach and
+ * keeps a leaf instruction `acc = op(acc, prim(p))` only if, somewhere in the tile's cone, it could change the
+ * accumulator (1-Lipschitz bounds on the margins prim - acc - k, prim + acc, acc - prim); each block then interprets
+ * only its tile's instructions.  A dropped instruction is a no-op bit for bit at every point the tile's rays visit, so
+ * image, AOVs and work counters are IDENTICAL to the unculled paint in both arithmetic modes — only the work per
+ * evaluation is no longer the shader's literal arithmetic, which is why this is reported separately.  Applies to
+ * RM_KERNEL_DIRECT paints of reference-set programs of at most 64 decoded instructions (others paint as usual); paints
+ * through the interpreter (specialised kernels are not used while it is on).
+ * rm_get_cull_stats: algorithmic flops of the map_scene evaluations as EXECUTED (sum over evaluations of the flops of
+ * the instructions the tile kept) by the culled paints made with rm_set_counters on, and the number of culled paints. */
+RM_API int rm_set_cull(rm_ctx *ctx, int on);
+RM_API int rm_get_cull_stats(rm_ctx *ctx, uint64_t *executed_map_flops, uint64_t *culled_paints, int reset);
+
 /* ---- program specialisation (optional; the reference compiles its shader once, RayMarchingResources::new
  *      renderer.rs:55-62 — here the SCENE can be compiled too) --------------------------------------------------- */
 /* By default the kernels interpret the decoded command stream: any program, no set-up cost.  A program can instead be

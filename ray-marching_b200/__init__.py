@@ -38,7 +38,7 @@ ABI_SYMBOLS = [
     "rm_flush_l2", "rm_fp32_peak", "rm_launch_count", "rm_host_alloc", "rm_host_free", "rm_last_error",
     "rm_strerror", "rm_version",
     "rm_group_create", "rm_group_destroy", "rm_group_size", "rm_group_ctx", "rm_group_set_mode", "rm_group_set_limits",
-    "rm_specialize", "rm_set_specialize", "rm_spec_info", "rm_spec_status", "rm_spec_source", "rm_spec_compile_check", "rm_spec_params", "rm_spec_cache", "rm_set_spec_literal_after", "rm_spec_tier",
+    "rm_specialize", "rm_set_specialize", "rm_spec_info", "rm_spec_status", "rm_spec_source", "rm_spec_compile_check", "rm_spec_params", "rm_spec_cache", "rm_set_spec_literal_after", "rm_spec_tier", "rm_set_cull", "rm_get_cull_stats",
     "rm_group_specialize", "rm_group_prepare", "rm_group_paint_bands", "rm_group_frame", "rm_group_paint_poses", "rm_group_last_error",
 ]
 
@@ -122,6 +122,8 @@ def lib() -> C.CDLL:
             "rm_spec_source": (i, [u32, vp, u32, i, i, C.c_char_p, sz, C.POINTER(sz)]),
             "rm_spec_compile_check": (i, [u32, vp, u32, i, i, C.POINTER(u64), C.POINTER(C.c_double), C.c_char_p, sz]),
             "rm_spec_params": (i, [u32, vp, u32, i, vp, sz, C.POINTER(sz)]),
+            "rm_set_cull": (i, [vp, i]),
+            "rm_get_cull_stats": (i, [vp, C.POINTER(u64), C.POINTER(u64), i]),
             "rm_set_spec_literal_after": (i, [vp, u32]),
             "rm_spec_tier": (i, [vp]),
             "rm_spec_cache": (i, [u64, C.POINTER(u64), C.POINTER(u64), C.POINTER(u64)]),
@@ -272,6 +274,15 @@ class Context:
     # ---- prepare (renderer.rs:196-242)
     def set_early_out(self, on: bool):
         self._chk(self._L.rm_set_early_out(self._h, int(bool(on))))
+
+    def set_cull(self, on: bool):
+        """Opt-in per-tile culling of the program (exact: identical frames; reported separately, never the headline)."""
+        self._chk(self._L.rm_set_cull(self._h, int(bool(on))))
+
+    def cull_stats(self, reset: bool = True) -> dict:
+        f, n = C.c_uint64(), C.c_uint64()
+        self._chk(self._L.rm_get_cull_stats(self._h, C.byref(f), C.byref(n), int(reset)))
+        return {"executed_map_flops": int(f.value), "culled_paints": int(n.value)}
 
     # ---- program specialisation (run-time compiled straight-line map_scene)
     def specialize(self):

@@ -3,7 +3,9 @@
 // all wgpu plumbing — limits, command buffer (decoded), uniforms — plus a framebuffer.
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <atomic>
+#include <cmath>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -13,6 +15,8 @@
 #include <thread>
 
 #include "../../include/rm_b200.h"
+#include "rm_cull.h"
+#include "rm_direct_body.cuh"
 #include "rm_frame.h"
 #include "rm_jit.h"
 #include "rm_kernels.h"
@@ -43,6 +47,12 @@ struct rm_ctx {
     bool prepared = false;
     bool counters_on = false;
     bool early_out = false;  // rm_set_early_out: opt-in, never on by default
+    // rm_set_cull: opt-in per-tile culling of the program (rm_cull.cu); like the early-out it paints through the interpreter
+    bool cull = false;
+    unsigned long long *d_masks = nullptr;  // one per block tile of the band being painted (ctx-wide scratch)
+    size_t masks_cap = 0;
+    float cull_t_end = 0.0f;                // per program + uniforms: beyond this ray parameter no ray of the frame is marching
+    uint64_t cull_paints = 0;
     // program specialisation (rm_jit.cu): paint the DIRECT kernel through run-time compiled straight-line code
     int spec_policy = 0;          // rm_set_specialize: 1 = every program, compiled at its first paint; 2 = compiled in the background
     // policy 2: one worker thread per context compiles while the interpreter keeps painting
@@ -194,8 +204,8 @@ int rm_create_ex(int cuda_device, uint32_t max_words, rm_ctx **out) {
     c->prog_cap = max_words;
     ok = ok && cudaMalloc(&c->d_prog, 2 * c->prog_cap * sizeof(RmInsn)) == cudaSuccess;
     ok = ok && cudaMallocHost(&c->h_prog, 2 * c->prog_cap * sizeof(RmInsn)) == cudaSuccess;
-    ok = ok && cudaMalloc(&c->d_counters, 4 * sizeof(unsigned long long)) == cudaSuccess;
-    ok = ok && cudaMemset(c->d_counters, 0, 4 * sizeof(unsigned long long)) == cudaSuccess;
+    ok = ok && cudaMalloc(&c->d_counters, 8 * sizeof(unsigned long long)) == cudaSuccess;  // 4 work counters + executed flops (culled paints)
+    ok = ok && cudaMemset(c->d_counters, 0, 8 * sizeof(unsigned long long)) == cudaSuccess;
     ok = ok && wavefront_init(&c->wf, cuda_device) == cudaSuccess;
     if (!ok) {
         rm_destroy(c);
@@ -229,6 +239,7 @@ void rm_destroy(rm_ctx *c) {
     for (auto &e : c->ring_rendered) if (e) cudaEventDestroy(e);
     for (auto &e : c->ring_copied) if (e) cudaEventDestroy(e);
     if (c->d_codes) cudaFree(c->d_codes);
+    if (c->d_masks) cudaFree(c->d_masks);
     if (c->d_flush) cudaFree(c->d_flush);
     if (c->d_counters) cudaFree(c->d_counters);
     if (c->stream) cudaStreamDestroy(c->stream);

@@ -48,17 +48,48 @@ constexpr int direct_min_blocks(int R, bool EXT) {
     return EXT ? (R == 8 ? RM_DIRECT_MINB8_EXT : RM_DIRECT_MINB4_EXT) : (R == 8 ? RM_DIRECT_MINB8 : RM_DIRECT_MINB4);
 }
 
-template <bool EX, int R, bool COUNT, bool EO, bool EXT>
+// algorithmic flops of one decoded instruction, for the executed-flop counter of culled paints
+__device__ __forceinline__ uint32_t insn_flops(uint32_t fl) {
+    uint32_t f = 0;
+    if (!(fl & FLAG_POP)) f += (fl & FLAG_BOX) ? 22u : 10u;
+    if (fl & FLAG_SMOOTH) f += 10u;
+    else if (fl & FLAG_SUB) f += 2u;
+    else if (fl & (FLAG_UNION | FLAG_INTER)) f += 1u;
+    return f;
+}
+
+// CULL (opt-in, rm_cull.cu): the block stages only the instructions its tile's mask keeps — a shorter program, the same bits.
+template <bool EX, int R, bool COUNT, bool EO, bool EXT, bool CULL = false>
 __global__ void __launch_bounds__(DIRECT_THREADS, direct_min_blocks(R, EXT))
 k_direct(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ prog_g, uint8_t *__restrict__ dst, size_t pitch,
-         unsigned long long *__restrict__ counters) {
+         unsigned long long *__restrict__ counters, const unsigned long long *__restrict__ masks) {
     extern __shared__ float4 s_prog[];
-    const uint32_t nq = fp.n_insn * 3;
-    for (uint32_t i = threadIdx.x; i < nq; i += blockDim.x) s_prog[i] = reinterpret_cast<const float4 *>(prog_g)[i];
-    __syncthreads();
     InterpMap<EX, R, EO, EXT> map;
-    map.prog = s_prog; map.n_insn = fp.n_insn; map.max_dist = fp.max_dist;
-    direct_body<EX, R, COUNT, false>(fp, dst, pitch, counters, nullptr, nullptr, map);
+    uint32_t eval_flops = 0;
+    if constexpr (CULL) {
+        __shared__ uint32_t s_flops;
+        const unsigned long long mask = masks[blockIdx.x];
+        if (threadIdx.x == 0) s_flops = 0;
+        __syncthreads();
+        for (uint32_t i = threadIdx.x; i < fp.n_insn; i += blockDim.x) {
+            if ((mask >> i) & 1ull) {
+                const uint32_t pos = (uint32_t)__popcll(mask & ((1ull << i) - 1ull));
+                const float4 *src = reinterpret_cast<const float4 *>(prog_g) + 3 * i;
+                s_prog[3 * pos] = src[0]; s_prog[3 * pos + 1] = src[1]; s_prog[3 * pos + 2] = src[2];
+                if (COUNT) atomicAdd(&s_flops, insn_flops(__float_as_uint(src[2].w)));
+            }
+        }
+        __syncthreads();
+        map.n_insn = (uint32_t)__popcll(mask);
+        if (COUNT) eval_flops = s_flops;
+    } else {
+        const uint32_t nq = fp.n_insn * 3;
+        for (uint32_t i = threadIdx.x; i < nq; i += blockDim.x) s_prog[i] = reinterpret_cast<const float4 *>(prog_g)[i];
+        __syncthreads();
+        map.n_insn = fp.n_insn;
+    }
+    map.prog = s_prog; map.max_dist = fp.max_dist;
+    direct_body<EX, R, COUNT, false>(fp, dst, pitch, counters, nullptr, nullptr, map, eval_flops);
 }
 
 // the same kernel with the per-sample AOVs written out (verification: rm_paint_aov)
@@ -88,16 +119,16 @@ cudaError_t launch_direct_aov_t(const FrameParams &fp, const RmInsn *prog, uint8
     return cudaGetLastError();
 }
 
-template <bool EX, int R, bool COUNT, bool EO, bool EXT>
+template <bool EX, int R, bool COUNT, bool EO, bool EXT, bool CULL = false>
 cudaError_t launch_direct_t(const FrameParams &fp, const RmInsn *prog, uint8_t *dst, size_t pitch,
-                            unsigned long long *counters, cudaStream_t st) {
-    auto kern = k_direct<EX, R, COUNT, EO, EXT>;
+                            unsigned long long *counters, cudaStream_t st, const unsigned long long *masks = nullptr) {
+    auto kern = k_direct<EX, R, COUNT, EO, EXT, CULL>;
     constexpr uint32_t tile_h = direct_tile_rows(R);
     const size_t smem = (size_t)fp.n_insn * sizeof(RmInsn);
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     const unsigned grid = ((fp.W + TILE_W_D - 1) / TILE_W_D) * ((fp.nrows + tile_h - 1) / tile_h);
-    kern<<<grid, DIRECT_THREADS, smem, st>>>(fp, prog, dst, pitch, counters);
+    kern<<<grid, DIRECT_THREADS, smem, st>>>(fp, prog, dst, pitch, counters, masks);
     return cudaGetLastError();
 }
 
@@ -130,6 +161,21 @@ cudaError_t launch_direct(bool exact, bool early_out, bool extended, const Frame
     return kR == 8 ? RM_DIRECT_DISPATCH(false, 8) : RM_DIRECT_DISPATCH(false, 4);
 #undef RM_DIRECT_DISPATCH2
 #undef RM_DIRECT_DISPATCH
+}
+
+int direct_rays_for(const FrameParams &fp) { return direct_rays_per_thread(fp); }
+
+// The culled paint (rm_cull.cu): reference-set programs of at most 64 instructions, no early-out.  masks: one per block tile.
+cudaError_t launch_direct_culled(bool exact, const FrameParams &fp, const RmInsn *prog_dev, uint8_t *dst, size_t pitch,
+                                 unsigned long long *counters, const unsigned long long *masks, cudaStream_t st) {
+    if (fp.nrows == 0 || fp.W == 0) return cudaSuccess;
+    const int kR = direct_rays_per_thread(fp);
+#define RM_CULL_DISPATCH(EXV, RV)                                                                                 \
+    (counters ? launch_direct_t<EXV, RV, true, false, false, true>(fp, prog_dev, dst, pitch, counters, st, masks)  \
+              : launch_direct_t<EXV, RV, false, false, false, true>(fp, prog_dev, dst, pitch, counters, st, masks))
+    if (exact) return kR == 8 ? RM_CULL_DISPATCH(true, 8) : RM_CULL_DISPATCH(true, 4);
+    return kR == 8 ? RM_CULL_DISPATCH(false, 8) : RM_CULL_DISPATCH(false, 4);
+#undef RM_CULL_DISPATCH
 }
 
 // Rays per thread: 4 for shallow programs (more threads, less lock-step waste), 8 for deep ones (fetch/dispatch

@@ -28,7 +28,7 @@ __host__ __device__ constexpr uint32_t direct_tile_rows(int R) { return 4u * (32
 template <bool EX, int R, bool COUNT, bool AOV, class MAP>
 __device__ __forceinline__ void direct_body(const FrameParams &fp, uint8_t *__restrict__ dst, size_t pitch,
                                             unsigned long long *__restrict__ counters, uint8_t *__restrict__ aov_cls,
-                                            float *__restrict__ aov_t, MAP &map) {
+                                            float *__restrict__ aov_t, MAP &map, uint32_t eval_flops = 0) {
     static_assert(R == 2 || R == 4 || R == 8, "2, 4 or 8 rays per thread");
     constexpr int TPP = 16 / R;           // threads per pixel
     constexpr int PPW = 32 / TPP;         // pixels per warp: 4, 8 or 16 consecutive pixels of the block's 8-wide tile
@@ -224,6 +224,8 @@ __device__ __forceinline__ void direct_body(const FrameParams &fp, uint8_t *__re
             atomicAdd(&counters[1], (unsigned long long)b);
             atomicAdd(&counters[2], (unsigned long long)c);
             atomicAdd(&counters[3], (unsigned long long)d);
+            // culled paints (rm_cull.cu): algorithmic flops of the map_scene evaluations as EXECUTED with this block's program
+            if (eval_flops) atomicAdd(&counters[4], ((unsigned long long)a + 4ull * b) * eval_flops);
         }
     }
 }

@@ -32,6 +32,12 @@ cudaError_t launch_wavefront2(WavefrontState *ws, bool exact, const FrameParams 
 cudaError_t launch_direct(bool exact, bool early_out, bool extended, const FrameParams &fp, const RmInsn *prog_dev, uint8_t *dst,
                           size_t pitch, unsigned long long *counters, cudaStream_t st);
 
+// Culled paint (rm_cull.cu, opt-in): the same kernel, every block running only the instructions its tile's mask keeps.
+// direct_rays_for: the rays per thread launch_direct picks for this program (the mask tiles are 8 x direct_tile_rows(R)).
+int direct_rays_for(const FrameParams &fp);
+cudaError_t launch_direct_culled(bool exact, const FrameParams &fp, const RmInsn *prog_dev, uint8_t *dst, size_t pitch,
+                                 unsigned long long *counters, const unsigned long long *masks, cudaStream_t st);
+
 // The same kernel with the per-sample classes / distances of its own march written out (verification, rm_paint_aov).
 cudaError_t launch_direct_aov(bool exact, bool extended, const FrameParams &fp, const RmInsn *prog_dev, uint8_t *dst, size_t pitch,
                               uint8_t *cls, float *t, cudaStream_t st);

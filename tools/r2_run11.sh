@@ -1,0 +1,6 @@
+set -x
+python -m pytest tests/test_gpu_cull.py tests/test_gpu_spec.py tests/test_gpu_wavefront2.py tests/test_gpu_parity.py -m gpu -q > gpurun_out/r2_s11_pytest.log 2>&1; tail -15 gpurun_out/r2_s11_pytest.log
+python bench.py --cull on --steps 10 --warmup 3 --strong off --parity off > gpurun_out/r2_s11_bench_cfg3_cull.json 2> gpurun_out/r2_s11_bench_cfg3_cull.err; echo rc=$?; tail -3 gpurun_out/r2_s11_bench_cfg3_cull.err
+python bench.py --cull on --workload cfg2 --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/r2_s11_bench_cfg2_cull.json 2>&1
+python bench.py --e2e pipelined --steps 10 --warmup 3 --strong off --parity off --no-cpu-baseline > gpurun_out/r2_s11_bench_cfg3_pipelined.json 2> gpurun_out/r2_s11_pipelined.err; echo rc=$?
+cut -c1-700 gpurun_out/r2_s11_bench_cfg3_cull.json
