@@ -144,7 +144,7 @@ RM_API int rm_validate_program(uint32_t cmd_count, const uint32_t *words, uint32
  * only its tile's instructions.  A dropped instruction is a no-op bit for bit at every point the tile's rays visit, so
  * image, AOVs and work counters are IDENTICAL to the unculled paint in both arithmetic modes — only the work per
  * evaluation is no longer the shader's literal arithmetic, which is why this is reported separately.  Applies to
- * RM_KERNEL_DIRECT paints of reference-set programs of at most 64 decoded instructions (others paint as usual); paints
+ * RM_KERNEL_DIRECT paints of reference-set programs of 8 to 64 decoded instructions (others paint as usual); paints
  * through the interpreter (specialised kernels are not used while it is on).
  * rm_get_cull_stats: algorithmic flops of the map_scene evaluations as EXECUTED (sum over evaluations of the flops of
  * the instructions the tile kept) by the culled paints made with rm_set_counters on, and the number of culled paints. */

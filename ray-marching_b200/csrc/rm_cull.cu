@@ -25,7 +25,8 @@ namespace rm {
 
 namespace {
 
-constexpr int kMaxSamples = 4096;
+constexpr int kMaxSamples = 8192;
+constexpr float kMaxWidth = 0.25f;
 constexpr float kSlack = 1e-3f;  // float evaluation error of the margins (values of a few units: ~1e-6) with a wide berth
 
 __device__ __forceinline__ void affine_dir(const FrameParams &fp, float X, float Y, float d[3]) {
@@ -128,8 +129,10 @@ __global__ void __launch_bounds__(64) k_cull_masks(const __grid_constant__ Frame
                 acc = v;
             }
         }
-        // interval width from the scene distance here: fine near surfaces, geometric far away
-        const float w = fminf(fmaxf(0.5f * fabsf(acc), fmaxf(0.02f, 2.f * t * chi)), 64.f);
+        // interval width: fine near surfaces, a quarter of the scene distance further out, but never wide — a margin has
+        // to clear TWICE the ball radius, and far from the scene the leaves' distances differ by no more than the scene is
+        // deep, so wide intervals there would keep every instruction alive for the (many) far steps of the escaping rays
+        const float w = fminf(fmaxf(0.25f * fabsf(acc), fmaxf(0.02f, t * chi)), kMaxWidth);
         const float bound = 2.f * (w + (t + w) * chi + 2e-4f) + kSlack;
         for (uint32_t i = 0; i < n; ++i)
             if (!(margin[i] >= bound)) active |= 1ull << i;
