@@ -61,7 +61,7 @@ int hc_paint(int exact, int rays_per_thread, uint32_t cmd_count, const uint32_t 
              const void *limits12, uint32_t W, uint32_t H, uint32_t row0, uint32_t nrows, uint32_t strip_rows, uint32_t strip_pitch,
              int dst_frame_rows, uint8_t *dst, size_t pitch, uint64_t *counters4, uint8_t *aov_cls, float *aov_t) {
     Program p;
-    // exact < 0: fast mode with the experimental collapsed lowering of extended programs (RM_N4_COLLAPSE)
+    // exact < 0: fast mode with the collapsed lowering of extended programs (the fast form rm_prepare decodes)
     const int rc = decode_program(cmd_count, words, n_words, 3072, &p, /*fast_form=*/exact <= 0, /*collapse_chains=*/exact < 0);
     if (exact < 0) exact = 0;
     if (rc != RM_OK) return rc;

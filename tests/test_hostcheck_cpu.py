@@ -188,7 +188,7 @@ def test_instruction_stream_can_outgrow_the_word_stream(hc):
     assert same_bits(hc_map(hc, cmd, words, pts, True, 8), h.oracle_map(cmd, words, pts))
 
 
-# ---- experimental fast-mode lowering (RM_N4_COLLAPSE=1): one similarity per primitive ------------------------------
+# ---- fast-form lowering of extended programs (what RM_MODE_FAST paints): one similarity per primitive ------------------------------
 @pytest.mark.parametrize("seed", range(8))
 def test_collapsed_chains_agree_with_the_oracle_within_fast_mode_tolerance(hc, seed):
     rng = np.random.default_rng(1300 + seed)

@@ -174,7 +174,7 @@ def test_fast_mode_on_the_host_is_inside_the_gates(hc):
 
 
 def test_collapsed_lowering_through_the_whole_kernel_body_is_inside_the_gates(hc):
-    # RM_N4_COLLAPSE experiment (rm_program.h): one similarity per primitive, fast mode only
+    # the fast form of extended programs (rm_program.h collapse_chains): one similarity per primitive
     cmd, words = h.scene_s3()
     W, H = 48, 27
     u = h.orbit_uniforms(W, H, yaw=0.6, pitch=0.4)

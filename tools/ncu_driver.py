@@ -21,6 +21,7 @@ def main():
     ap.add_argument("--tier", default="literal", choices=["literal", "structure", "interp"])
     ap.add_argument("--frames", type=int, default=4)
     ap.add_argument("--mode", default="fast")
+    ap.add_argument("--cull", action="store_true", help="opt-in per-tile culling (interpreter tier)")
     a = ap.parse_args()
     rm = rm_import.load()
     scenes = importlib.import_module("ray_marching_b200.scenes")
@@ -31,6 +32,8 @@ def main():
     with rm.Context(0) as ctx:
         ctx.set_mode(rm.MODE_FAST if a.mode == "fast" else rm.MODE_EXACT)
         ctx.prepare(u, cmd, words)
+        if a.cull:
+            ctx.set_cull(True)
         if a.tier != "interp":
             ctx.set_spec_literal_after(8 if a.tier == "literal" else 0)
             ctx.specialize()
