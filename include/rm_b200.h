@@ -118,7 +118,10 @@ RM_API int rm_set_kernel(rm_ctx *ctx, int kernel);
 /* Opt-in (default 0), RM_KERNEL_DIRECT only: skip the rest of a primitive+operator instruction when a cheap lower bound of
  * the primitive proves the accumulator unchanged.  Output is bit-identical; the work done per map_scene evaluation is not
  * the shader's literal arithmetic any more, so numbers measured with it are reported separately.
- * Ignored for programs that use the N4 commands (the bounds are written for the reference instruction set). */
+ * Ignored for programs that use the N4 commands (the bounds are written for the reference instruction set).
+ * Precondition of the bit-identity: the bounds carry a fixed slack of 1e-4 for the few roundings between bound and value,
+ * which covers evaluation points and primitive parameters up to a few hundred in magnitude (the reference's max_dist is
+ * 100); with coordinates of 1e4 and more a float32 rounding can exceed it — leave the option off for such scenes. */
 RM_API int rm_set_early_out(rm_ctx *ctx, int on);
 
 /* ---- per frame: replaces RayMarchingCallback::prepare, renderer.rs:196-242 ------------------ */
@@ -157,8 +160,8 @@ RM_API int rm_get_cull_stats(rm_ctx *ctx, uint64_t *executed_map_flops, uint64_t
  * compiled: map_scene is emitted as straight-line CUDA — no fetch, no dispatch — and built at run time (NVRTC, sm_100a)
  * around the same kernel body.  The generated code depends on the program's STRUCTURE only: the opcode sequence, which
  * parameters are exactly zero (those stay literals so that `p - 0` folds) and, in exact mode, which smooth-union k are
- * powers of two.  Every other centre, radius, k, offset or matrix entry travels as a kernel argument (constant bank: an
- * operand of the arithmetic instruction itself, no load, no register).  So the reference's per-frame re-flatten and
+ * powers of two.  Every other centre, radius, k, offset or matrix entry travels as a kernel argument (constant bank,
+ * read through uniform registers).  So the reference's per-frame re-flatten and
  * re-upload (renderer.rs:224-239) and an editor dragging a value keep their compiled kernel: rm_prepare with new values
  * of the same structure costs no compile.  Arithmetic per ray is operation for operation the interpreter's: exact mode
  * stays bit-identical, fast mode may round differently where the compiler contracts multiply-adds (within the parity
