@@ -68,6 +68,8 @@ extern "C" {
                           needed: *mut usize) -> i32;
     pub fn rm_set_cull(ctx: *mut RmCtx, on: i32) -> i32;
     pub fn rm_get_cull_stats(ctx: *mut RmCtx, executed_map_flops: *mut u64, culled_paints: *mut u64, reset: i32) -> i32;
+    pub fn rm_paint_culled_static(ctx: *mut RmCtx, w: u32, h: u32, row0: u32, nrows: u32, dst_rgba8_dev: *mut c_void,
+                                  pitch_bytes: usize, cuda_stream: *mut c_void) -> i32;
     pub fn rm_set_spec_literal_after(ctx: *mut RmCtx, n_paints: u32) -> i32;
     pub fn rm_spec_tier(ctx: *mut RmCtx) -> i32;
     pub fn rm_spec_cache(new_capacity: u64, entries: *mut u64, capacity: *mut u64, evictions: *mut u64) -> i32;

@@ -153,6 +153,20 @@ RM_API int rm_validate_program(uint32_t cmd_count, const uint32_t *words, uint32
  * the instructions the tile kept) by the culled paints made with rm_set_counters on, and the number of culled paints. */
 RM_API int rm_set_cull(rm_ctx *ctx, int on);
 RM_API int rm_get_cull_stats(rm_ctx *ctx, uint64_t *executed_map_flops, uint64_t *culled_paints, int reset);
+/* NO COUNTERPART IN THE REFERENCE — added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The culled paint of rm_set_cull with its
+ * scratch — one 64-bit mask per pixel tile — in a file-scope static device array instead of an allocated buffer: the call
+ * allocates NOTHING (no cudaMalloc / cudaFree, no allocating library routine).  Paints rows [row0, row0+nrows) of the
+ * prepared program into the CALLER's dst_rgba8_dev (required, 16-byte aligned, pitch >= 4*W); the frame bytes equal
+ * rm_paint's.  Limits: RM_KERNEL_DIRECT, reference-set programs of 8 to 64 decoded instructions (else RM_E_UNSUPPORTED);
+ * at most RM_CULL_STATIC_MAX_TILES = 262144 tiles of 8 x 8 pixels per call (one 3840x2160 frame; larger frames in row
+ * bands), beyond that RM_E_INVALID_ARG with the numbers in rm_last_error.  The array (2 MiB) is held by every GPU that loads
+ * the library until exit, is shared by every call and context on that GPU and keeps the last call's contents (the call
+ * rewrites every mask it reads): calls that OVERLAP on one GPU — two streams, two contexts — race; serialise them.  The
+ * first call per device resolves the array's device address (cudaGetSymbolAddress): make one call outside a capture. */
+#define RM_CULL_STATIC_MAX_TILES 262144u
+RM_API int rm_paint_culled_static(rm_ctx *ctx, uint32_t W, uint32_t H, uint32_t row0, uint32_t nrows, void *dst_rgba8_dev,
+                                  size_t pitch_bytes, void *cuda_stream);
 
 /* ---- program specialisation (optional; the reference compiles its shader once, RayMarchingResources::new
  *      renderer.rs:55-62 — here the SCENE can be compiled too) --------------------------------------------------- */

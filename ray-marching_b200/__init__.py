@@ -38,7 +38,7 @@ ABI_SYMBOLS = [
     "rm_flush_l2", "rm_fp32_peak", "rm_launch_count", "rm_host_alloc", "rm_host_free", "rm_last_error",
     "rm_strerror", "rm_version",
     "rm_group_create", "rm_group_destroy", "rm_group_size", "rm_group_ctx", "rm_group_set_mode", "rm_group_set_limits",
-    "rm_specialize", "rm_set_specialize", "rm_spec_info", "rm_spec_status", "rm_spec_source", "rm_spec_compile_check", "rm_spec_params", "rm_spec_cache", "rm_set_spec_literal_after", "rm_spec_tier", "rm_set_cull", "rm_get_cull_stats",
+    "rm_specialize", "rm_set_specialize", "rm_spec_info", "rm_spec_status", "rm_spec_source", "rm_spec_compile_check", "rm_spec_params", "rm_spec_cache", "rm_set_spec_literal_after", "rm_spec_tier", "rm_set_cull", "rm_get_cull_stats", "rm_paint_culled_static",
     "rm_group_specialize", "rm_group_prepare", "rm_group_paint_bands", "rm_group_frame", "rm_group_paint_poses", "rm_group_last_error",
 ]
 
@@ -123,6 +123,7 @@ def lib() -> C.CDLL:
             "rm_spec_compile_check": (i, [u32, vp, u32, i, i, C.POINTER(u64), C.POINTER(C.c_double), C.c_char_p, sz]),
             "rm_spec_params": (i, [u32, vp, u32, i, vp, sz, C.POINTER(sz)]),
             "rm_set_cull": (i, [vp, i]),
+            "rm_paint_culled_static": (i, [vp, u32, u32, u32, u32, vp, sz, vp]),
             "rm_get_cull_stats": (i, [vp, C.POINTER(u64), C.POINTER(u64), i]),
             "rm_set_spec_literal_after": (i, [vp, u32]),
             "rm_spec_tier": (i, [vp]),
@@ -278,6 +279,10 @@ class Context:
     def set_cull(self, on: bool):
         """Opt-in per-tile culling of the program (exact: identical frames; reported separately, never the headline)."""
         self._chk(self._L.rm_set_cull(self._h, int(bool(on))))
+
+    def paint_culled_static(self, W: int, H: int, row0: int, nrows: int, dst_ptr: int, pitch: int = 0, stream: int | None = None):
+        """Allocation-free culled paint into the caller's device buffer (masks in a static device array; rm_b200.h)."""
+        self._chk(self._L.rm_paint_culled_static(self._h, W, H, row0, nrows, dst_ptr, pitch or W * 4, stream))
 
     def cull_stats(self, reset: bool = True) -> dict:
         f, n = C.c_uint64(), C.c_uint64()

@@ -19,6 +19,8 @@
 // reported with EXECUTED flops beside the algorithmic ones and is never the roofline headline.
 #include "rm_cull.h"
 
+#include <mutex>
+
 #include "rm_program.h"
 
 namespace rm {
@@ -151,6 +153,48 @@ cudaError_t launch_cull_masks(const FrameParams &fp, const RmInsn *prog_dev, uin
     const unsigned blocks = (n_tiles + 63u) / 64u;
     k_cull_masks<<<blocks, 64, (size_t)fp.n_insn * sizeof(RmInsn), st>>>(fp, prog_dev, tile_h, tiles_x, n_tiles, t_end, masks_dev);
     return cudaGetLastError();
+}
+
+// ---- allocation-free variant (rm_paint_culled_static; no counterpart in the reference)
+// -----------------------------------------------------------------------------------------------------------
+// The masks of rm_paint_culled_static live in this file-scope device array instead of a cudaMalloc'ed buffer: callers that
+// cannot allocate (CUDA graph capture, tight serving loops) get the culled paint without any allocation.  Every GPU that
+// loads the library holds the RM_CULL_STATIC_MAX_TILES * 8 bytes (2 MiB) until exit.  In HOST code the array's name is only
+// a stand-in for the symbol, not a device address: the address comes from cudaGetSymbolAddress, once per device with that
+// device current, and that pointer is what the kernels are given.  The pre-pass writes the mask of every tile the paint
+// reads (nothing has to start at zero); the array keeps the last call's contents, and calls that overlap on one GPU race.
+static __device__ __align__(256) unsigned long long g_cull_static_masks[RM_CULL_STATIC_MAX_TILES];
+
+cudaError_t cull_static_masks(int device, unsigned long long **ptr) {
+    static std::mutex mu;
+    static unsigned long long *ptrs[64] = {};
+    if (!ptr || device < 0 || device >= 64) return cudaErrorInvalidValue;
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ptrs[device]) {
+        int cur = -1;
+        cudaError_t e = cudaGetDevice(&cur);
+        if (e != cudaSuccess) return e;
+        if (cur != device) return cudaErrorInvalidDevice;  // the symbol's address belongs to the device that is current
+        void *p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_cull_static_masks);
+        if (e != cudaSuccess) return e;
+        ptrs[device] = static_cast<unsigned long long *>(p);
+    }
+    *ptr = ptrs[device];
+    return cudaSuccess;
+}
+
+// The pre-pass of launch_cull_masks into the static array of `device` (which must be current): same kernel, the masks go
+// to the symbol's device address; *masks_out receives that address for the paint kernel.
+cudaError_t launch_cull_masks_static(int device, const FrameParams &fp, const RmInsn *prog_dev, uint32_t tile_h, float t_end,
+                                     const unsigned long long **masks_out, cudaStream_t st) {
+    const size_t n_tiles = (size_t)((fp.W + 7u) / 8u) * ((fp.nrows + tile_h - 1u) / tile_h);
+    if (n_tiles > RM_CULL_STATIC_MAX_TILES) return cudaErrorInvalidValue;
+    unsigned long long *masks = nullptr;
+    cudaError_t e = cull_static_masks(device, &masks);
+    if (e != cudaSuccess) return e;
+    *masks_out = masks;
+    return launch_cull_masks(fp, prog_dev, tile_h, t_end, masks, st);
 }
 
 }  // namespace rm

@@ -13,4 +13,13 @@ namespace rm {
 cudaError_t launch_cull_masks(const FrameParams &fp, const RmInsn *prog_dev, uint32_t tile_h, float t_end, unsigned long long *masks_dev,
                               cudaStream_t st);
 
+// Allocation-free variant (rm_paint_culled_static): the masks live in a file-scope static __device__ array of
+// RM_CULL_STATIC_MAX_TILES entries (2 MiB per GPU that loads the library) instead of a cudaMalloc'ed buffer.  `device` must
+// be the current device; returns cudaErrorInvalidValue when the band has more tiles than the array holds.
+#ifndef RM_CULL_STATIC_MAX_TILES  /* the same value as include/rm_b200.h declares */
+#define RM_CULL_STATIC_MAX_TILES 262144u
+#endif
+cudaError_t launch_cull_masks_static(int device, const FrameParams &fp, const RmInsn *prog_dev, uint32_t tile_h, float t_end,
+                                     const unsigned long long **masks_out, cudaStream_t st);
+
 }  // namespace rm
