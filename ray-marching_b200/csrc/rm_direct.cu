@@ -28,9 +28,6 @@ constexpr int TILE_W_D = RM_DIRECT_TILE_W;
 //   6: 44.76, 7 (72 registers, 196 B spill): 44.02, 8 (64 registers): 45.13.  One more warp per scheduler beats the spill up to 7.
 //   4-ray variant, cfg2: no hint (70 registers) 1.203 ms, 8 blocks (64 registers, 44 B spill) 1.184, 9: 1.189, 10: 1.232;
 //   an explicit hint of 1 let ptxas take 77 registers and cost 6 %.
-#ifndef RM_DIRECT_RECOMP
-#define RM_DIRECT_RECOMP 1
-#endif
 #ifndef RM_DIRECT_MINB8
 #define RM_DIRECT_MINB8 7
 #endif
@@ -92,9 +89,7 @@ k_direct(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ prog
         map.n_insn = fp.n_insn;
     }
     map.prog = s_prog; map.max_dist = fp.max_dist;
-    // fast-mode 8-ray kernels recompute the ray directions instead of holding them (rm_direct_body.cuh RECOMP)
-    constexpr bool kRecomp = RM_DIRECT_RECOMP && !EX && R == 8 && !EO;
-    direct_body<EX, R, COUNT, false, decltype(map), kRecomp>(fp, dst, pitch, counters, nullptr, nullptr, map, eval_flops);
+    direct_body<EX, R, COUNT, false>(fp, dst, pitch, counters, nullptr, nullptr, map, eval_flops);
 }
 
 // the same kernel with the per-sample AOVs written out (verification: rm_paint_aov)

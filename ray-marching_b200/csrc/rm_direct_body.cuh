@@ -25,16 +25,11 @@ __host__ __device__ constexpr uint32_t direct_tile_rows(int R) { return 4u * (32
 // AOV (verification only): also writes every sample's class (0 sky, 1 floor, 2 object) and distance (hit distance, else
 // the floor distance of wgsl:120) to aov_cls / aov_t[(row * W + x) * 16 + sample] — the same outputs, in the same
 // layout, as the one-thread-per-sample verification kernel (rm_kernels.cu), but from THIS kernel's own march.
-// RECOMP (fast mode only; the 8-ray interpreter kernels): the ray directions are NOT held in registers across the march —
-// 3 registers per ray, 24 of the interpreter kernel's 72 — but recomputed from the per-frame affine form where they are
-// needed (gen_ray_affine: ~16 instructions per ray per trip against the ~600 of one map_scene evaluation of a deep
-// program).  Same function, same inputs: the directions, and with them the frame, are bit-identical to the stored form.
-template <bool EX, int R, bool COUNT, bool AOV, class MAP, bool RECOMP = false>
+template <bool EX, int R, bool COUNT, bool AOV, class MAP>
 __device__ __forceinline__ void direct_body(const FrameParams &fp, uint8_t *__restrict__ dst, size_t pitch,
                                             unsigned long long *__restrict__ counters, uint8_t *__restrict__ aov_cls,
                                             float *__restrict__ aov_t, MAP &map, uint32_t eval_flops = 0) {
     static_assert(R == 2 || R == 4 || R == 8, "2, 4 or 8 rays per thread");
-    static_assert(!(RECOMP && EX), "directions are recomputed from the fast-mode affine form only");
     constexpr int TPP = 16 / R;           // threads per pixel
     constexpr int PPW = 32 / TPP;         // pixels per warp: 4, 8 or 16 consecutive pixels of the block's 8-wide tile
     constexpr uint32_t TILE_ROWS = direct_tile_rows(R);  // 2, 4 or 8
@@ -54,25 +49,9 @@ __device__ __forceinline__ void direct_body(const FrameParams &fp, uint8_t *__re
     uint32_t live = 0, hit = 0;  // bit r: ray r still marching / ray r hit the scene
     uint32_t c_step = 0, c_hit = 0, c_floor = 0, c_sample = 0;
     RM_FOR_R { rdx[r] = rdy[r] = rdz[r] = 0.f; dist[r] = 0.f; }
-    // RECOMP: the pixel's position in the affine form; made opaque at every use so that the compiler cannot hoist the
-    // (loop-invariant) directions back into registers
-    float rc_x = 0.f, rc_y = 0.f;
-    auto ray_dir = [&](int r, float &dx, float &dy, float &dz) {
-        if constexpr (RECOMP) {
-            float fx = rc_x, fy = rc_y, fz = 0.f;
-            RM_OPAQUE_F3(fx, fy, fz);
-            float d[3];
-            gen_ray_affine(fp, fx, fy, grp * R + (uint32_t)r, d);
-            dx = d[0]; dy = d[1]; dz = d[2];
-        } else {
-            dx = rdx[r]; dy = rdy[r]; dz = rdz[r];
-        }
-    };
     if (inside) {
         const uint32_t fy = frame_row(fp, ry);
-        if constexpr (RECOMP) {
-            rc_x = (float)px + fp.ray_bx; rc_y = (float)fy + fp.ray_by;
-        } else if constexpr (EX) {
+        if constexpr (EX) {
             RM_FOR_R {
                 float o[3], d[3];
                 gen_ray<EX>(fp, px, fy, grp * R + (uint32_t)r, o, d);  // wgsl:39-62, one rounding per operation
@@ -101,11 +80,9 @@ __device__ __forceinline__ void direct_body(const FrameParams &fp, uint8_t *__re
         // rays still live when it runs out fall through to the floor / sky code exactly like aborted ones, Q5)
         for (uint32_t it = 0; live != 0 && it < fp.max_iter; ++it) {
             RM_FOR_R {  // pos = origin + direction * dist   wgsl:91
-                float dx, dy, dz;
-                ray_dir(r, dx, dy, dz);
-                px_[r] = A::mad(dx, dist[r], ox);
-                py_[r] = A::mad(dy, dist[r], oy);
-                pz_[r] = A::mad(dz, dist[r], oz);
+                px_[r] = A::mad(rdx[r], dist[r], ox);
+                py_[r] = A::mad(rdy[r], dist[r], oy);
+                pz_[r] = A::mad(rdz[r], dist[r], oz);
             }
             RM_FOR_R RM_OPAQUE_F3(px_[r], py_[r], pz_[r]);
             map(px_, py_, pz_, s);
@@ -134,9 +111,7 @@ __device__ __forceinline__ void direct_body(const FrameParams &fp, uint8_t *__re
             RM_FOR_R {
                 if constexpr (AOV) { t_miss[r] = 0.f; cls_miss[r] = 0; }
                 if (inside && !((hit0 >> r) & 1u)) {
-                    float d[3];
-                    ray_dir(r, d[0], d[1], d[2]);
-                    const float o[3] = {ox, oy, oz};
+                    const float o[3] = {ox, oy, oz}, d[3] = {rdx[r], rdy[r], rdz[r]};
                     float c[3], t;
                     const int cls = shade_miss(o, d, c, t);
                     code[r] = cls == 0 ? RM_CODE_SKY : (c[0] > 0.2f ? RM_CODE_FLOOR_LIGHT : RM_CODE_FLOOR_DARK);
@@ -179,7 +154,7 @@ __device__ __forceinline__ void direct_body(const FrameParams &fp, uint8_t *__re
                     rr[j] = hit ? __ffs((int)hit) - 1 : -1;
                     hit &= hit - 1u;  // 0 stays 0
                     float dx = 0.f, dy = 0.f, dz = 0.f, dd = 0.f;
-                    RM_FOR_R if (r == rr[j]) { ray_dir(r, dx, dy, dz); dd = dist[r]; }
+                    RM_FOR_R if (r == rr[j]) { dx = rdx[r]; dy = rdy[r]; dz = rdz[r]; dd = dist[r]; }
                     hx[j] = A::mad(dx, dd, ox); hy[j] = A::mad(dy, dd, oy); hz[j] = A::mad(dz, dd, oz);
                     // tetrahedron taps wgsl:138-142: (+,-,-) (-,-,+) (-,+,-) (+,+,+), eps = 1e-4
                     px_[4 * j + 0] = __fadd_rn(hx[j], ep); py_[4 * j + 0] = __fadd_rn(hy[j], en); pz_[4 * j + 0] = __fadd_rn(hz[j], en);
