@@ -234,3 +234,74 @@ def test_k12_gamma_is_applied_per_sample_before_the_mean():
     mean_then_gamma = np.floor(np.clip(np.sqrt(cols.sum(0) / 16), 0, 1) * 255 + 0.5)
     assert np.abs(gamma_then_mean - mean_then_gamma).max() > 10       # the two orders are far apart for this pixel
     assert np.abs(out["rgba"][py, px, :3].astype(int) - gamma_then_mean).max() <= 1, (out["rgba"][py, px], gamma_then_mean)
+
+
+# ---- more shader facts pinned analytically (round 2) -----------------------------------------------------------------
+def test_k13_box_distance_outside_edge_corner_and_inside():
+    # wgsl:235-240: q = abs(pos - c) - r; length(max(q, 0)) + min(max(q.x, max(q.y, q.z)), 0)
+    b = h.box((1.0, -2.0, 0.5), (1.0, 2.0, 0.5))
+    pts = np.array([[4.0, -2.0, 0.5],      # off the +x face: q = (2, -2, -0.5) -> 2
+                    [4.0, 4.0, 0.5],       # off an edge: q = (2, 4, -0.5) -> sqrt(20)
+                    [5.0, 3.0, 3.0],       # off a corner: q = (3, 3, 2) -> sqrt(22)
+                    [1.0, -2.0, 0.5],      # centre: q = (-1, -2, -0.5) -> max = -0.5
+                    [1.75, -2.0, 0.5],     # inside, nearest the x faces: q = (-0.25, -2, -0.5) -> -0.25
+                    [2.0, 0.0, 1.0]],      # exactly on a corner -> 0
+                   np.float32)
+    got = h.oracle_map(1, b, pts)
+    exp = np.array([2.0, np.sqrt(np.float32(20.0)), np.sqrt(np.float32(22.0)), -0.5, -0.25, 0.0], np.float32)
+    np.testing.assert_array_equal(got, exp)
+
+
+def test_k14_operand_order_subtraction_is_a_minus_b():
+    # operations/mod.rs:7-18 emits A, then B, then the opcode; wgsl:248-252 pops b first, then a, and returns max(a, -b):
+    # Subtraction(A, B) is A with B carved out — a ray through the carved part passes A's front and hits further in
+    A, B = h.sphere((0, 0, 0), 1.0), h.sphere((0, 0, 1.0), 0.6)
+    r = h.oracle_trace(3, A + B + [h.OP_SUBTRACTION], [0, 0, 5], [0, 0, -1])
+    assert r["cls"] == 2 and abs(r["t"] - 4.6) < 0.02        # the bottom of the bowl B carved: z = 1 - 0.6 = 0.4
+    r = h.oracle_trace(3, B + A + [h.OP_SUBTRACTION], [0, 0, 5], [0, 0, -1])
+    assert r["cls"] == 2 and abs(r["t"] - 3.4) < 0.02        # B \\ A: what is left of B outside A: its cap from z = 1.6
+    # union and intersection commute; the distance values show which operand is which for the subtraction
+    p = np.array([[0.0, 0.0, 2.0]], np.float32)
+    da, db = h.oracle_map(1, A, p)[0], h.oracle_map(1, B, p)[0]
+    assert h.oracle_map(3, A + B + [h.OP_SUBTRACTION], p)[0] == max(da, -db)
+    assert h.oracle_map(3, B + A + [h.OP_SUBTRACTION], p)[0] == max(db, -da)
+
+
+def test_k15_q5_exhausting_max_iter_falls_through_to_the_floor():
+    # wgsl:90,115-130: a ray that neither hits nor aborts within max_iter iterations gets the floor / sky code like an
+    # aborted one.  A ray grazing the sphere: with 3 iterations it runs out of budget close to the surface -> floor colour.
+    c, w = h.scene_s0()
+    o, d = [0.0, 1.02, 5.0], [0.0, -0.0040, -1.0]
+    d = (np.array(d) / np.linalg.norm(d)).tolist()
+    full = h.oracle_trace(c, w, o, d)
+    short = h.oracle_trace(c, w, o, d, limits=h.limits_bytes(0.01, 100.0, 3))
+    assert short["n_step"] == 3 and short["cls"] == 1            # out of iterations: floor (the ray points slightly down)
+    assert full["n_step"] > 3
+    # the floor colour is the same analytic plane either way (no distance limit, Q6)
+    miss = h.oracle_trace(0, [], o, d, limits=h.limits_bytes(0.01, 100.0, 1))
+    np.testing.assert_array_equal(short["rgb"], miss["rgb"])
+
+
+def test_k16_perspective_pixel_to_ray_closed_form():
+    # A1 + wgsl:52-62 for the identity camera at (0,0,5): the ray through sample (i, j) of pixel (px, py) has direction
+    # proportional to (p.x * aspect * tan(fov/2), p.y * tan(fov/2), -1) with p = pt_screen + offset (near = 1)
+    W, H = 640, 480
+    u = h.orbit_uniforms(W, H)
+    t = math.tan(math.pi / 8)
+    for px, py in ((0, 0), (639, 479), (320, 100), (17, 400)):
+        ro, dirs = _sample_rays(u, W, H, px, py)
+        np.testing.assert_allclose(ro, [0, 0, 5], atol=1e-6)
+        for i in range(4):
+            for j in range(4):
+                x = (px + 0.5) / W * 2 - 1 + ((i + 0.5) / 4 - 0.5) / W * 2
+                y = 1 - (py + 0.5) / H * 2 + ((j + 0.5) / 4 - 0.5) / H * 2
+                v = np.array([x * (W / H) * t, y * t, -1.0])
+                # the shader normalises the 4-vector (w component of pt_world - ro_world is 1 - 1 = 0 here)
+                np.testing.assert_allclose(dirs[4 * i + j], v / np.linalg.norm(v), atol=2e-6)
+    # and the oracle's image agrees with tracing those rays one by one (class of every sample of two pixels)
+    c, w = h.scene_s0()
+    out = h.oracle_render(u, c, w, W, H, row0=240, nrows=1, aov=True)
+    for px in (200, 201):
+        ro, dirs = _sample_rays(u, W, H, px, 240)
+        cls = [h.oracle_trace(c, w, ro.astype(np.float32), dd.astype(np.float32))["cls"] for dd in dirs]
+        assert cls == out["cls"][0, px].tolist()
