@@ -139,6 +139,34 @@ def ncu_traffic(workload: str, kernel: str, specialised: bool = False):
     return None, None
 
 
+def ncu_executed_fp32(workload: str, kernel: str, specialised: bool = False):
+    """Executed FP32 arithmetic of the dominant kernel from the same committed ncu capture: thread-level FADD + FMUL +
+    2 x FFMA per elapsed cycle (ncu's sass_thread_inst_executed_op_f* counters) against the 2 x 128 x SMs the FFMA peak
+    allows.  ncu's classes leave out FMNMX / abs / neg / MUFU, which the ALGORITHMIC count includes at one flop
+    each: this is the pessimistic companion of roofline.frac, not a replacement.  -> dict or None"""
+    for name in NCU_SUMMARIES.get((workload, kernel, specialised), []):
+        f = ROOT / "profiles" / name
+        if not f.exists():
+            continue
+        v = {}
+        for line in f.read_text().splitlines():
+            parts = [p.strip('"') for p in line.split('","')]
+            if len(parts) == 3:
+                v[parts[0]] = parts[1]
+        try:
+            fadd = float(v["smsp__sass_thread_inst_executed_op_fadd_pred_on.sum.per_cycle_elapsed"])
+            fmul = float(v["smsp__sass_thread_inst_executed_op_fmul_pred_on.sum.per_cycle_elapsed"])
+            ffma = float(v["smsp__sass_thread_inst_executed_op_ffma_pred_on.sum.per_cycle_elapsed"])
+            peak = float(v["derived__sm__sass_thread_inst_executed_op_ffma_pred_on_x2"])
+        except (KeyError, ValueError):
+            return None
+        return {"fadd_per_cycle": fadd, "fmul_per_cycle": fmul, "ffma_per_cycle": ffma, "flops_per_cycle": fadd + fmul + 2 * ffma,
+                "peak_flops_per_cycle": peak, "frac": (fadd + fmul + 2 * ffma) / peak, "source": f"profiles/{name}",
+                "note": "FADD + FMUL + 2 x FFMA thread instructions per elapsed cycle under ncu (FMNMX, abs / neg modifiers and MUFU are "
+                        "not in these classes; the algorithmic count gives them one flop each)"}
+    return None
+
+
 def cpu_sample_rows(H: int, n: int):
     n = max(1, min(n, H))
     return sorted({min(H - 1, int((i + 0.5) * H / n)) for i in range(n)})  # evenly spaced over the whole frame
@@ -892,6 +920,8 @@ def b200_arm(args) -> int:
                 "framebuffer_gbs": fb_bytes / (ms_local * 1e-3) / 1e9,
                 "hbm_peak_gbs": hbm_gbs, "hbm_peak_source": "MEASURED_PEAKS.json hbm_gbs" if hbm_gbs else "MEASURED_PEAKS.json absent",
                 "framebuffer_frac_of_hbm_peak": (fb_bytes / (ms_local * 1e-3) / 1e9 / hbm_gbs) if hbm_gbs else None}
+        if args.mode == "fast" and args.cull != "on":
+            roof["executed_fp32_ncu"] = ncu_executed_fp32(args.workload, args.kernel, spec["active"])
         if args.cull == "on" and getattr(rig, "cull_stats", {}).get("culled_paints"):
             n_eval = float(counters[0]) + 4.0 * float(counters[1])
             executed = flops - n_eval * fmap + float(rig.cull_stats["executed_map_flops"])
