@@ -46,7 +46,7 @@ __device__ __forceinline__ void direct_body(const FrameParams &fp, uint8_t *__re
     // The ray origin is the same for every ray of the frame (wgsl:39-40): read where it is used, it stays a uniform operand.
     const float ox = fp.ro4[0], oy = fp.ro4[1], oz = fp.ro4[2];
     float rdx[R], rdy[R], rdz[R], dist[R];
-    uint32_t live = 0, hit = 0;  // bit r: ray r still marching / ray r hit the scene
+    uint32_t live = 0, hit = 0;  // bit r: ray r hit the scene; live: rays still marching (counting build only)
     uint32_t c_step = 0, c_hit = 0, c_floor = 0, c_sample = 0;
     RM_FOR_R { rdx[r] = rdy[r] = rdz[r] = 0.f; dist[r] = 0.f; }
     if (inside) {
@@ -78,7 +78,14 @@ __device__ __forceinline__ void direct_body(const FrameParams &fp, uint8_t *__re
         // ---------------- march: all live rays of the thread take one step per trip (wgsl:88-115) ----------------
         // (the loop bound of wgsl:90 is the same for every ray — they all start at trip 0 — so it bounds the loop itself:
         // rays still live when it runs out fall through to the floor / sky code exactly like aborted ones, Q5)
-        for (uint32_t it = 0; live != 0 && it < fp.max_iter; ++it) {
+        // A stopped ray is not masked out of the later trips: its position is frozen, so MAP returns the same distance
+        // for it every time, the two comparisons below come out the same way and its distance stays put (a fixed
+        // point).  The loop therefore carries no live / hit masks: a ray has hit iff the distance of the LAST trip is
+        // under min_dist (a ray still marching when the bound runs out was not), and the thread goes on while any of
+        // its rays advanced.  Per ray and trip: two compares and one predicated add, no divergent branch.
+        bool go = inside;
+        RM_FOR_R s[r] = 3.0e38f;
+        for (uint32_t it = 0; go && it < fp.max_iter; ++it) {
             RM_FOR_R {  // pos = origin + direction * dist   wgsl:91
                 px_[r] = A::mad(rdx[r], dist[r], ox);
                 py_[r] = A::mad(rdy[r], dist[r], oy);
@@ -86,21 +93,19 @@ __device__ __forceinline__ void direct_body(const FrameParams &fp, uint8_t *__re
             }
             RM_FOR_R RM_OPAQUE_F3(px_[r], py_[r], pz_[r]);
             map(px_, py_, pz_, s);
+            go = false;
             RM_FOR_R {
-                const uint32_t bit = 1u << r;
-                if (live & bit) {
-                    if (COUNT) ++c_step;
-                    if (s[r] < fp.min_dist) {  // wgsl:97: hit, dist stays at the hit distance
-                        hit |= bit;
-                        live &= ~bit;
-                    } else if (s[r] > fp.max_dist) {  // wgsl:109-111
-                        live &= ~bit;
-                    } else {
-                        dist[r] = A::add(dist[r], s[r]);  // wgsl:114
-                    }
+                // wgsl:97 hit, dist stays at the hit distance; wgsl:109-111 gone past max_dist; else wgsl:114 advance
+                const bool stop = (s[r] < fp.min_dist) | (s[r] > fp.max_dist);
+                if (COUNT) {
+                    c_step += (live >> r) & 1u;
+                    live &= stop ? ~(1u << r) : ~0u;
                 }
+                dist[r] = stop ? dist[r] : A::add(dist[r], s[r]);  // wgsl:114
+                go |= !stop;
             }
         }
+        RM_FOR_R hit |= (s[r] < fp.min_dist) ? (1u << r) : 0u;
         // ---------------- normals + diffuse term of the rays that hit (wgsl:98-105,138-143) ----------------
         hit0 = hit;
         RM_FOR_R code[r] = RM_CODE_SKY;
