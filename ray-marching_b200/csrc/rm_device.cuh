@@ -402,6 +402,25 @@ __device__ __forceinline__ uint32_t unorm8(float v) {
 #define RM_CODE_FLOOR_LIGHT (-2.0f)
 #define RM_CODE_SKY (-3.0f)
 
+// shade_miss, returning the sample code directly (the cell's parity picks the code; no colour is formed).
+__device__ __forceinline__ float shade_miss_code(const float ro[3], const float rd[3], float &t, int &cls) {
+    const float fd = __fdiv_rn(__fsub_rn(RM_FLOOR_Y, ro[1]), rd[1]);  // wgsl:120
+    t = fd;
+    cls = 0;
+    if (fd > 0.0f) {
+        const float fx = __fadd_rn(ro[0], __fmul_rn(rd[0], fd)), fz = __fadd_rn(ro[2], __fmul_rn(rd[2], fd));
+        const int ix = __float2int_rn(__fadd_rn(fx, 0.5f)), iz = __float2int_rn(__fadd_rn(fz, 0.5f));
+        cls = 1;
+        return ((ix ^ iz) & 1) ? RM_CODE_FLOOR_LIGHT : RM_CODE_FLOOR_DARK;  // 0.1 + 0.2 col > 0.2 iff col == 1
+    }
+    return RM_CODE_SKY;
+}
+
+#define RM_GAMMA_FLOOR_DARK_RG 0.31622776f   /* 0x3ea1e89b */
+#define RM_GAMMA_FLOOR_DARK_B 0.4472136f     /* 0x3ee4f92e */
+#define RM_GAMMA_FLOOR_LIGHT_RG 0.5477226f   /* 0x3f0c378c */
+#define RM_GAMMA_FLOOR_LIGHT_B 0.6324555f    /* 0x3f21e89b */
+
 // Colour of a sample code, gamma'd (wgsl:68) — always with exact roundings (negligible cost).
 __device__ __forceinline__ void code_to_gamma(float code, float g[3]) {
     if (code >= 0.0f) {
@@ -411,10 +430,11 @@ __device__ __forceinline__ void code_to_gamma(float code, float g[3]) {
     } else if (code == RM_CODE_SKY) {
         g[0] = g[1] = g[2] = 0.0f;
     } else {
-        const float col = (code == RM_CODE_FLOOR_LIGHT) ? 1.0f : 0.0f;
-        const float rg = __fadd_rn(0.1f, __fmul_rn(0.2f, col)), b = __fadd_rn(0.2f, __fmul_rn(0.2f, col));
-        g[0] = g[1] = __fsqrt_rn(rg);
-        g[2] = __fsqrt_rn(b);
+        // sqrt_rn(0.1 + 0.2 col), sqrt_rn(0.2 + 0.2 col) (wgsl:124-127, 68) for col = 0 / 1: four constants, the correctly
+        // rounded roots of fl(0.1), fl(0.2), fl(0.1 + 0.2), fl(0.2 + 0.2) (tests/test_hostcheck_cpu.py recomputes them)
+        const bool light = code == RM_CODE_FLOOR_LIGHT;
+        g[0] = g[1] = light ? RM_GAMMA_FLOOR_LIGHT_RG : RM_GAMMA_FLOOR_DARK_RG;
+        g[2] = light ? RM_GAMMA_FLOOR_LIGHT_B : RM_GAMMA_FLOOR_DARK_B;
     }
 }
 
@@ -437,6 +457,13 @@ __device__ __forceinline__ void code_to_gamma_t(float code, float g[3]) {
     }
 }
 
+// sum / 16 (wgsl:75) as sum * 0.0625: 16 is a power of two, so both are the correctly rounded value of the same real
+// number for every float (subnormal results, infinities and NaN included) — one multiply instead of an IEEE division.
+__device__ __forceinline__ uint32_t pack_mean16(float sr, float sg, float sb) {
+    return unorm8(__fmul_rn(sr, 0.0625f)) | (unorm8(__fmul_rn(sg, 0.0625f)) << 8) | (unorm8(__fmul_rn(sb, 0.0625f)) << 16) |
+           0xff000000u;
+}
+
 // In-order 16-sample mean (wgsl:44-45,68-75) and RGBA8 pack.
 __device__ __forceinline__ uint32_t resolve_pixel(const float *codes16) {
     float sr = 0.0f, sg = 0.0f, sb = 0.0f;
@@ -446,8 +473,7 @@ __device__ __forceinline__ uint32_t resolve_pixel(const float *codes16) {
         code_to_gamma(codes16[s], g);
         sr = __fadd_rn(sr, g[0]); sg = __fadd_rn(sg, g[1]); sb = __fadd_rn(sb, g[2]);
     }
-    return unorm8(__fdiv_rn(sr, 16.0f)) | (unorm8(__fdiv_rn(sg, 16.0f)) << 8) |
-           (unorm8(__fdiv_rn(sb, 16.0f)) << 16) | 0xff000000u;
+    return pack_mean16(sr, sg, sb);
 }
 
 }  // namespace rm

@@ -117,9 +117,9 @@ __device__ __forceinline__ void direct_body(const FrameParams &fp, uint8_t *__re
                 if constexpr (AOV) { t_miss[r] = 0.f; cls_miss[r] = 0; }
                 if (inside && !((hit0 >> r) & 1u)) {
                     const float o[3] = {ox, oy, oz}, d[3] = {rdx[r], rdy[r], rdz[r]};
-                    float c[3], t;
-                    const int cls = shade_miss(o, d, c, t);
-                    code[r] = cls == 0 ? RM_CODE_SKY : (c[0] > 0.2f ? RM_CODE_FLOOR_LIGHT : RM_CODE_FLOOR_DARK);
+                    float t;
+                    int cls;
+                    code[r] = shade_miss_code(o, d, t, cls);
                     if (COUNT && cls != 0) ++c_floor;
                     if constexpr (AOV) { t_miss[r] = t; cls_miss[r] = cls; }
                 }
@@ -201,8 +201,7 @@ __device__ __forceinline__ void direct_body(const FrameParams &fp, uint8_t *__re
         const int src = (lane / TPP) * TPP + g;
         sr = __shfl_sync(RM_FULL_MASK, sr, src); sg = __shfl_sync(RM_FULL_MASK, sg, src); sb = __shfl_sync(RM_FULL_MASK, sb, src);
     }
-    const uint32_t pix = unorm8(__fdiv_rn(sr, 16.0f)) | (unorm8(__fdiv_rn(sg, 16.0f)) << 8) |
-                         (unorm8(__fdiv_rn(sb, 16.0f)) << 16) | 0xff000000u;
+    const uint32_t pix = pack_mean16(sr, sg, sb);
     // ---------------- store: every 4 consecutive pixels of a row go out as one 128-bit store ----------------
     const uint32_t x0 = tx * RM_DIRECT_TILE_W;
     constexpr int QUADS = PPW / 4;               // 4-pixel groups per warp

@@ -276,8 +276,7 @@ __device__ __noinline__ uint32_t wf_resolve(const float *codes, int lane) {
         code_to_gamma(codes[sidx * 32 + lane], g);
         sr = __fadd_rn(sr, g[0]); sg = __fadd_rn(sg, g[1]); sb = __fadd_rn(sb, g[2]);
     }
-    return unorm8(__fdiv_rn(sr, 16.0f)) | (unorm8(__fdiv_rn(sg, 16.0f)) << 8) |
-           (unorm8(__fdiv_rn(sb, 16.0f)) << 16) | 0xff000000u;
+    return pack_mean16(sr, sg, sb);
 }
 
 }  // namespace

@@ -358,3 +358,25 @@ def test_generated_code_of_the_reference_set_matches_too(hc, rm_lib, tmp_path):
     cmd, words = h.scene_s1()
     got, _ = _spec_map_on_host(tmp_path, rm_lib, cmd, words, True, 0, PTS)
     assert same_bits(got, h.oracle_map(cmd, words, PTS))
+
+
+def test_epilogue_constants_are_the_correctly_rounded_values_the_shader_computes():
+    """rm_device.cuh holds the four gamma'd floor colours as constants and divides the 16-sample sum by 16 with a multiply:
+    both must be what the oracle's operation-by-operation arithmetic gives (wgsl:124-127, 68, 75)."""
+    import re
+    src = (CSRC / "rm_device.cuh").read_text()
+    got = {m.group(1): np.float32(m.group(2)) for m in re.finditer(r"#define RM_GAMMA_FLOOR_(\w+) ([0-9.]+)f", src)}
+    f = np.float32
+    want = {"DARK_RG": np.sqrt(f(0.1) + f(0.2) * f(0)), "DARK_B": np.sqrt(f(0.2) + f(0.2) * f(0)),
+            "LIGHT_RG": np.sqrt(f(0.1) + f(0.2) * f(1)), "LIGHT_B": np.sqrt(f(0.2) + f(0.2) * f(1))}
+    assert set(got) == set(want)
+    for k in want:
+        assert want[k].dtype == np.float32 and got[k].view(np.uint32) == want[k].view(np.uint32), k
+    assert f(0.1) + f(0.2) * f(1) > f(0.2) and not f(0.1) + f(0.2) * f(0) > f(0.2)   # the light / dark test of the code
+    rng = np.random.default_rng(5)
+    x = np.concatenate([rng.integers(0, 2**32, 2_000_000, dtype=np.uint64).astype(np.uint32).view(np.float32),
+                        np.array([0.0, -0.0, 1e-45, 2e-44, 1.7e-38, 16.0, 3.4e38, np.inf, -np.inf], np.float32)])
+    with np.errstate(all="ignore"):
+        a, b = x / f(16.0), x * f(0.0625)
+    ok = (a.view(np.uint32) == b.view(np.uint32)) | (np.isnan(a) & np.isnan(b))
+    assert ok.all()
