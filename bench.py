@@ -10,7 +10,7 @@ A "step" is one pass of the hot path over one batch: rm_paint of the workload's 
                   quoted on.  N>1: every rank renders the same 4K pose per step (fixed work per GPU, no data-path
                   collective) -> "scaling": "weak".  The same invocation then measures the two SHARDED configs of the
                   north star and reports them under "strong" (--strong off skips them):
-                    cfg4  ONE 7680x4320 S2 frame per step, interleaved 16-row strips over the ranks, every rank's render
+                    cfg4  ONE 7680x4320 S2 frame per step, interleaved strips (16 rows, or the largest height that gives every rank the same count) over the ranks, every rank's render
                           kernel storing its strips straight into rank 0's frame over NVLink (CUDA IPC mapping)
                     cfg5  1024 orbit poses of S1 at 1080p per step, pose k -> rank k % N
                   each with the time of rank 0 doing the whole step ALONE on the same box (n1_ms_same_box), so that the
@@ -43,7 +43,7 @@ WORKLOADS = {
     "cfg1": ("S0", 640, 480, 1, "configs[0]: single-sphere S0 640x480"),
     "cfg2": ("S1", 1920, 1080, 1, "configs[1]: editor CSG scene S1 (box U sphere \\ sphere) 1920x1080"),
     "cfg3": ("S2", 3840, 2160, 1, "configs[2]: deep CSG S2 (32 leaves, 28 smooth-unions, 3 subtractions; 251 words) 3840x2160"),
-    "cfg4": ("S2", 7680, 4320, 1, "configs[3]: S2 at 7680x4320, one frame row-sharded in interleaved 16-row strips, gathered on rank 0"),
+    "cfg4": ("S2", 7680, 4320, 1, "configs[3]: S2 at 7680x4320, one frame row-sharded in interleaved strips, gathered on rank 0"),
     "cfg5": ("S1", 1920, 1080, 1024, "configs[4]: 1024 orbit poses of S1 at 1920x1080, frame-parallel"),
     # not a BASELINE.json config: the N4 extension scene (plane + translation / rotation / scale groups), single GPU
     "n4": ("S3", 1920, 1080, 1, "extension (SURVEY 8(f) N4, not a BASELINE config): S3, 8 rotated / translated / scaled instances over a plane, 1920x1080"),
@@ -432,7 +432,7 @@ def run_cfg4(rig: Rig, args, steps: int, warm: int, with_n1: bool) -> dict:
     scene, W, H, _, desc = WORKLOADS["cfg4"]
     cmd, words = rig.scenes.program(scene)
     uniforms = rig.scenes.orbit_uniforms(W, H, yaw=0.6, pitch=0.4)
-    strip = rig.sharding.DEFAULT_STRIP_ROWS
+    strip = rig.sharding.balanced_strip_rows(H, world)   # every rank the same number of strips (16 rows when that works)
     ctx.prepare(uniforms, cmd, words)
     spec = rig.specialise(args)
     out = {"workload": desc, "ranks": world, "kernel": kernel_label(args, spec)}

@@ -17,6 +17,18 @@ def n_strips(H: int, strip_rows: int) -> int:
     return (H + strip_rows - 1) // strip_rows
 
 
+def balanced_strip_rows(H: int, world: int, max_rows: int = DEFAULT_STRIP_ROWS, min_rows: int = 4) -> int:
+    """The strip height for an H-row frame over `world` ranks: the largest height <= max_rows that gives every rank the SAME
+    number of whole strips (H % s == 0 and (H / s) % world == 0), even heights before odd ones; DEFAULT_STRIP_ROWS when none
+    in [min_rows, max_rows] does.  4320 rows over 8 ranks: 16-row strips are 270 strips = 34 for six ranks and 33 for two
+    (the step waits for the ranks with 34: 3 % of imbalance, measured 16.6 against 16.1 ms); 12-row strips are 45 each."""
+    if world <= 1:
+        return max_rows
+    ok = [s for s in range(max_rows, min_rows - 1, -1) if H % s == 0 and (H // s) % world == 0]
+    even = [s for s in ok if s % 2 == 0]
+    return (even or ok or [DEFAULT_STRIP_ROWS])[0]
+
+
 def local_rows(H: int, strip_rows: int, rank: int, world: int) -> int:
     """Rows rank `rank` renders (what rm_paint_strips reports in *rows_painted)."""
     rows = 0

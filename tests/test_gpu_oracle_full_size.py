@@ -126,7 +126,10 @@ def test_cfg3_270_rows_of_3840x2160_against_the_oracle(rm, ctx):
 
 def test_cfg4_rows_of_7680x4320_through_strips_into_against_the_oracle(rm, ctx):
     import torch
-    W, H, strip, world = 7680, 4320, 16, 8
+    import importlib
+    W, H, world = 7680, 4320, 8
+    strip = importlib.import_module("ray_marching_b200.sharding").balanced_strip_rows(H, world)   # what bench.py runs: 12 rows
+    assert strip == 12
     cmd, words = h.scene_s2()
     u = h.orbit_uniforms(W, H, yaw=0.6, pitch=0.4)
     rows = spaced_rows(H, 72)

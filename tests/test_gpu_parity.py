@@ -196,7 +196,7 @@ def test_row_bands_bit_identical_to_full_frame(rm, ctx):
         assert np.array_equal(np.concatenate(parts, 0), full)
 
 
-@pytest.mark.parametrize("H,strip,world", [(144, 16, 8), (50, 16, 3), (43, 4, 2)])
+@pytest.mark.parametrize("H,strip,world", [(144, 16, 8), (50, 16, 3), (43, 4, 2), (96, 12, 8), (90, 15, 3), (70, 10, 7)])
 def test_interleaved_strips_bit_identical_to_full_frame(rm, ctx, H, strip, world):
     import importlib
     sh = importlib.import_module("ray_marching_b200.sharding")

@@ -20,7 +20,21 @@ def sharding():
     return importlib.import_module("ray_marching_b200.sharding")
 
 
-@pytest.mark.parametrize("H,strip,world", [(4320, 16, 8), (2160, 16, 4), (100, 16, 3), (7, 4, 2), (33, 8, 8), (16, 16, 2)])
+def test_balanced_strip_height_gives_every_rank_the_same_number_of_strips():
+    sh = sharding()
+    assert sh.balanced_strip_rows(4320, 1) == 16 and sh.balanced_strip_rows(4320, 2) == 16      # 270 strips: 135 each
+    assert sh.balanced_strip_rows(4320, 8) == 12 and sh.balanced_strip_rows(4320, 4) == 12      # 360 strips: 45 / 90 each
+    assert sh.balanced_strip_rows(2160, 8) == 10                                                 # 216 strips: 27 each
+    assert sh.balanced_strip_rows(1080, 7) == 16                                                 # nothing balances: the default
+    for H, world in ((4320, 8), (4320, 4), (4320, 2), (2160, 8), (2160, 3), (1080, 5)):
+        s = sh.balanced_strip_rows(H, world)
+        rows = [sh.local_rows(H, s, r, world) for r in range(world)]
+        assert sum(rows) == H and 4 <= s <= 16
+        if H % s == 0 and (H // s) % world == 0:
+            assert len(set(rows)) == 1, (H, world, s, rows)
+
+
+@pytest.mark.parametrize("H,strip,world", [(4320, 16, 8), (4320, 12, 8), (2160, 15, 8), (2160, 16, 4), (100, 16, 3), (7, 4, 2), (33, 8, 8), (16, 16, 2)])
 def test_strip_plan_covers_every_row_once(H, strip, world):
     sh = sharding()
     assert sum(sh.local_rows(H, strip, r, world) for r in range(world)) == H
