@@ -24,6 +24,8 @@
 #define RM_PTX_SUB_ACC(acc, v) asm("sub.rn.f32 %0, %0, %1;" : "+f"(acc) : "f"(v))
 #define RM_PTX_FMA_ACC(acc, a, b) asm("fma.rn.f32 %0, %1, %2, %0;" : "+f"(acc) : "f"(a), "f"(b))
 #define RM_OPAQUE_F3(a, b, c) asm volatile("" : "+f"(a), "+f"(b), "+f"(c))  /* scheduling fence: values become opaque */
+/* the block's tile coordinates, read again where they are needed so that nothing derived from them lives across the loops */
+#define RM_REREAD_CTAID(cx_, cy_) asm volatile("mov.u32 %0, %%ctaid.x;\n\tmov.u32 %1, %%ctaid.y;" : "=r"(cx_), "=r"(cy_))
 #else
 #define RM_PTX_SQRT_APPROX(r, a) ((r) = sqrtf(a))
 #define RM_PTX_MIN_ACC(acc, v) ((acc) = fminf((acc), (v)))
@@ -31,6 +33,7 @@
 #define RM_PTX_SUB_ACC(acc, v) ((acc) = (acc) - (v))
 #define RM_PTX_FMA_ACC(acc, a, b) ((acc) = fmaf((a), (b), (acc)))
 #define RM_OPAQUE_F3(a, b, c) ((void)0)
+#define RM_REREAD_CTAID(cx_, cy_) ((cx_) = blockIdx.x, (cy_) = blockIdx.y)
 #endif
 
 namespace rm {

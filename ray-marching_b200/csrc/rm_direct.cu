@@ -68,7 +68,7 @@ k_direct(const __grid_constant__ FrameParams fp, const RmInsn *__restrict__ prog
     uint32_t eval_flops = 0;
     if constexpr (CULL) {
         __shared__ uint32_t s_flops;
-        const unsigned long long mask = masks[blockIdx.x];
+        const unsigned long long mask = masks[blockIdx.y * gridDim.x + blockIdx.x];  // row-major over the tiles, as k_cull_masks wrote them
         if (threadIdx.x == 0) s_flops = 0;
         __syncthreads();
         for (uint32_t i = threadIdx.x; i < fp.n_insn; i += blockDim.x) {
@@ -114,8 +114,7 @@ cudaError_t launch_direct_aov_t(const FrameParams &fp, const RmInsn *prog, uint8
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     const uint32_t tile_h = direct_tile_rows(R);
-    const unsigned grid = ((fp.W + TILE_W_D - 1) / TILE_W_D) * ((fp.nrows + tile_h - 1) / tile_h);
-    kern<<<grid, DIRECT_THREADS, smem, st>>>(fp, prog, dst, pitch, cls, t);
+    kern<<<direct_grid(fp, tile_h), DIRECT_THREADS, smem, st>>>(fp, prog, dst, pitch, cls, t);
     return cudaGetLastError();
 }
 
@@ -127,8 +126,7 @@ cudaError_t launch_direct_t(const FrameParams &fp, const RmInsn *prog, uint8_t *
     const size_t smem = (size_t)fp.n_insn * sizeof(RmInsn);
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    const unsigned grid = ((fp.W + TILE_W_D - 1) / TILE_W_D) * ((fp.nrows + tile_h - 1) / tile_h);
-    kern<<<grid, DIRECT_THREADS, smem, st>>>(fp, prog, dst, pitch, counters, masks);
+    kern<<<direct_grid(fp, tile_h), DIRECT_THREADS, smem, st>>>(fp, prog, dst, pitch, counters, masks);
     return cudaGetLastError();
 }
 

@@ -21,6 +21,16 @@ namespace rm {
 
 // rows of the 8-wide pixel tile one 128-thread block covers
 __host__ __device__ constexpr uint32_t direct_tile_rows(int R) { return 4u * (32u / (16u / (uint32_t)R)) / 8u; }
+// The launch grid of the body: one block per 8 x direct_tile_rows(R) pixel tile, tile column in x and tile row in y (a
+// linear grid cost every thread a 32-bit division to find its tile).  y holds up to 65535 tile rows = 131070 frame rows at
+// 2 rays per thread.
+__host__ __device__ inline dim3 direct_grid(const FrameParams &fp, uint32_t tile_h) {
+    dim3 g;
+    g.x = (fp.W + RM_DIRECT_TILE_W - 1) / RM_DIRECT_TILE_W;
+    g.y = (fp.nrows + tile_h - 1) / tile_h;
+    g.z = 1;
+    return g;
+}
 
 // AOV (verification only): also writes every sample's class (0 sky, 1 floor, 2 object) and distance (hit distance, else
 // the floor distance of wgsl:120) to aov_cls / aov_t[(row * W + x) * 16 + sample] — the same outputs, in the same
@@ -36,8 +46,7 @@ __device__ __forceinline__ void direct_body(const FrameParams &fp, uint8_t *__re
     using A = Arith<EX>;
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint32_t tiles_x = (fp.W + RM_DIRECT_TILE_W - 1) / RM_DIRECT_TILE_W;
-    const uint32_t tx = blockIdx.x % tiles_x, ty = blockIdx.x / tiles_x;
+    const uint32_t tx = blockIdx.x, ty = blockIdx.y;  // direct_grid
     const uint32_t pb = (uint32_t)warp * PPW + (uint32_t)lane / TPP;  // pixel of the block, row-major over its 8-wide tile
     const uint32_t px = tx * RM_DIRECT_TILE_W + (pb & 7u), ry = ty * TILE_ROWS + (pb >> 3);
     const uint32_t grp = (uint32_t)lane % TPP;  // this thread holds samples grp*R .. grp*R+R-1 (sample = 4*i + j)
@@ -113,9 +122,12 @@ __device__ __forceinline__ void direct_body(const FrameParams &fp, uint8_t *__re
         // loop; always with exact roundings (one division per missed ray).  With 2 rays per thread it runs BEFORE the taps
         // (the ray directions are then dead while MAP runs again), else after them.
         auto shade_missed = [&]() {
+            uint32_t tx_m, ty_m;
+            RM_REREAD_CTAID(tx_m, ty_m);  // `inside` again, from scratch: nothing of it lives across the march
+            const bool inside_m = tx_m * RM_DIRECT_TILE_W + (pb & 7u) < fp.W && ty_m * TILE_ROWS + (pb >> 3) < fp.nrows;
             RM_FOR_R {
                 if constexpr (AOV) { t_miss[r] = 0.f; cls_miss[r] = 0; }
-                if (inside && !((hit0 >> r) & 1u)) {
+                if (inside_m && !((hit0 >> r) & 1u)) {
                     const float o[3] = {ox, oy, oz}, d[3] = {rdx[r], rdy[r], rdz[r]};
                     float t;
                     int cls;
@@ -181,8 +193,13 @@ __device__ __forceinline__ void direct_body(const FrameParams &fp, uint8_t *__re
         }
         if constexpr (R != 2) shade_missed();
     }
-    if constexpr (AOV) if (inside) {
-        const size_t base = ((size_t)ry * fp.W + px) * 16 + grp * R;
+    // the tile's coordinates once more for the outputs (see RM_REREAD_CTAID)
+    uint32_t tx_o, ty_o;
+    RM_REREAD_CTAID(tx_o, ty_o);
+    const uint32_t px_o = tx_o * RM_DIRECT_TILE_W + (pb & 7u), ry_o = ty_o * TILE_ROWS + (pb >> 3);
+    const bool inside_o = px_o < fp.W && ry_o < fp.nrows;
+    if constexpr (AOV) if (inside_o) {
+        const size_t base = ((size_t)ry_o * fp.W + px_o) * 16 + grp * R;
         RM_FOR_R {
             const bool h = (hit0 >> r) & 1u;
             aov_cls[base + r] = (uint8_t)(h ? 2 : cls_miss[r]);
@@ -195,15 +212,25 @@ __device__ __forceinline__ void direct_body(const FrameParams &fp, uint8_t *__re
     float gm[R][3];
     RM_FOR_R code_to_gamma_t<EX>(code[r], gm[r]);
     float sr = 0.0f, sg = 0.0f, sb = 0.0f;
+    if constexpr (EX) {
 #pragma unroll
-    for (int g = 0; g < TPP; ++g) {
-        if ((int)grp == g) RM_FOR_R { sr = __fadd_rn(sr, gm[r][0]); sg = __fadd_rn(sg, gm[r][1]); sb = __fadd_rn(sb, gm[r][2]); }
-        const int src = (lane / TPP) * TPP + g;
-        sr = __shfl_sync(RM_FULL_MASK, sr, src); sg = __shfl_sync(RM_FULL_MASK, sg, src); sb = __shfl_sync(RM_FULL_MASK, sb, src);
+        for (int g = 0; g < TPP; ++g) {
+            if ((int)grp == g) RM_FOR_R { sr = __fadd_rn(sr, gm[r][0]); sg = __fadd_rn(sg, gm[r][1]); sb = __fadd_rn(sb, gm[r][2]); }
+            const int src = (lane / TPP) * TPP + g;
+            sr = __shfl_sync(RM_FULL_MASK, sr, src); sg = __shfl_sync(RM_FULL_MASK, sg, src); sb = __shfl_sync(RM_FULL_MASK, sb, src);
+        }
+    } else {
+        // fast mode: the same 16 terms as a tree — each thread its own R, then a butterfly over the pixel's lanes (every
+        // lane ends with the same bits: a + b and b + a).  Differs from the sequential sum by roundings of ~1e-7 relative.
+        RM_FOR_R { sr += gm[r][0]; sg += gm[r][1]; sb += gm[r][2]; }
+#pragma unroll
+        for (int d = 1; d < TPP; d <<= 1) {
+            sr += __shfl_xor_sync(RM_FULL_MASK, sr, d); sg += __shfl_xor_sync(RM_FULL_MASK, sg, d); sb += __shfl_xor_sync(RM_FULL_MASK, sb, d);
+        }
     }
     const uint32_t pix = pack_mean16(sr, sg, sb);
     // ---------------- store: every 4 consecutive pixels of a row go out as one 128-bit store ----------------
-    const uint32_t x0 = tx * RM_DIRECT_TILE_W;
+    const uint32_t x0 = tx_o * RM_DIRECT_TILE_W;
     constexpr int QUADS = PPW / 4;               // 4-pixel groups per warp
     const int q4 = (lane & (QUADS - 1)) * 4;     // first of the 4 pixels this lane gathers (used by lanes < QUADS)
     uint4 v;
@@ -212,12 +239,12 @@ __device__ __forceinline__ void direct_body(const FrameParams &fp, uint8_t *__re
     v.z = __shfl_sync(RM_FULL_MASK, pix, (q4 + 2) * TPP);
     v.w = __shfl_sync(RM_FULL_MASK, pix, (q4 + 3) * TPP);
     const uint32_t pb_q = (uint32_t)warp * PPW + (uint32_t)q4;
-    const uint32_t row_q = ty * TILE_ROWS + (pb_q >> 3);
+    const uint32_t row_q = ty_o * TILE_ROWS + (pb_q >> 3);
     if (x0 + RM_DIRECT_TILE_W <= fp.W && (pitch & 15) == 0) {  // warp-uniform
         if (lane < QUADS && row_q < fp.nrows)
             *reinterpret_cast<uint4 *>(dst + (size_t)dst_row(fp, row_q) * pitch + (size_t)(x0 + (pb_q & 7u)) * 4) = v;
-    } else if (inside && grp == 0) {
-        *reinterpret_cast<uint32_t *>(dst + (size_t)dst_row(fp, ry) * pitch + (size_t)px * 4) = pix;
+    } else if (inside_o && grp == 0) {
+        *reinterpret_cast<uint32_t *>(dst + (size_t)dst_row(fp, ry_o) * pitch + (size_t)px_o * 4) = pix;
     }
 
     if (COUNT) {

@@ -536,7 +536,6 @@ cudaError_t launch_spec(const SpecKernel &k, const FrameParams &fp, const float 
                         unsigned long long *counters, uint8_t *aov_cls, float *aov_t, cudaStream_t st) {
     if (fp.nrows == 0 || fp.W == 0) return cudaSuccess;
     const uint32_t tile_h = direct_tile_rows(k.rays_per_thread);
-    const unsigned grid = ((fp.W + RM_DIRECT_TILE_W - 1) / RM_DIRECT_TILE_W) * ((fp.nrows + tile_h - 1) / tile_h);
     FrameParams p = fp;
     static const float kNoParams[4] = {0.0f, 0.0f, 0.0f, 0.0f};
     const float *pp = params ? params : kNoParams;  // the launch copies sizeof(SpecParams) bytes from here
@@ -544,7 +543,7 @@ cudaError_t launch_spec(const SpecKernel &k, const FrameParams &fp, const float 
     cudaGetDevice(&dev);
     k.dev_mask.fetch_or(1ull << (dev & 63));
     void *args[] = {&p, (void *)pp, &dst, &pitch, &counters, &aov_cls, &aov_t};
-    return cudaLaunchKernel((const void *)k.fn, dim3(grid), dim3(RM_DIRECT_THREADS), args, 0, st);
+    return cudaLaunchKernel((const void *)k.fn, direct_grid(fp, tile_h), dim3(RM_DIRECT_THREADS), args, 0, st);
 }
 
 }  // namespace rm

@@ -11,8 +11,11 @@ inline thread_local dim3 threadIdx, blockIdx, blockDim;
 inline thread_local HcWarp *hc_warp = nullptr;
 inline thread_local int hc_lane = 0;
 
+inline thread_local dim3 gridDim;
+
 template <class F>
-void hc_run_grid(unsigned grid, unsigned block_threads, F body) {
+void hc_run_grid(dim3 grid3, unsigned block_threads, F body) {
+    const unsigned grid = grid3.x * grid3.y;
     const unsigned warps_per_block = block_threads / 32, n_warps = grid * warps_per_block;
     unsigned workers = std::thread::hardware_concurrency() / 2;
     workers = workers < 1 ? 1 : (workers > 8 ? 8 : workers);
@@ -26,7 +29,9 @@ void hc_run_grid(unsigned grid, unsigned block_threads, F body) {
                 for (int lane = 0; lane < 32; ++lane) {
                     lanes[lane] = std::thread([&, lane] {
                         threadIdx.x = (g % warps_per_block) * 32 + lane;
-                        blockIdx.x = g / warps_per_block;
+                        blockIdx.x = (g / warps_per_block) % grid3.x;
+                        blockIdx.y = (g / warps_per_block) / grid3.x;
+                        gridDim = grid3;
                         blockDim.x = block_threads;
                         hc_warp = &warp;
                         hc_lane = lane;

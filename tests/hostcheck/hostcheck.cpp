@@ -43,8 +43,7 @@ template <bool EX, int R, bool COUNT, bool AOV, bool EXT>
 void paint_t(const FrameParams &fp, const Program &p, uint8_t *dst, size_t pitch, unsigned long long *counters, uint8_t *cls, float *t) {
     const float4 *prog = reinterpret_cast<const float4 *>(p.insns.data());
     const uint32_t tile_h = direct_tile_rows(R);
-    const unsigned grid = ((fp.W + RM_DIRECT_TILE_W - 1) / RM_DIRECT_TILE_W) * ((fp.nrows + tile_h - 1) / tile_h);
-    hc_run_grid(grid, RM_DIRECT_THREADS, [&] {
+    hc_run_grid(direct_grid(fp, tile_h), RM_DIRECT_THREADS, [&] {
         InterpMap<EX, R, false, EXT> map;
         map.prog = prog; map.n_insn = fp.n_insn; map.max_dist = fp.max_dist;
         direct_body<EX, R, COUNT, AOV>(fp, dst, pitch, counters, cls, t, map);

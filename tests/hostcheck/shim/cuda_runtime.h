@@ -73,6 +73,7 @@ static inline unsigned hc_exchange(unsigned v, int src) {
 }
 static inline unsigned __shfl_sync(unsigned, unsigned v, int src) { return hc_exchange(v, src); }
 static inline float __shfl_sync(unsigned, float v, int src) { return __uint_as_float(hc_exchange(__float_as_uint(v), src)); }
+static inline float __shfl_xor_sync(unsigned, float v, int lane_mask) { return __uint_as_float(hc_exchange(__float_as_uint(v), hc_lane ^ lane_mask)); }
 static inline unsigned __reduce_add_sync(unsigned, unsigned v) {
     hc_warp->slot[hc_lane] = v;
     pthread_barrier_wait(&hc_warp->bar);

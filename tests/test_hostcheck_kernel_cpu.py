@@ -202,8 +202,7 @@ extern "C" int hc_spec_paint(const void *uniforms144, const void *limits12, uint
     rm::FrameParams fp = rm::make_frame_params(u, lim[0], lim[1], max_iter, 0, W, H, row0, nrows);
     fp.strip_rows = strip_rows; fp.strip_pitch = strip_pitch; fp.dst_frame_rows = dst_frame_rows ? 1u : 0u;
     const uint32_t tile_h = rm::direct_tile_rows(HC_R);
-    const unsigned grid = ((W + RM_DIRECT_TILE_W - 1) / RM_DIRECT_TILE_W) * ((nrows + tile_h - 1) / tile_h);
-    hc_run_grid(grid, RM_DIRECT_THREADS, [&] { rm_spec(fp, P, dst, pitch, (unsigned long long *)counters4, aov_cls, aov_t); });
+    hc_run_grid(rm::direct_grid(fp, tile_h), RM_DIRECT_THREADS, [&] { rm_spec(fp, P, dst, pitch, (unsigned long long *)counters4, aov_cls, aov_t); });
     return 0;
 }
 """
