@@ -175,7 +175,9 @@ RM_API int rm_paint_culled_static(rm_ctx *ctx, uint32_t W, uint32_t H, uint32_t 
  * around the same kernel body.  The generated code depends on the program's STRUCTURE only: the opcode sequence, which
  * parameters are exactly zero (those stay literals so that `p - 0` folds) and, in exact mode, which smooth-union k are
  * powers of two.  Every other centre, radius, k, offset or matrix entry travels as a kernel argument (constant bank,
- * read through uniform registers).  So the reference's per-frame re-flatten and
+ * read through uniform registers) — or, for deep programs, whose scene code is one out-of-line function, in a constant
+ * block of the generated module that the paint refills on its stream when the values change (one block per device,
+ * shared by the contexts painting that structure: their launches of it are ordered).  So the reference's per-frame re-flatten and
  * re-upload (renderer.rs:224-239) and an editor dragging a value keep their compiled kernel: rm_prepare with new values
  * of the same structure costs no compile.  Arithmetic per ray is operation for operation the interpreter's: exact mode
  * stays bit-identical, fast mode may round differently where the compiler contracts multiply-adds (within the parity

@@ -154,7 +154,7 @@ struct ParamSink {
         }
         if (sig) sig->push_back(0xF0000002u);
         if (params) params->push_back(as_f32(bits));
-        return "P.f[" + std::to_string(n++) + "]";
+        return "@P@.f[" + std::to_string(n++) + "]";  // @P@: the kernel argument or the module's __constant__ copy, decided below
     }
 };
 
@@ -209,6 +209,8 @@ SpecKernel::~SpecKernel() {
     const uint64_t m = dev_mask.load();
     for (int d = 0; d < 64; ++d)
         if (m & (1ull << d)) { cudaSetDevice(d); cudaDeviceSynchronize(); }
+    for (auto &kv : cb)
+        if (kv.second.last_launch) { cudaSetDevice(kv.first); cudaEventDestroy(kv.second.last_launch); }
     cudaSetDevice(cur);
     cudaLibraryUnload(lib);
 }
@@ -227,7 +229,7 @@ void spec_cache_stats(size_t *entries, size_t *capacity, uint64_t *evictions) {
 
 int spec_generate_source(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, bool exact, int variant, int R,
                          std::string *src, int *r_out, int *minb_out, uint32_t *est_out, std::string *err,
-                         std::vector<float> *params, std::vector<uint32_t> *sig, bool literals) {
+                         std::vector<float> *params, std::vector<uint32_t> *sig, bool literals, bool *constbank_out) {
     // walk the postfix stream (builder.rs:26-62) with a stack of SSA value numbers: command i defines v<i>.
     // The stream has been validated by decode_program (rm_prepare / rm_spec_source); the checks here only keep the walk
     // itself in bounds and accept exactly what the decoder accepts.
@@ -382,17 +384,23 @@ int spec_generate_source(uint32_t cmd_count, const uint32_t *words, uint32_t n_w
     // tap loop, instead of an inlined copy in each: half the code (the instruction cache holds it with room to spare), no
     // spill at all, half the compile time, and specialisation keeps paying up to 64 leaves instead of 48 (measured on B200,
     // profiles/r2_s9_crossover.txt: 32 / 48 / 64 leaves x1.26 / 1.21 / 1.18 over the interpreter against x1.25 / 1.13 / 1.03
-    // inlined).  Shallow programs (4 rays) stay inlined: the call costs more than it saves there (cfg2 0.708 vs 0.680 ms),
-    // and so does the structure tier: inlined, ptxas hoists part of the argument loads out of the march loop, out of line
-    // every LDCU is paid per evaluation (cfg3 structure tier 38.9 ms out of line, 37.4 inlined).
-    bool noinline = R == 2 && literals;
+    // inlined).  Shallow programs (4 rays) stay inlined: the call costs more than it saves there (cfg2 0.708 vs 0.680 ms).
+    // STRUCTURE tier of a deep program: an out-of-line function cannot read the kernel's arguments as constants (through a
+    // reference they become generic loads: 38.3 ms against 37.0 inlined on cfg3), so the parameter block then lives in a
+    // __constant__ variable of the generated module (g_rm_spec_P, filled by launch_spec before the launch whenever the
+    // values change): LDCU / LDC from bank 3, one copy of the code — 35.8 ms (profiles/r2_s36_constbank.txt).
+    bool noinline = R == 2;
     if (const char *ns = std::getenv("RM_SPEC_NOINLINE")) noinline = ns[0] == '1';
+    bool constbank = noinline && !literals && par.n > 0;
+    if (const char *cs = std::getenv("RM_SPEC_CONSTBANK")) constbank = constbank && cs[0] == '1';
+    if (noinline && !literals && !constbank) noinline = std::getenv("RM_SPEC_NOINLINE") != nullptr;  // without the bank: inlined (measured)
     int minb = env_int("RM_SPEC_MINB");
     if (minb <= 0) minb = R == 2 ? (noinline ? 10 : 12) : (R == 4 ? 10 : 7);  // measured on B200: profiles/r1_s14_NOTES.md, r2_s8_noinline_sweep.jsonl
-    if (sig) { sig->push_back(0xF0000020u | (uint32_t)R); sig->push_back(0xF0000040u | (uint32_t)minb); sig->push_back(0xF0000080u | (noinline ? 1u : 0u)); }
+    if (sig) { sig->push_back(0xF0000020u | (uint32_t)R); sig->push_back(0xF0000040u | (uint32_t)minb); sig->push_back(0xF0000080u | (noinline ? 1u : 0u) | (constbank ? 2u : 0u)); }
     if (r_out) *r_out = R;
     if (minb_out) *minb_out = minb;
     if (est_out) *est_out = est;
+    if (constbank_out) *constbank_out = constbank;
     if (params) while (params->size() < 4 || params->size() % 4) params->push_back(0.0f);  // = sizeof(SpecParams): the launch copies all of it
     if (!src) return RM_OK;
 
@@ -400,9 +408,22 @@ int spec_generate_source(uint32_t cmd_count, const uint32_t *words, uint32_t n_w
     s += "// generated by rm_jit.cu: map_scene of one " + std::to_string(cmd_count) + "-command stream as straight-line code\n";
     s += "#include \"rm_direct_body.cuh\"\n";
     s += "namespace rm {\n";
+    {   // the parameter block's name in the scene code
+        const std::string name = constbank ? "g_rm_spec_P" : "P";
+        for (size_t at = body.find("@P@"); at != std::string::npos; at = body.find("@P@", at)) body.replace(at, 3, name);
+    }
     s += "struct alignas(16) SpecParams { float f[" + std::to_string(par.n ? ((par.n + 3u) & ~3u) : 4u) + "]; };  // the stream's non-zero parameters, in stream order\n";
-    s += "template <bool EX, int R>\nstruct SpecMap {\n    float max_dist;\n    const SpecParams &P;  // the kernel's __grid_constant__ argument: every use is a constant-bank operand\n";
-    s += "    __device__ __forceinline__ SpecMap(float md, const SpecParams &p) : max_dist(md), P(p) {}\n";
+    if (constbank) {
+        s += "}  // namespace rm\n#define RM_SPEC_CONSTBANK 1\n";
+        s += "extern \"C\" { __constant__ rm::SpecParams g_rm_spec_P; }  // written by launch_spec (a small kernel on the paint's stream) when the values change\n";
+        s += "namespace rm {\n";
+    }
+    s += "template <bool EX, int R>\nstruct SpecMap {\n    float max_dist;\n";
+    if (constbank) s += "    __device__ __forceinline__ SpecMap(float md, const SpecParams &) : max_dist(md) {}\n";
+    else {
+        s += "    const SpecParams &P;  // the kernel's __grid_constant__ argument\n";
+        s += "    __device__ __forceinline__ SpecMap(float md, const SpecParams &p) : max_dist(md), P(p) {}\n";
+    }
     if (noinline) {  // scalar arguments and a by-value result: nothing of the call goes through memory
         s += "    struct Out { float v[R]; };\n";
         s += "    __device__ __noinline__ Out eval(";
@@ -469,7 +490,7 @@ int spec_get(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, bool e
     SpecKernel meta;
     // generation is cheap (string building); it yields the structure signature = the cache key, and the parameter block
     int rc = spec_generate_source(cmd_count, words, n_words, exact, variant, 0, &src, &meta.rays_per_thread, &meta.min_blocks,
-                                  &meta.est_insn_per_ray, &gen_err, params, &key.sig, literals);
+                                  &meta.est_insn_per_ray, &gen_err, params, &key.sig, literals, &meta.constbank);
     if (rc != RM_OK) {
         if (err) *err = gen_err;
         return rc;
@@ -499,7 +520,7 @@ int spec_get(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, bool e
         const auto t0 = std::chrono::steady_clock::now();
         std::string cubin;
         auto k = std::make_shared<SpecKernel>();
-        k->exact = exact; k->variant = variant; k->literals = literals;
+        k->exact = exact; k->variant = variant; k->literals = literals; k->constbank = meta.constbank;
         k->rays_per_thread = meta.rays_per_thread; k->min_blocks = meta.min_blocks; k->est_insn_per_ray = meta.est_insn_per_ray;
         k->n_params = params ? (uint32_t)params->size() : 0;
         e.rc = spec_compile(src, &cubin, &e.err);
@@ -532,6 +553,15 @@ int spec_get(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, bool e
     return RM_OK;
 }
 
+namespace {
+// the refill of a module's __constant__ parameter block: the values travel as a kernel argument (no host buffer has to
+// outlive the call, no host synchronisation), the stores go through the symbol's global address
+struct ParamBlock { float f[kMaxParamBytes / sizeof(float)]; };
+__global__ void k_set_spec_params(float *__restrict__ dst, const __grid_constant__ ParamBlock p, uint32_t n) {
+    for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) dst[i] = p.f[i];
+}
+}  // namespace
+
 cudaError_t launch_spec(const SpecKernel &k, const FrameParams &fp, const float *params, uint8_t *dst, size_t pitch,
                         unsigned long long *counters, uint8_t *aov_cls, float *aov_t, cudaStream_t st) {
     if (fp.nrows == 0 || fp.W == 0) return cudaSuccess;
@@ -543,7 +573,34 @@ cudaError_t launch_spec(const SpecKernel &k, const FrameParams &fp, const float 
     cudaGetDevice(&dev);
     k.dev_mask.fetch_or(1ull << (dev & 63));
     void *args[] = {&p, (void *)pp, &dst, &pitch, &counters, &aov_cls, &aov_t};
-    return cudaLaunchKernel((const void *)k.fn, direct_grid(fp, tile_h), dim3(RM_DIRECT_THREADS), args, 0, st);
+    if (!k.constbank) return cudaLaunchKernel((const void *)k.fn, direct_grid(fp, tile_h), dim3(RM_DIRECT_THREADS), args, 0, st);
+
+    std::lock_guard<std::mutex> lock(k.cb_mu);
+    SpecKernel::ConstBank &b = k.cb[dev];
+    cudaError_t e = cudaSuccess;
+    if (!b.sym) {
+        void *sym = nullptr;
+        size_t bytes = 0;
+        e = cudaLibraryGetGlobal(&sym, &bytes, k.lib, "g_rm_spec_P");
+        if (e == cudaSuccess && bytes < (size_t)k.n_params * sizeof(float)) e = cudaErrorInvalidSymbol;
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&b.last_launch, cudaEventDisableTiming);
+        if (e != cudaSuccess) return e;
+        b.sym = (float *)sym;
+    }
+    // launches of this kernel on this device run one after the other, whatever their streams
+    if (b.launched && b.last_stream != st && (e = cudaStreamWaitEvent(st, b.last_launch, 0)) != cudaSuccess) return e;
+    if (b.written.size() != k.n_params || memcmp(b.written.data(), pp, (size_t)k.n_params * sizeof(float)) != 0) {
+        ParamBlock blk;
+        memcpy(blk.f, pp, (size_t)k.n_params * sizeof(float));
+        k_set_spec_params<<<1, 256, 0, st>>>(b.sym, blk, k.n_params);
+        if ((e = cudaGetLastError()) != cudaSuccess) return e;
+        b.written.assign(pp, pp + k.n_params);
+    }
+    e = cudaLaunchKernel((const void *)k.fn, direct_grid(fp, tile_h), dim3(RM_DIRECT_THREADS), args, 0, st);
+    if (e != cudaSuccess) return e;
+    b.launched = true;
+    b.last_stream = st;
+    return cudaEventRecord(b.last_launch, st);
 }
 
 }  // namespace rm

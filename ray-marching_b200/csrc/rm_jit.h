@@ -17,6 +17,10 @@
 #include <string>
 #include <vector>
 
+#include <map>
+#include <mutex>
+#include <vector>
+
 #include "rm_device.cuh"
 
 namespace rm {
@@ -36,6 +40,21 @@ struct SpecKernel {
     uint32_t est_insn_per_ray = 0;
     uint32_t n_params = 0;     // floats of the SpecParams kernel argument
     bool literals = false;     // literal tier: every parameter an immediate, one kernel per word stream
+    // Structure tier of a deep program: the scene code is out of line and reads its parameters from the module's
+    // __constant__ copy g_rm_spec_P (one per device).  launch_spec refills it — a small kernel on the paint's stream —
+    // whenever the values differ from the ones last written on that device, and orders the launches of this kernel on a
+    // device one after the other across streams, so that no launch still reads the block while it is rewritten (two
+    // contexts of one device may paint the same structure with different values).
+    bool constbank = false;
+    struct ConstBank {
+        float *sym = nullptr;            // device address of g_rm_spec_P on this device
+        std::vector<float> written;      // the values last written (n_params floats)
+        cudaEvent_t last_launch = nullptr;
+        cudaStream_t last_stream = nullptr;
+        bool launched = false;
+    };
+    mutable std::mutex cb_mu;
+    mutable std::map<int, ConstBank> cb;  // by device
     mutable std::atomic<uint64_t> dev_mask{0};  // devices that have launched it (synchronised before the cubin is unloaded)
     SpecKernel() = default;
     SpecKernel(const SpecKernel &) = delete;
@@ -57,7 +76,8 @@ using SpecHandle = std::shared_ptr<const SpecKernel>;
 // (no LDCU loads), worth compiling for words that stay put.
 int spec_generate_source(uint32_t cmd_count, const uint32_t *words, uint32_t n_words, bool exact, int variant,
                          int rays_per_thread, std::string *src, int *r_out, int *minb_out, uint32_t *est_out, std::string *err,
-                         std::vector<float> *params = nullptr, std::vector<uint32_t> *sig = nullptr, bool literals = false);
+                         std::vector<float> *params = nullptr, std::vector<uint32_t> *sig = nullptr, bool literals = false,
+                         bool *constbank_out = nullptr);
 
 // NVRTC-compiles `src` for sm_100a to a cubin (no GPU needed).  RM_E_JIT + message when libnvrtc cannot be loaded or
 // the compile fails.

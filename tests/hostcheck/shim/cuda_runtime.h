@@ -25,6 +25,7 @@
 #define __noinline__ __attribute__((noinline))
 #define __launch_bounds__(...)
 #define __grid_constant__
+#define __constant__ /* a plain global of the host build */
 
 struct float4 { float x, y, z, w; };
 struct uint4 { unsigned x, y, z, w; };

@@ -427,3 +427,74 @@ def test_specialize_compiles_both_tiers_at_once_and_fast_mode_tiers_agree(rm, ct
     for a, b in ((lit, par), (par, interp)):
         d = np.abs(a.astype(np.int16) - b.astype(np.int16)).max(-1)
         assert d.max() <= 1 and (d > 0).mean() <= 2e-3, (int(d.max()), float((d > 0).mean()))
+
+
+def _s2_variant(scale):
+    """S2's structure with other values: every radius scaled (no zero appears or disappears, so the structure is the same)."""
+    cmd, words = h.scene_s2()
+    w = np.array(words, np.uint32)
+    f = w.view(np.float32)
+    i = 0
+    while i < len(w):
+        op = int(w[i])
+        if op == 0:
+            f[i + 4] *= scale
+            i += 5
+        elif op == 1:
+            f[i + 4:i + 7] *= scale
+            i += 7
+        elif op == h.OP_SMOOTH_UNION:
+            i += 2
+        else:
+            i += 1
+    return cmd, [int(x) for x in w]
+
+
+def test_deep_structure_tier_reads_its_values_from_the_modules_constant_block(rm):
+    """The structure tier of a deep program keeps its parameters in a __constant__ block of the generated module, ONE per
+    device, shared by every context that paints that structure (rm_jit.cu launch_spec).  Two contexts of one GPU painting
+    the same structure with DIFFERENT values, launches interleaved on their own streams with no synchronisation in between,
+    and one context alternating values frame by frame, must each get their own frame — bit-identical to the oracle."""
+    W, H = 512, 288
+    u = h.orbit_uniforms(W, H, yaw=0.6, pitch=0.4)
+    progs = [_s2_variant(s) for s in (1.0, 0.8, 1.15)]
+    assert rm.spec_source(*progs[0]) == rm.spec_source(*progs[1]) == rm.spec_source(*progs[2])
+    assert "__constant__ rm::SpecParams g_rm_spec_P;" in rm.spec_source(*progs[0])
+    rows = [0, 57, 143, 144, 287]
+    refs = [np.stack([h.oracle_render(u, c, w, W, H, row0=r, nrows=1)["rgba"][0] for r in rows]) for c, w in progs]
+    with rm.Context(0) as a, rm.Context(0) as b:
+        for c in (a, b):
+            c.set_mode(rm.MODE_EXACT)
+            c.set_specialize(1)
+            c.set_spec_literal_after(0)          # never promoted: every paint below runs the structure kernel
+        out_a, out_b = np.zeros((H, W, 4), np.uint8), np.zeros((H, W, 4), np.uint8)
+        for it in range(6):
+            ia, ib = (0, 2)[it % 2], 1           # a alternates between two value sets, b keeps its own
+            a.prepare(u, *progs[ia])
+            a.paint(W, H)                        # asynchronous, a's stream
+            b.prepare(u, *progs[ib])
+            b.paint(W, H)                        # asynchronous, b's stream: a's kernel may still be running
+            assert a.spec_tier == 1 and b.spec_tier == 1 and a.spec_info()["rays_per_thread"] == 2
+            if it >= 4:                          # the last two rounds are read back (a: one frame of each value set)
+                a.download(out_a)
+                b.download(out_b)
+                assert np.array_equal(out_a[rows], refs[ia]), (it, "a")
+                assert np.array_equal(out_b[rows], refs[ib]), (it, "b")
+        assert a.spec_info()["compiles"] + b.spec_info()["compiles"] <= 1   # one structure: at most one compile (0 if cached)
+        # a pose batch (two streams inside the library) through the same kernel, in fast mode against single paints
+        a.set_mode(rm.MODE_FAST)
+        poses = [h.orbit_uniforms(W, H, yaw=0.4 * k, pitch=0.3) for k in range(4)]
+        buf = rm.PinnedBuffer(len(poses) * W * H * 4)
+        a.prepare(poses[0], *progs[2])
+        a.specialize()
+        a.set_spec_literal_after(0)
+        a.paint_poses_host(b"".join(poses), len(poses), W, H, buf.ptr)
+        got = buf.array.reshape(len(poses), H, W, 4).copy()
+        buf.free()
+        assert a.spec_tier == 1
+        for k, pu in enumerate(poses):
+            b.set_mode(rm.MODE_FAST)
+            b.set_specialize(False)
+            ref = b.render(pu, *progs[2], W, H)  # the interpreter, another context
+            d = np.abs(got[k].astype(np.int32) - ref.astype(np.int32)).max(-1)
+            assert float((d > 1).mean()) <= 4e-3, (k, int(d.max()))

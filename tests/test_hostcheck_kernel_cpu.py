@@ -196,6 +196,10 @@ extern "C" int hc_spec_paint(const void *uniforms144, const void *limits12, uint
                              uint64_t *counters4, uint8_t *aov_cls, float *aov_t) {
     rm::SpecParams P;
     memcpy(&P, hc_spec_params, sizeof P);
+#ifdef RM_SPEC_CONSTBANK   /* structure tier of a deep program: the scene code reads the module's copy (launch_spec refills it) */
+    memcpy(&g_rm_spec_P, hc_spec_params, sizeof g_rm_spec_P);
+    memset(&P, 0xff, sizeof P);   /* the kernel argument is not read */
+#endif
     float u[36], lim[2];
     uint32_t max_iter;
     memcpy(u, uniforms144, 144); memcpy(lim, limits12, 8); memcpy(&max_iter, (const char *)limits12 + 8, 4);

@@ -87,7 +87,12 @@ def test_rays_per_thread_follow_the_code_size(rm):
     assert "direct_body<false, 4," in rm.spec_source(cmd, words)
     cmd, words = h.scene_s2()  # 63 commands: ~9 KB of code per ray -> 2 rays keep the march loop in the instruction cache
     src = rm.spec_source(cmd, words)
-    assert "direct_body<false, 2," in src and "__launch_bounds__(RM_DIRECT_THREADS, 12)" in src and "__noinline__" not in src
+    # structure tier of a deep program: ONE out-of-line copy of the scene code too, its parameters in the module's
+    # __constant__ block (an out-of-line function cannot read the kernel's arguments as constants)
+    assert "direct_body<false, 2," in src and "__launch_bounds__(RM_DIRECT_THREADS, 10)" in src and "__noinline__ Out eval(" in src
+    assert "__constant__ rm::SpecParams g_rm_spec_P;" in src and "g_rm_spec_P.f[0]" in src and " P.f[" not in src and "@P@" not in src
+    s1 = rm.spec_source(*h.scene_s1())                    # shallow: inlined, parameters from the kernel argument
+    assert "__constant__" not in s1 and "P.f[0]" in s1 and "__noinline__" not in s1 and "@P@" not in s1
     lit = rm.spec_source(cmd, words, rm.MODE_FAST | rm.SPEC_LITERAL_TIER)   # the literal tier of a deep program: ONE out-of-line copy of the scene code
     assert "direct_body<false, 2," in lit and "__launch_bounds__(RM_DIRECT_THREADS, 10)" in lit
     assert "__noinline__ Out eval(float x0, float y0, float z0, float x1, float y1, float z1)" in lit
