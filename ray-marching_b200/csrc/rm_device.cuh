@@ -194,7 +194,8 @@ __device__ __forceinline__ void xf_scale(float bx, float by, float bz, float s, 
 // Exact mode evaluates that literally (inv_k = 1/k, used when k is a power of two).  Fast mode uses the algebraically
 // equal  min(a,b) - e*e,  e = max(k*s - |a-b|*s, 0),  s = sqrt(1/(4k)):  the FAST form of the program carries
 // (k*s, s) in the (inv_k, c4k) positions (rm_program.h smooth_constants_fast), and the blend is FADD, FFMA, 2 FMNMX, FFMA.
-template <bool EX>
+// SAT (fast mode, k*s <= 1 — rm_program.h smooth_fast_sat_ok): the clamp at 0 as the FFMA's .SAT modifier, same value.
+template <bool EX, bool SAT = false>
 __device__ __forceinline__ float op_smooth(float a, float b, float k, float inv_k, float c4k, bool k_pow2) {
     using A = Arith<EX>;
     if (EX) {
@@ -204,7 +205,7 @@ __device__ __forceinline__ float op_smooth(float a, float b, float k, float inv_
         return __fsub_rn(m, __fmul_rn(__fmul_rn(__fmul_rn(h, h), k), 0.25f));
     } else {
         const float ks = inv_k, s = c4k;
-        const float e = fmaxf(fmaf(-fabsf(a - b), s, ks), 0.0f);
+        const float e = SAT ? __saturatef(fmaf(-fabsf(a - b), s, ks)) : fmaxf(fmaf(-fabsf(a - b), s, ks), 0.0f);
         return fmaf(-e, e, fminf(a, b));
     }
 }

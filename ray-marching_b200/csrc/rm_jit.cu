@@ -351,7 +351,10 @@ int spec_generate_source(uint32_t cmd_count, const uint32_t *words, uint32_t n_w
                     smooth_constants_fast(k, &ks, &sk);
                     const uint32_t kb[2] = {as_u32(ks), as_u32(sk)};
                     par.group(kb, 2);
-                    e = "op_smooth<EX>(" + a + ", " + b + ", 0.0f, " + par(kb[0]) + ", " + par(kb[1]) + ", false)";
+                    // k*s <= 1: the clamp at 0 is the FFMA's .SAT — structural (a k dragged across 4 is another kernel)
+                    const bool sat = smooth_fast_sat_ok(ks);
+                    if (sig && !literals) sig->push_back(0xF0000010u | (sat ? 2u : 0u));
+                    e = std::string("op_smooth<EX, ") + (sat ? "true" : "false") + ">(" + a + ", " + b + ", 0.0f, " + par(kb[0]) + ", " + par(kb[1]) + ", false)";
                 }
                 est += kInsnSmooth;
             }

@@ -39,7 +39,10 @@ inline void set_k(RmInsn &in, float k, bool fast_form) {
     bool pow2 = false;
     smooth_constants(k, &in.inv_k, &in.c4k, &pow2);
     if (pow2) in.flags |= FLAG_K_POW2;
-    if (fast_form) smooth_constants_fast(k, &in.inv_k, &in.c4k);  // (k*s, s) in the slots of (1/k, 1/(4k))
+    if (fast_form) {
+        smooth_constants_fast(k, &in.inv_k, &in.c4k);  // (k*s, s) in the slots of (1/k, 1/(4k))
+        if (smooth_fast_sat_ok(in.inv_k)) in.flags |= FLAG_SAT_OK;
+    }
 }
 }  // namespace
 

@@ -77,6 +77,7 @@ enum : uint32_t {
     FLAG_PLANE = 1u << 9,
     FLAG_XF = 1u << 10,      // XOP_TRANSLATE / ROTATE / SCALE / RESET; slot bit 0: base = p (first step of a chain), else base = q
     FLAG_ACCMUL = 1u << 11,  // XOP_ACCMUL
+    FLAG_SAT_OK = 1u << 12,  // FAST form only: the smooth union's k*s <= 1, so max(k*s - s|a-b|, 0) is a saturate (smooth_constants_fast)
 };
 
 // RmInsn::op is a DENSE fused opcode 0..15 so that the interpreter dispatches through a single
@@ -131,7 +132,12 @@ void smooth_constants(float k, float *inv_k, float *c4k, bool *k_pow2);
 // Fast mode evaluates  min(a,b) - h*h*k/4  (h = max(k-|a-b|,0)/k)  as  min(a,b) - e*e  with
 // e = max(ks - |a-b|*s, 0),  s = sqrt(1/(4k)),  ks = k*s:  FADD, FFMA, 2 FMNMX, FFMA — one instruction fewer than
 // min(a,b) - (max(k-|a-b|,0))^2 * (1/(4k)).  For k a power of four (k = 0.25: s = 1) the two are the same numbers.
+// When k*s <= 1 (k <= 4) the clamp at 0 can be the FFMA's own .SAT modifier: k*s - s|a-b| never exceeds k*s, so the clamp
+// at 1 that comes with it never acts and the value is the same bit for bit — 4 instructions (FADD, FFMA.SAT, FMNMX, FFMA).
+// The compiled kernels use it (the choice is part of the structure signature), and so does the 8-ray interpreter
+// (FLAG_SAT_OK on the decoded instruction).
 void smooth_constants_fast(float k, float *ks, float *s);
+inline bool smooth_fast_sat_ok(float ks) { return ks <= 1.0f; }
 
 // Returns an RM_* code (rm_b200.h).  `out` may be null for validation only.
 // A prepared program is decoded twice (rm_abi.cu): the EXACT form keeps the sequential operation order and roundings of

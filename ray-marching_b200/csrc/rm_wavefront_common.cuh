@@ -100,7 +100,11 @@ __device__ __forceinline__ void map_evalR_tail(const float4 *__restrict__ prog, 
             if (fl & FLAG_BOX) tail_prim<R, true>(q0, q1, px, py, pz, v);
             else tail_prim<R, false>(q0, q1, px, py, pz, v);
             if (fl & FLAG_SMOOTH) {
-                RM_FOR_R { e[r] = fmaxf(fmaf(-fabsf(acc[r] - v[r]), q2.x, q1.w), 0.0f); m[r] = fminf(acc[r], v[r]); }
+                if (fl & FLAG_SAT_OK) {  // k*s <= 1: the clamp at 0 is the FFMA's .SAT (same value, one FMNMX fewer per ray)
+                    RM_FOR_R { e[r] = __saturatef(fmaf(-fabsf(acc[r] - v[r]), q2.x, q1.w)); m[r] = fminf(acc[r], v[r]); }
+                } else {
+                    RM_FOR_R { e[r] = fmaxf(fmaf(-fabsf(acc[r] - v[r]), q2.x, q1.w), 0.0f); m[r] = fminf(acc[r], v[r]); }
+                }
             } else {
                 if (fl & FLAG_UNION) {
                     RM_FOR_R m[r] = fminf(acc[r], v[r]);

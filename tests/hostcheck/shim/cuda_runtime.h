@@ -34,6 +34,7 @@ typedef int cudaError_t;
 typedef struct CUstream_st *cudaStream_t;
 static const cudaError_t cudaSuccess = 0;
 
+static inline float __saturatef(float x) { return fminf(fmaxf(x, 0.0f), 1.0f); }  /* NaN -> 0 like the device's .sat */
 static inline float __fadd_rn(float a, float b) { return a + b; }
 static inline float __fsub_rn(float a, float b) { return a - b; }
 static inline float __fmul_rn(float a, float b) { return a * b; }

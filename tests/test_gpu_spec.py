@@ -498,3 +498,46 @@ def test_deep_structure_tier_reads_its_values_from_the_modules_constant_block(rm
             ref = b.render(pu, *progs[2], W, H)  # the interpreter, another context
             d = np.abs(got[k].astype(np.int32) - ref.astype(np.int32)).max(-1)
             assert float((d > 1).mean()) <= 4e-3, (k, int(d.max()))
+
+
+@pytest.mark.parametrize("k", [0.05, 1.0, 3.99, 4.0, 4.01, 9.0])
+def test_fast_smooth_union_as_a_saturate_up_to_k_4_and_the_general_form_beyond(rm, ctx, k):
+    """Fast mode clamps the smooth union's blend term with the FFMA's .SAT modifier when k*s <= 1 (k <= 4) — the same value
+    as max(.,0) there — and keeps max(.,0) beyond.  A 10-leaf chain (8-ray interpreter with the common tail, both compiled
+    tiers) on either side of the switch: every kernel meets the image gate against the oracle (the one-sample kernel never
+    uses the saturate), and the production kernel's three builds differ only by multiply-add contraction."""
+    W, H = 192, 108
+    u = h.orbit_uniforms(W, H, yaw=0.5, pitch=0.35, radius=7.0)
+    words = h.sphere((-2.0, 0.0, 0.0), 0.7)
+    for i in range(1, 10):
+        leaf = h.box((-2.0 + 0.45 * i, 0.15 * (i % 3), 0.1 * i), (0.35, 0.3, 0.25)) if i % 2 else h.sphere((-2.0 + 0.45 * i, 0.2, 0.0), 0.45)
+        words = words + leaf + [h.OP_SMOOTH_UNION, h.fbits(k)]
+    cmd = 1 + 2 * 9
+    ref = h.oracle_render(u, cmd, words, W, H)["rgba"]
+    src = rm.spec_source(cmd, words, rm.MODE_FAST)
+    assert ("op_smooth<EX, true>(" in src) == (k <= 4.0) and ("op_smooth<EX, false>(" in src) == (k > 4.0)
+    ctx.set_mode(rm.MODE_FAST)
+    ctx.set_kernel(rm.KERNEL_SIMPLE)
+    plain = ctx.render(u, cmd, words, W, H)          # map_eval1: always max(.,0)
+    ctx.set_kernel(rm.KERNEL_DIRECT)
+    imgs = {}
+    ctx.set_specialize(False)
+    imgs["interpreter"] = ctx.render(u, cmd, words, W, H)
+    for name, after in (("structure", 0), ("literal", 1)):
+        ctx.set_spec_literal_after(after)
+        ctx.prepare(u, cmd, words)
+        ctx.specialize()
+        ctx.paint(W, H)
+        ctx.paint(W, H)
+        assert ctx.spec_tier == (1 if name == "structure" else 2)
+        imgs[name] = ctx.download(np.zeros((H, W, 4), np.uint8))
+    imgs["one-sample kernel"] = plain
+    for name, img in imgs.items():
+        g = gates(img, ref)                          # a blend clamped wrongly would move the whole surface (silhouette
+        assert g["rgba_frac"] <= 1e-2, (name, k, g)  # flips alone reach 0.6 % of the pixels of so small a frame at k = 0.05)
+    for name in ("structure", "literal"):            # the production kernel's three builds: contraction differences only
+        d = np.abs(imgs[name].astype(np.int32) - imgs["interpreter"].astype(np.int32)).max(-1)
+        assert int(d.max()) <= 2 and float((d > 0).mean()) <= 5e-3, (name, k, int(d.max()), float((d > 0).mean()))
+    ctx.set_mode(rm.MODE_EXACT)                      # and exact mode is what it was
+    ctx.set_specialize(False)
+    assert np.array_equal(ctx.render(u, cmd, words, W, H), ref)

@@ -268,3 +268,21 @@ def test_generated_kernel_with_eight_rays_per_thread(hc, rm_lib, tmp_path):
     u = h.orbit_uniforms(19, 11, yaw=0.6, pitch=0.4)
     got, r = spec_paint(tmp_path, rm_lib, cmd, words, u, 19, 11, R=8)
     assert r == 8 and np.array_equal(got["rgba"], h.oracle_render(u, cmd, words, 19, 11)["rgba"])
+
+
+@pytest.mark.parametrize("k", [0.05, 1.0, 4.0, 4.01, 9.0])
+def test_fast_smooth_union_saturate_form_equals_the_max_form_bit_for_bit(hc, k):
+    """Fast mode, 8 rays per thread: the common-tail interpreter clamps the blend term with a saturate when k*s <= 1
+    (FLAG_SAT_OK, rm_program.h); 4 rays per thread: map_evalR always uses max(., 0).  Same frame, bit for bit, on both
+    sides of k = 4 (beyond it neither uses the saturate)."""
+    W, H = 64, 36
+    u = h.orbit_uniforms(W, H, yaw=0.5, pitch=0.35, radius=7.0)
+    words = h.sphere((-2.0, 0.0, 0.0), 0.7)
+    for i in range(1, 10):
+        leaf = h.box((-2.0 + 0.45 * i, 0.15 * (i % 3), 0.1 * i), (0.35, 0.3, 0.25)) if i % 2 else h.sphere((-2.0 + 0.45 * i, 0.2, 0.0), 0.45)
+        words = words + leaf + [h.OP_SMOOTH_UNION, h.fbits(k)]
+    a = paint(hc, 19, words, u, W, H, exact=0, R=8, aov=True)
+    b = paint(hc, 19, words, u, W, H, exact=0, R=4, aov=True)
+    assert np.array_equal(a["rgba"], b["rgba"]) and np.array_equal(a["cls"], b["cls"])
+    assert np.array_equal(a["t"].view(np.uint32), b["t"].view(np.uint32))
+    assert (a["cls"] == 2).any()      # the chain is in view

@@ -52,8 +52,18 @@ def test_literal_tier_emits_constants_by_their_bits(rm):
     src = rm.spec_source(3, words, lit)
     s = np.float32(np.sqrt(0.25 / np.float64(np.float32(k))))
     ks = np.float32(np.float64(np.float32(k)) * np.sqrt(0.25 / np.float64(np.float32(k))))
-    m = re.search(r"op_smooth<EX>\(v0\[r\], v1\[r\], 0.0f, (\S+), (\S+), false\)", src)
+    # k*s <= 1 (k <= 4): the clamp at 0 rides on the FFMA as its .SAT modifier (op_smooth<EX, true>)
+    m = re.search(r"op_smooth<EX, true>\(v0\[r\], v1\[r\], 0.0f, (\S+), (\S+), false\)", src)
     assert m and m.group(1) == "__uint_as_float(0x%08xu)" % int(ks.view(np.uint32)) and m.group(2) == "__uint_as_float(0x%08xu)" % int(s.view(np.uint32))
+    big = list(words)
+    big[-1] = h.fbits(4.5)      # k*s = sqrt(k)/2 > 1: the general form
+    assert "op_smooth<EX, false>(" in rm.spec_source(3, big, lit) and "op_smooth<EX, true>(" not in rm.spec_source(3, big, lit)
+    four = list(words)
+    four[-1] = h.fbits(4.0)     # k*s = 1 exactly: still a saturate
+    assert "op_smooth<EX, true>(" in rm.spec_source(3, four, lit)
+    # structure tier: which of the two forms is structural, the value of k is not
+    st = lambda kk: rm.spec_source(3, words[:-1] + [h.fbits(kk)], rm.MODE_FAST)
+    assert st(0.3) == st(3.9) and st(0.3) != st(4.5) and st(4.5) == st(100.0)
     words[-1] = h.fbits(0.25)  # power of two: the exact-mode divide becomes a multiply by the exact reciprocal
     assert ", true)" in rm.spec_source(3, words, rm.MODE_EXACT | rm.SPEC_LITERAL_TIER)
 
