@@ -269,6 +269,29 @@ def reference_arm(args) -> int:
 
 
 # ---------------------------------------------------------------------------------------------- B200 arm
+def bind_to_gpu_cpus(index: int) -> str:
+    """Multi-rank runs: keep this process — and with it the first touch of its pinned host buffers — on the CPUs NVML names
+    as local to its GPU (what `numactl` would do for a launcher that does not).  The frames of cfg4 / cfg5 go back to host
+    memory over N PCIe links at once, and a buffer on the far socket halves a link's rate.  Returns what it did."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        hnd = pynvml.nvmlDeviceGetHandleByIndex(index)
+        n_cpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(hnd, (n_cpu + 63) // 64)
+        cpus = {64 * w + b for w, bits in enumerate(words) for b in range(64) if (int(bits) >> b) & 1}
+        allowed = os.sched_getaffinity(0)
+        cpus &= allowed
+        if not cpus:
+            return "no GPU-local CPU in this process's affinity mask: unchanged"
+        if cpus == allowed:
+            return f"all {len(allowed)} allowed CPUs are local to GPU {index}: unchanged"
+        os.sched_setaffinity(0, cpus)
+        return f"bound to the {len(cpus)} CPUs local to GPU {index} (of {len(allowed)} allowed)"
+    except Exception as e:  # NVML missing or no affinity information: run as launched
+        return f"unchanged ({type(e).__name__}: {e})"
+
+
 class Rig:
     """One rank's CUDA plumbing: the product context, a dedicated stream (the ABI reads a NULL stream as "the ctx's own
     stream", and the events that time the steps must sit on the stream the kernels are launched on), torch.distributed."""
@@ -283,6 +306,7 @@ class Rig:
         self.rank = int(os.environ.get("RANK", "0"))
         self.local_rank = int(os.environ.get("LOCAL_RANK", "0"))
         self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.cpu_binding = bind_to_gpu_cpus(self.local_rank) if self.world > 1 and args.bind_cpus == "on" else "not asked for"
         torch.cuda.set_device(self.local_rank)
         self.dev = torch.device("cuda", self.local_rank)
         self.dist = None
@@ -764,6 +788,8 @@ def b200_arm(args) -> int:
                           "(csrc/rm_cull.cu); frames and work counters are identical to the unculled paint, the work per evaluation is not "
                           "the shader's literal arithmetic: roofline.frac counts ALGORITHMIC flops and overstates, frac_executed counts the "
                           "flops of the instructions actually run")
+    if world > 1:
+        config["cpu_binding_rank0"] = rig.cpu_binding
     peaks = measured_peaks()
     hbm_gbs = float(peaks.get("hbm_gbs", 0.0)) or None
     extra = {}
@@ -1001,6 +1027,8 @@ def main():
     ap.add_argument("--cull", default="off", choices=["on", "off"],
                     help="opt-in per-tile culling of the program (exact: identical frames and counters; reported with executed flops, "
                          "never the headline); paints through the interpreter")
+    ap.add_argument("--bind-cpus", default="on", choices=["on", "off"],
+                    help="N > 1: bind each rank to the CPUs NVML reports as local to its GPU before it allocates pinned host memory")
     ap.add_argument("--e2e", default="serial", choices=["serial", "pipelined"],
                     help="end-to-end leg of the single-frame workloads.  serial (default): rm_prepare + rm_paint + rm_download per step, "
                          "each step waits for its frame.  pipelined: the steps go through rm_paint_poses_host, which copies frame k to "
