@@ -13,6 +13,7 @@
 #include "rm_program.h"
 
 #define RM_FOR_R _Pragma("unroll") for (int r = 0; r < R; ++r)
+#define RM_FOR_H _Pragma("unroll") for (int h = 0; h < R / 2; ++h)  /* pairs of rays (f2_t) */
 
 // The few places that pin an instruction with inline PTX go through these macros.  RM_HOST_CHECK is defined only by
 // tests/hostcheck (a host compile of the interpreters and of generated map_scene code, checked against the oracle
@@ -148,6 +149,62 @@ __device__ __forceinline__ float sd_box(float px, float py, float pz, float cx, 
     float qz = A::sub(fabsf(A::sub(pz, cz)), rz);
     float len = A::length3(fmaxf(qx, 0.0f), fmaxf(qy, 0.0f), fmaxf(qz, 0.0f));
     return A::add(len, fminf(fmaxf(qx, fmaxf(qy, qz)), 0.0f));
+}
+
+// ---- two rays at a time: the packed FP32 instructions of sm_100 (FADD2 / FMUL2 / FFMA2) -----------------------------
+// add / mul / fma.rn.f32x2 work on a 64-bit register pair holding two floats and issue ONCE for both: the kernels here are
+// bound by instruction issue, with the FMA pipe a third idle, so the generated scene code evaluates the rays of a thread
+// in pairs.  ptxas folds a broadcast scalar (immediate or uniform register), |x| and -x of the halves into the packed
+// instruction's operands (FADD2 R, |R|.F32x2.HI_LO, -UR.F32), so constants and modifiers cost nothing extra.  Per lane the
+// operations, their order and their roundings are the scalar fast-mode ones (sd_sphere<false>, sd_box<false>,
+// op_smooth<false, SAT>): the same bits.  Fast mode only; min / max / sqrt stay scalar per half (no packed form).
+#ifndef RM_HOST_CHECK
+typedef unsigned long long f2_t;
+__device__ __forceinline__ f2_t f2_pack(float lo, float hi) { f2_t r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ float f2_lo(f2_t v) { float a, b; asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); return a; }
+__device__ __forceinline__ float f2_hi(f2_t v) { float a, b; asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); return b; }
+__device__ __forceinline__ f2_t f2_add(f2_t a, f2_t b) { f2_t r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f2_t f2_sub(f2_t a, f2_t b) { f2_t r; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f2_t f2_mul(f2_t a, f2_t b) { f2_t r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f2_t f2_fma(f2_t a, f2_t b, f2_t c) { f2_t r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+#else
+struct f2_t { float lo, hi; };
+static inline f2_t f2_pack(float lo, float hi) { f2_t r; r.lo = lo; r.hi = hi; return r; }
+static inline float f2_lo(f2_t v) { return v.lo; }
+static inline float f2_hi(f2_t v) { return v.hi; }
+static inline f2_t f2_add(f2_t a, f2_t b) { return f2_pack(a.lo + b.lo, a.hi + b.hi); }
+static inline f2_t f2_sub(f2_t a, f2_t b) { return f2_pack(a.lo - b.lo, a.hi - b.hi); }
+static inline f2_t f2_mul(f2_t a, f2_t b) { return f2_pack(a.lo * b.lo, a.hi * b.hi); }
+static inline f2_t f2_fma(f2_t a, f2_t b, f2_t c) { return f2_pack(fmaf(a.lo, b.lo, c.lo), fmaf(a.hi, b.hi, c.hi)); }
+#endif
+__device__ __forceinline__ f2_t f2_all(float c) { return f2_pack(c, c); }
+__device__ __forceinline__ f2_t f2_abs(f2_t v) { return f2_pack(fabsf(f2_lo(v)), fabsf(f2_hi(v))); }
+__device__ __forceinline__ f2_t f2_neg(f2_t v) { return f2_pack(-f2_lo(v), -f2_hi(v)); }
+__device__ __forceinline__ f2_t f2_min(f2_t a, f2_t b) { return f2_pack(fminf(f2_lo(a), f2_lo(b)), fminf(f2_hi(a), f2_hi(b))); }
+__device__ __forceinline__ f2_t f2_max(f2_t a, f2_t b) { return f2_pack(fmaxf(f2_lo(a), f2_lo(b)), fmaxf(f2_hi(a), f2_hi(b))); }
+__device__ __forceinline__ f2_t f2_sqrt(f2_t v) { return f2_pack(Arith<false>::sqrt(f2_lo(v)), Arith<false>::sqrt(f2_hi(v))); }
+// sd_sphere<false> for two rays
+__device__ __forceinline__ f2_t sd_sphere2(f2_t px, f2_t py, f2_t pz, float cx, float cy, float cz, float r) {
+    const f2_t dx = f2_sub(px, f2_all(cx)), dy = f2_sub(py, f2_all(cy)), dz = f2_sub(pz, f2_all(cz));
+    return f2_sub(f2_sqrt(f2_fma(dz, dz, f2_fma(dy, dy, f2_mul(dx, dx)))), f2_all(r));
+}
+// sd_box<false> for two rays
+__device__ __forceinline__ f2_t sd_box2(f2_t px, f2_t py, f2_t pz, float cx, float cy, float cz, float rx, float ry, float rz) {
+    const f2_t qx = f2_sub(f2_abs(f2_sub(px, f2_all(cx))), f2_all(rx));
+    const f2_t qy = f2_sub(f2_abs(f2_sub(py, f2_all(cy))), f2_all(ry));
+    const f2_t qz = f2_sub(f2_abs(f2_sub(pz, f2_all(cz))), f2_all(rz));
+    const f2_t zero = f2_all(0.0f);
+    const f2_t ux = f2_max(qx, zero), uy = f2_max(qy, zero), uz = f2_max(qz, zero);
+    const f2_t len = f2_sqrt(f2_fma(uz, uz, f2_fma(uy, uy, f2_mul(ux, ux))));
+    return f2_add(len, f2_min(f2_max(qx, f2_max(qy, qz)), zero));
+}
+// op_smooth<false, SAT> for two rays: (ks, s) = (k*s, s) of smooth_constants_fast
+template <bool SAT>
+__device__ __forceinline__ f2_t op_smooth2(f2_t a, f2_t b, float ks, float s) {
+    const f2_t d = f2_sub(a, b);
+    const float x0 = fmaf(-fabsf(f2_lo(d)), s, ks), x1 = fmaf(-fabsf(f2_hi(d)), s, ks);
+    const f2_t e = SAT ? f2_pack(__saturatef(x0), __saturatef(x1)) : f2_pack(fmaxf(x0, 0.0f), fmaxf(x1, 0.0f));
+    return f2_fma(f2_neg(e), e, f2_min(a, b));
 }
 
 // ---- N4 extension (include/rm_b200.h RM_OP_PLANE, RM_OP_*_PUSH; normative order: oracle/rm_oracle.c map_scene) ----

@@ -241,6 +241,10 @@ int spec_generate_source(uint32_t cmd_count, const uint32_t *words, uint32_t n_w
     }
     auto sig_op = [&](uint32_t op) { if (sig && !literals) sig->push_back(op); };
     std::string body;
+    // the same scene code on PAIRS of rays (f2_t, rm_device.cuh: FADD2 / FMUL2 / FFMA2): fast mode, reference-set programs
+    std::string body2;
+    bool packable = !exact;
+    auto wvar = [](uint32_t i) { return "w" + std::to_string(i); };
     std::vector<uint32_t> stack;
     // N4: the evaluation point is an SSA value too — a Push defines q<i>x/y/z from the point in force, the Pop goes back
     // to the previous names.  The root point is the functor's argument (px, py, pz).
@@ -253,21 +257,24 @@ int spec_generate_source(uint32_t cmd_count, const uint32_t *words, uint32_t n_w
         if (!need(1)) { if (err) *err = "truncated command stream"; return RM_E_STACK_UNBALANCED; }
         const uint32_t op = words[ptr++];
         sig_op(op);
-        std::string e;
+        std::string e, e2;
+        if (op == RM_OP_PLANE || (op >= RM_OP_TRANSLATION_PUSH && op <= RM_OP_SCALE_POP)) packable = false;
         if (op == RM_OP_SPHERE) {
             if (!need(4)) { if (err) *err = "truncated sphere"; return RM_E_STACK_UNBALANCED; }
             par.group(words + ptr, 4);
             e = "sd_sphere<EX>(" + at();
-            for (int j = 0; j < 4; ++j) e += ", " + par(words[ptr + j]);
-            e += ")";
+            e2 = "sd_sphere2(PX[h], PY[h], PZ[h]";
+            for (int j = 0; j < 4; ++j) { const std::string a_ = par(words[ptr + j]); e += ", " + a_; e2 += ", " + a_; }
+            e += ")"; e2 += ")";
             ptr += 4; est += kInsnSphere;
             stack.push_back(i);
         } else if (op == RM_OP_BOX) {
             if (!need(6)) { if (err) *err = "truncated box"; return RM_E_STACK_UNBALANCED; }
             par.group(words + ptr, 6);
             e = "sd_box<EX>(" + at();
-            for (int j = 0; j < 6; ++j) e += ", " + par(words[ptr + j]);
-            e += ")";
+            e2 = "sd_box2(PX[h], PY[h], PZ[h]";
+            for (int j = 0; j < 6; ++j) { const std::string a_ = par(words[ptr + j]); e += ", " + a_; e2 += ", " + a_; }
+            e += ")"; e2 += ")";
             ptr += 6; est += kInsnBox;
             stack.push_back(i);
         } else if (op == RM_OP_PLANE) {
@@ -321,13 +328,13 @@ int spec_generate_source(uint32_t cmd_count, const uint32_t *words, uint32_t n_w
             continue;
         } else if (op == RM_OP_UNION || op == RM_OP_SUBTRACTION || op == RM_OP_INTERSECTION || op == RM_OP_SMOOTH_UNION) {
             if (stack.size() < 2 + pos.back().depth) { if (err) *err = "value stack underflow"; return RM_E_STACK_UNBALANCED; }
-            const std::string b = var(stack.back()) + "[r]";  // b = pop, a = pop  (wgsl:243-244)
+            const std::string b = var(stack.back()) + "[r]", b2 = wvar(stack.back()) + "[h]";  // b = pop, a = pop  (wgsl:243-244)
             stack.pop_back();
-            const std::string a = var(stack.back()) + "[r]";
+            const std::string a = var(stack.back()) + "[r]", a2 = wvar(stack.back()) + "[h]";
             stack.pop_back();
-            if (op == RM_OP_UNION) { e = "fminf(" + a + ", " + b + ")"; est += kInsnMinMax; }
-            else if (op == RM_OP_SUBTRACTION) { e = "fmaxf(" + a + ", -" + b + ")"; est += kInsnMinMax; }
-            else if (op == RM_OP_INTERSECTION) { e = "fmaxf(" + a + ", " + b + ")"; est += kInsnMinMax; }
+            if (op == RM_OP_UNION) { e = "fminf(" + a + ", " + b + ")"; e2 = "f2_min(" + a2 + ", " + b2 + ")"; est += kInsnMinMax; }
+            else if (op == RM_OP_SUBTRACTION) { e = "fmaxf(" + a + ", -" + b + ")"; e2 = "f2_max(" + a2 + ", f2_neg(" + b2 + "))"; est += kInsnMinMax; }
+            else if (op == RM_OP_INTERSECTION) { e = "fmaxf(" + a + ", " + b + ")"; e2 = "f2_max(" + a2 + ", " + b2 + ")"; est += kInsnMinMax; }
             else {
                 if (!need(1)) { if (err) *err = "truncated smooth union"; return RM_E_STACK_UNBALANCED; }
                 const float k = as_f32(words[ptr++]);
@@ -354,7 +361,9 @@ int spec_generate_source(uint32_t cmd_count, const uint32_t *words, uint32_t n_w
                     // k*s <= 1: the clamp at 0 is the FFMA's .SAT — structural (a k dragged across 4 is another kernel)
                     const bool sat = smooth_fast_sat_ok(ks);
                     if (sig && !literals) sig->push_back(0xF0000010u | (sat ? 2u : 0u));
-                    e = std::string("op_smooth<EX, ") + (sat ? "true" : "false") + ">(" + a + ", " + b + ", 0.0f, " + par(kb[0]) + ", " + par(kb[1]) + ", false)";
+                    const std::string ks_ = par(kb[0]), s_ = par(kb[1]);
+                    e = std::string("op_smooth<EX, ") + (sat ? "true" : "false") + ">(" + a + ", " + b + ", 0.0f, " + ks_ + ", " + s_ + ", false)";
+                    e2 = std::string("op_smooth2<") + (sat ? "true" : "false") + ">(" + a2 + ", " + b2 + ", " + ks_ + ", " + s_ + ")";
                 }
                 est += kInsnSmooth;
             }
@@ -365,6 +374,7 @@ int spec_generate_source(uint32_t cmd_count, const uint32_t *words, uint32_t n_w
         }
         if (stack.size() > RM_STACK_MAX) { if (err) *err = "value stack deeper than 32"; return RM_E_STACK_OVERFLOW; }
         body += "        float " + var(i) + "[R];\n        RM_FOR_R " + var(i) + "[r] = " + e + ";\n";
+        if (packable) body2 += "        f2_t " + wvar(i) + "[R / 2];\n        RM_FOR_H " + wvar(i) + "[h] = " + e2 + ";\n";
     }
     // same acceptance as decode_program: at least one value left (the shader's final pop_value takes the top), all groups closed
     if (cmd_count != 0 && (stack.empty() || pos.size() != 1)) { if (err) *err = "value stack ends empty or a transform group is open"; return RM_E_STACK_UNBALANCED; }
@@ -397,9 +407,18 @@ int spec_generate_source(uint32_t cmd_count, const uint32_t *words, uint32_t n_w
     bool constbank = noinline && !literals && par.n > 0;
     if (const char *cs = std::getenv("RM_SPEC_CONSTBANK")) constbank = constbank && cs[0] == '1';
     if (noinline && !literals && !constbank) noinline = std::getenv("RM_SPEC_NOINLINE") != nullptr;  // without the bank: inlined (measured)
+    // pairs of rays through the packed FP32 instructions: fast mode, reference-set programs (RM_SPEC_PACKED=0: measurement switch)
+    bool packed = packable && cmd_count != 0;
+    if (const char *ps = std::getenv("RM_SPEC_PACKED")) packed = packed && ps[0] != '0';
     int minb = env_int("RM_SPEC_MINB");
-    if (minb <= 0) minb = R == 2 ? (noinline ? 10 : 12) : (R == 4 ? 10 : 7);  // measured on B200: profiles/r1_s14_NOTES.md, r2_s8_noinline_sweep.jsonl
-    if (sig) { sig->push_back(0xF0000020u | (uint32_t)R); sig->push_back(0xF0000040u | (uint32_t)minb); sig->push_back(0xF0000080u | (noinline ? 1u : 0u) | (constbank ? 2u : 0u)); }
+    // measured on B200: profiles/r1_s14_NOTES.md, r2_s8_noinline_sweep.jsonl; in ray pairs (64-bit register pairs want more
+    // registers) profiles/r2_s45_packed.txt: cfg3 8 / 9 / 10 / 11 / 12 blocks 28.04 / 27.27 / 27.10 / 26.92 / 26.92 ms, cfg2 8 / 9 /
+    // 10 blocks 0.500 / 0.512 / 0.547 ms (10 spills inside the march loop)
+    if (minb <= 0) {
+        if (packed) minb = R == 2 ? (noinline ? (literals ? 11 : 10) : 12) : (R == 4 ? 8 : 7);  // structure tier: 28.47 ms at 10, 29.55 at 11
+        else minb = R == 2 ? (noinline ? 10 : 12) : (R == 4 ? 10 : 7);
+    }
+    if (sig) { sig->push_back(0xF0000020u | (uint32_t)R); sig->push_back(0xF0000040u | (uint32_t)minb); sig->push_back(0xF0000080u | (noinline ? 1u : 0u) | (constbank ? 2u : 0u) | (packed ? 4u : 0u)); }
     if (r_out) *r_out = R;
     if (minb_out) *minb_out = minb;
     if (est_out) *est_out = est;
@@ -414,7 +433,16 @@ int spec_generate_source(uint32_t cmd_count, const uint32_t *words, uint32_t n_w
     {   // the parameter block's name in the scene code
         const std::string name = constbank ? "g_rm_spec_P" : "P";
         for (size_t at = body.find("@P@"); at != std::string::npos; at = body.find("@P@", at)) body.replace(at, 3, name);
+        for (size_t at = body2.find("@P@"); at != std::string::npos; at = body2.find("@P@", at)) body2.replace(at, 3, name);
     }
+    // the scene code of one evaluation: px / py / pz[R] in, out[R] out
+    std::string scene;
+    if (cmd_count == 0) scene = "        RM_FOR_R out[r] = max_dist;  // wgsl:189-191\n";
+    else if (packed) {
+        scene = "        f2_t PX[R / 2], PY[R / 2], PZ[R / 2];  // rays 2h and 2h+1 side by side: every FADD / FMUL / FFMA below issues once for both\n"
+                "        RM_FOR_H { PX[h] = f2_pack(px[2 * h], px[2 * h + 1]); PY[h] = f2_pack(py[2 * h], py[2 * h + 1]); PZ[h] = f2_pack(pz[2 * h], pz[2 * h + 1]); }\n" +
+                body2 + "        RM_FOR_H { out[2 * h] = f2_lo(" + wvar(stack.back()) + "[h]); out[2 * h + 1] = f2_hi(" + wvar(stack.back()) + "[h]); }\n";
+    } else scene = body + "        RM_FOR_R out[r] = " + var(stack.back()) + "[r];\n";
     s += "struct alignas(16) SpecParams { float f[" + std::to_string(par.n ? ((par.n + 3u) & ~3u) : 4u) + "]; };  // the stream's non-zero parameters, in stream order\n";
     if (constbank) {
         s += "}  // namespace rm\n#define RM_SPEC_CONSTBANK 1\n";
@@ -433,16 +461,14 @@ int spec_generate_source(uint32_t cmd_count, const uint32_t *words, uint32_t n_w
         for (int r = 0; r < R; ++r) s += std::string(r ? ", " : "") + "float x" + std::to_string(r) + ", float y" + std::to_string(r) + ", float z" + std::to_string(r);
         s += ") const {\n        float px[R], py[R], pz[R], out[R];\n";
         for (int r = 0; r < R; ++r) s += "        px[" + std::to_string(r) + "] = x" + std::to_string(r) + "; py[" + std::to_string(r) + "] = y" + std::to_string(r) + "; pz[" + std::to_string(r) + "] = z" + std::to_string(r) + ";\n";
-        if (cmd_count == 0) s += "        RM_FOR_R out[r] = max_dist;\n";
-        else s += body + "        RM_FOR_R out[r] = " + var(stack.back()) + "[r];\n";
+        s += scene;
         s += "        Out o;\n        RM_FOR_R o.v[r] = out[r];\n        return o;\n    }\n";
         s += "    __device__ __forceinline__ void operator()(const float (&px)[R], const float (&py)[R], const float (&pz)[R], float (&out)[R]) {\n        const Out o = eval(";
         for (int r = 0; r < R; ++r) s += std::string(r ? ", " : "") + "px[" + std::to_string(r) + "], py[" + std::to_string(r) + "], pz[" + std::to_string(r) + "]";
         s += ");\n        RM_FOR_R out[r] = o.v[r];\n";
     } else {
     s += "    __device__ __forceinline__ void operator()(const float (&px)[R], const float (&py)[R], const float (&pz)[R], float (&out)[R]) {\n";
-    if (cmd_count == 0) s += "        RM_FOR_R out[r] = max_dist;  // wgsl:189-191\n";
-    else s += body + "        RM_FOR_R out[r] = " + var(stack.back()) + "[r];\n";
+    s += scene;
     }
     s += "    }\n};\n}  // namespace rm\n";
     s += "extern \"C\" __global__ void __launch_bounds__(RM_DIRECT_THREADS, " + std::to_string(minb) + ")\n";

@@ -74,6 +74,9 @@ __device__ __forceinline__ void acc_max(float &acc, float v) { RM_PTX_MAX_ACC(ac
 // Measured on B200 (profiles/r2_interp_NOTES.md): cfg3 with 8 rays 42.8 -> 41.2 ms; with 4 rays (short programs) it
 // loses (cfg2 1.07 -> 1.20 ms), so only the 8-ray kernels use it.  Dispatching PAIRS of instructions at once (decoder-
 // marked, 8 templated pair bodies) and 16 rays per thread were measured too and lost: 44.4 and 42.0 ms.
+// Evaluating the 8 rays as 4 PAIRS through FADD2 / FMUL2 / FFMA2 (rm_device.cuh f2_t — what the compiled kernels do) was
+// measured here too: 38.74 against 38.55 ms, no gain — at 72 registers the 64-bit register pairs cost ~350 MOV / IMAD.MOV
+// in the kernel and 192 instead of 144 bytes of spill (profiles/r2_s45_packed.txt).
 template <int R, bool BOX>
 __device__ __forceinline__ void tail_prim(const float4 &q0, const float4 &q1, const float (&px)[R], const float (&py)[R],
                                           const float (&pz)[R], float (&v)[R]) {

@@ -515,7 +515,7 @@ def test_fast_smooth_union_as_a_saturate_up_to_k_4_and_the_general_form_beyond(r
     cmd = 1 + 2 * 9
     ref = h.oracle_render(u, cmd, words, W, H)["rgba"]
     src = rm.spec_source(cmd, words, rm.MODE_FAST)
-    assert ("op_smooth<EX, true>(" in src) == (k <= 4.0) and ("op_smooth<EX, false>(" in src) == (k > 4.0)
+    assert ("op_smooth2<true>(" in src) == (k <= 4.0) and ("op_smooth2<false>(" in src) == (k > 4.0)   # fast mode: rays in pairs
     ctx.set_mode(rm.MODE_FAST)
     ctx.set_kernel(rm.KERNEL_SIMPLE)
     plain = ctx.render(u, cmd, words, W, H)          # map_eval1: always max(.,0)

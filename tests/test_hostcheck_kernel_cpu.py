@@ -286,3 +286,26 @@ def test_fast_smooth_union_saturate_form_equals_the_max_form_bit_for_bit(hc, k):
     assert np.array_equal(a["rgba"], b["rgba"]) and np.array_equal(a["cls"], b["cls"])
     assert np.array_equal(a["t"].view(np.uint32), b["t"].view(np.uint32))
     assert (a["cls"] == 2).any()      # the chain is in view
+
+
+@pytest.mark.parametrize("name,W,H", [("S1", 40, 22), ("S2", 40, 22), ("chain", 40, 22)])
+def test_generated_fast_kernel_in_ray_pairs_equals_the_interpreter_bit_for_bit(hc, rm_lib, tmp_path, name, W, H):
+    """Fast mode: the generated scene code evaluates the rays of a thread in PAIRS (f2_t; on the GPU FADD2 / FMUL2 / FFMA2).
+    Per lane it is the scalar fast-mode arithmetic, operation for operation, so the host build of the generated kernel —
+    S1 inlined with 4 rays per thread, S2 out of line with 2 and the constant block, a smooth-union chain on both sides of
+    k = 4 — gives the interpreter's fast-mode frame bit for bit."""
+    if name == "chain":
+        words = h.sphere((-2.0, 0.0, 0.0), 0.7)
+        for i in range(1, 10):
+            leaf = h.box((-2.0 + 0.45 * i, 0.15 * (i % 3), 0.1 * i), (0.35, 0.3, 0.25)) if i % 2 else h.sphere((-2.0 + 0.45 * i, 0.2, 0.0), 0.45)
+            words = words + leaf + [h.OP_SMOOTH_UNION, h.fbits((0.3, 4.0, 9.0)[i % 3])]
+        words = words + h.sphere((0.0, 0.4, 0.5), 0.5) + [h.OP_SUBTRACTION] + h.box((0, 0, 0), (3, 0.9, 0.9)) + [h.OP_INTERSECTION]
+        cmd = 19 + 4
+        u = h.orbit_uniforms(W, H, yaw=0.5, pitch=0.35, radius=7.0)
+    else:
+        cmd, words = h.SCENES[name]()
+        u = h.orbit_uniforms(W, H, yaw=0.6, pitch=0.4)
+    got, r = spec_paint(tmp_path, rm_lib, cmd, words, u, W, H, exact=False)
+    ref = paint(hc, cmd, words, u, W, H, exact=0, R=8 if name != "S1" else 4)
+    assert np.array_equal(got["rgba"], ref["rgba"]), (name, r)
+    assert (got["rgba"][..., :3] != got["rgba"][0, 0, :3]).any()

@@ -21,7 +21,8 @@ def _defs(src):
     return re.findall(r"RM_FOR_R (v\d+)\[r\] = (\w+)", src)
 
 
-def test_source_is_one_ssa_value_per_command_in_stream_order(rm):
+def test_source_is_one_ssa_value_per_command_in_stream_order(rm, monkeypatch):
+    monkeypatch.setenv("RM_SPEC_PACKED", "0")   # the scalar form of the fast-mode source (the packed one: test_fast_mode_source_evaluates_rays_in_pairs)
     cmd, words = h.scene_s1()  # box, sphere, union, sphere, subtraction  (main.rs:112-126)
     src = rm.spec_source(cmd, words, rm.MODE_FAST)
     assert [f for _, f in _defs(src)] == ["sd_box", "sd_sphere", "fminf", "sd_sphere", "fmaxf"]
@@ -32,7 +33,8 @@ def test_source_is_one_ssa_value_per_command_in_stream_order(rm):
     assert "direct_body<true, 4, false, false>" in rm.spec_source(cmd, words, rm.MODE_EXACT)
 
 
-def test_literal_tier_emits_constants_by_their_bits(rm):
+def test_literal_tier_emits_constants_by_their_bits(rm, monkeypatch):
+    monkeypatch.setenv("RM_SPEC_PACKED", "0")   # the scalar form of the fast-mode source (the packed one: test_fast_mode_source_evaluates_rays_in_pairs)
     lit = rm.MODE_FAST | rm.SPEC_LITERAL_TIER
     words = h.sphere((0.1, -2.5, 3.0e-7), 1.25)
     src = rm.spec_source(1, words, lit)
@@ -68,7 +70,8 @@ def test_literal_tier_emits_constants_by_their_bits(rm):
     assert ", true)" in rm.spec_source(3, words, rm.MODE_EXACT | rm.SPEC_LITERAL_TIER)
 
 
-def test_structure_tier_reads_parameters_from_the_kernel_argument(rm):
+def test_structure_tier_reads_parameters_from_the_kernel_argument(rm, monkeypatch):
+    monkeypatch.setenv("RM_SPEC_PACKED", "0")   # the scalar form of the fast-mode source (the packed one: test_fast_mode_source_evaluates_rays_in_pairs)
     """The default kernel depends on the STRUCTURE only: parameters are P.f[i] (a __grid_constant__ kernel argument), except
     exact zeros, which stay literals (and are part of the structure)."""
     a = h.sphere((0.1, -2.5, 0.0), 1.25) + h.box((0, 0, 0), (1, 2, 3)) + [103, h.fbits(0.3)]
@@ -104,7 +107,8 @@ def test_rays_per_thread_follow_the_code_size(rm):
     s1 = rm.spec_source(*h.scene_s1())                    # shallow: inlined, parameters from the kernel argument
     assert "__constant__" not in s1 and "P.f[0]" in s1 and "__noinline__" not in s1 and "@P@" not in s1
     lit = rm.spec_source(cmd, words, rm.MODE_FAST | rm.SPEC_LITERAL_TIER)   # the literal tier of a deep program: ONE out-of-line copy of the scene code
-    assert "direct_body<false, 2," in lit and "__launch_bounds__(RM_DIRECT_THREADS, 10)" in lit
+    assert "direct_body<false, 2," in lit and "__launch_bounds__(RM_DIRECT_THREADS, 11)" in lit   # in ray pairs: 11 resident blocks (10 scalar)
+    assert "__launch_bounds__(RM_DIRECT_THREADS, 10)" in rm.spec_source(cmd, words, rm.MODE_EXACT | rm.SPEC_LITERAL_TIER)
     assert "__noinline__ Out eval(float x0, float y0, float z0, float x1, float y1, float z1)" in lit
     assert "direct_body<false, 8," in rm.spec_source(cmd, words, rm.MODE_FAST, 8)  # explicit request is honoured
     # a chain far beyond the instruction-cache budget is refused (the interpreter is the better kernel there)
@@ -117,7 +121,8 @@ def test_rays_per_thread_follow_the_code_size(rm):
     assert e.value.code == -9
 
 
-def test_deep_stacks_and_empty_program(rm):
+def test_deep_stacks_and_empty_program(rm, monkeypatch):
+    monkeypatch.setenv("RM_SPEC_PACKED", "0")   # the scalar form of the fast-mode source (the packed one: test_fast_mode_source_evaluates_rays_in_pairs)
     # ((s0 u s1) n (s2 \ s3)): right operand is a subtree -> the interpreter needs a spill slot, SSA does not care
     s = [h.sphere((i, 0, 0), 1) for i in range(4)]
     words = s[0] + s[1] + [100] + s[2] + s[3] + [101] + [102]
@@ -134,7 +139,8 @@ def test_invalid_streams_are_rejected_with_the_validation_codes(rm, bad, code):
     assert e.value.code == code
 
 
-def test_generator_accepts_what_the_decoder_accepts(rm):
+def test_generator_accepts_what_the_decoder_accepts(rm, monkeypatch):
+    monkeypatch.setenv("RM_SPEC_PACKED", "0")   # the scalar form of the fast-mode source (the packed one: test_fast_mode_source_evaluates_rays_in_pairs)
     """ADVICE r1: a stream that leaves MORE than one value is valid — the shader's final pop_value takes the top
     (wgsl:200-202) — for rm_prepare and for the specialiser alike."""
     two = h.sphere((0, 0, 0), 1) + h.sphere((2, 0, 0), 0.5)
@@ -170,3 +176,22 @@ def test_extended_program_generates_position_ssa_and_compiles_for_sm_100a(rm):
         if r["rc"] == -9 and "NVRTC is not available" in r["log"]:
             pytest.skip("no libnvrtc in this environment: " + r["log"][:200])
         assert r["rc"] == 0, r["log"]
+
+
+def test_fast_mode_source_evaluates_rays_in_pairs(rm):
+    """Fast mode, reference-set programs: the scene code works on PAIRS of rays (f2_t: FADD2 / FMUL2 / FFMA2 of sm_100 issue
+    once for two rays), same operations per lane; exact mode and programs with N4 commands keep the scalar form."""
+    cmd, words = h.scene_s1()
+    src = rm.spec_source(cmd, words, rm.MODE_FAST)
+    assert re.findall(r"RM_FOR_H (w\d+)\[h\] = (\w+)", src) == [("w0", "sd_box2"), ("w1", "sd_sphere2"), ("w2", "f2_min"), ("w3", "sd_sphere2"), ("w4", "f2_max")]
+    assert "w4[h] = f2_max(w2[h], f2_neg(w3[h]))" in src and "PX[h] = f2_pack(px[2 * h], px[2 * h + 1])" in src
+    assert "out[2 * h] = f2_lo(w4[h]); out[2 * h + 1] = f2_hi(w4[h]);" in src and "RM_FOR_R v" not in src
+    ex = rm.spec_source(cmd, words, rm.MODE_EXACT)
+    assert "f2_t" not in ex and "RM_FOR_R v4[r] = fmaxf(v2[r], -v3[r])" in ex
+    c3, w3 = h.scene_s3()
+    assert "f2_t" not in rm.spec_source(c3, w3, rm.MODE_FAST)           # N4 commands: scalar
+    smooth = h.sphere((0, 0, 0), 1.0) + h.box((0.5, 0, 0), (1, 1, 1)) + [103, h.fbits(0.3)]
+    assert "w2[h] = op_smooth2<true>(w0[h], w1[h], " in rm.spec_source(3, smooth, rm.MODE_FAST)
+    big = smooth[:-1] + [h.fbits(9.0)]
+    assert "op_smooth2<false>(" in rm.spec_source(3, big, rm.MODE_FAST)
+    assert "RM_FOR_R out[r] = max_dist;" in rm.spec_source(0, [], rm.MODE_FAST)   # the empty program has nothing to pair
