@@ -119,8 +119,8 @@ class ClockSampler:
 
 # committed `ncu --set full` captures of (workload, kernel, specialised), newest first: DRAM bytes per launch
 NCU_SUMMARIES = {("cfg3", "wavefront2", False): ["r1_s3_wavefront2_R8_cfg3.ncu_summary.csv"],
-                 ("cfg3", "direct", False): ["r2_s41_interp_cfg3.ncu_summary.csv", "r2_s30_interp_cfg3.ncu_summary.csv", "r2_s22_interp_cfg3.ncu_summary.csv", "r2_interp_cfg3.ncu_summary.csv", "r1_final_direct_R8_cfg3.ncu_summary.csv"],
-                 ("cfg3", "direct", True): ["r2_s41_literal_cfg3.ncu_summary.csv", "r2_s30_literal_cfg3.ncu_summary.csv", "r2_s22_literal_cfg3.ncu_summary.csv", "r2_spec_cfg3.ncu_summary.csv", "r1_s14_spec_R2_cfg3.ncu_summary.csv"],
+                 ("cfg3", "direct", False): ["r2_s47_interp_cfg3.ncu_summary.csv", "r2_s41_interp_cfg3.ncu_summary.csv", "r2_s30_interp_cfg3.ncu_summary.csv", "r2_s22_interp_cfg3.ncu_summary.csv", "r2_interp_cfg3.ncu_summary.csv", "r1_final_direct_R8_cfg3.ncu_summary.csv"],
+                 ("cfg3", "direct", True): ["r2_s47_literal_cfg3.ncu_summary.csv", "r2_s41_literal_cfg3.ncu_summary.csv", "r2_s30_literal_cfg3.ncu_summary.csv", "r2_s22_literal_cfg3.ncu_summary.csv", "r2_spec_cfg3.ncu_summary.csv", "r1_s14_spec_R2_cfg3.ncu_summary.csv"],
                  ("n4", "direct", True): ["r1_s17_spec_R4_s3.ncu_summary.csv"]}
 
 
