@@ -160,10 +160,22 @@ def ncu_executed_fp32(workload: str, kernel: str, specialised: bool = False):
             peak = float(v["derived__sm__sass_thread_inst_executed_op_ffma_pred_on_x2"])
         except (KeyError, ValueError):
             return None
-        return {"fadd_per_cycle": fadd, "fmul_per_cycle": fmul, "ffma_per_cycle": ffma, "flops_per_cycle": fadd + fmul + 2 * ffma,
-                "peak_flops_per_cycle": peak, "frac": (fadd + fmul + 2 * ffma) / peak, "source": f"profiles/{name}",
-                "note": "FADD + FMUL + 2 x FFMA thread instructions per elapsed cycle under ncu (FMNMX, abs / neg modifiers and MUFU are "
-                        "not in these classes; the algorithmic count gives them one flop each)"}
+        def pct(key):
+            try:
+                return float(v[key])
+            except (KeyError, ValueError):
+                return None
+        out = {"fadd_per_cycle": fadd, "fmul_per_cycle": fmul, "ffma_per_cycle": ffma, "flops_per_cycle": fadd + fmul + 2 * ffma,
+               "peak_flops_per_cycle": peak, "frac": (fadd + fmul + 2 * ffma) / peak, "source": f"profiles/{name}",
+               "fma_pipe_cycles_active_pct": pct("sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active"),
+               "issue_slots_busy_pct": pct("sm__inst_issued.avg.pct_of_peak_sustained_active"),
+               "note": "FADD + FMUL + 2 x FFMA thread instructions per elapsed cycle under ncu (FMNMX, abs / neg modifiers and MUFU are "
+                       "not in these classes; the algorithmic count gives them one flop each)"}
+        if specialised:
+            out["note"] += ("; the compiled kernels do their adds / multiplies / FMAs as PACKED FADD2 / FMUL2 / FFMA2 (two rays per "
+                            "instruction), which ncu's scalar op classes do not count: for them frac here covers the scalar remainder "
+                            "only and fma_pipe_cycles_active_pct is the figure to read")
+        return out
     return None
 
 
