@@ -4,6 +4,7 @@ import re
 
 import numpy as np
 import pytest
+from pathlib import Path
 
 import helpers as h
 import rm_import
@@ -195,3 +196,40 @@ def test_fast_mode_source_evaluates_rays_in_pairs(rm):
     big = smooth[:-1] + [h.fbits(9.0)]
     assert "op_smooth2<false>(" in rm.spec_source(3, big, rm.MODE_FAST)
     assert "RM_FOR_R out[r] = max_dist;" in rm.spec_source(0, [], rm.MODE_FAST)   # the empty program has nothing to pair
+
+
+def test_the_newest_nvrtc_is_used_even_when_the_process_already_holds_an_older_one():
+    """A process that imported torch holds torch's bundled libnvrtc.so.12 (12.8 here) and a bare soname resolves to it; 12.8
+    builds the ray-pair scene code 24 % slower than the toolkit's 12.9.  rm_jit.cu loads every candidate
+    and keeps the newest: with the old one preloaded the cubin must be the one the toolkit's compiler produces."""
+    import os
+    import subprocess
+    import sys
+    old = Path(sys.prefix) / "lib" / f"python{sys.version_info.major}.{sys.version_info.minor}" / "site-packages" / "nvidia" / "cuda_nvrtc" / "lib" / "libnvrtc.so.12"
+    new = Path("/usr/local/cuda/lib64/libnvrtc.so.12")
+    if not old.exists() or not new.exists():
+        pytest.skip("needs both torch's bundled NVRTC and the toolkit's")
+    code = ("import ctypes, sys\n"
+            "pre = sys.argv[1]\n"
+            "if pre: ctypes.CDLL(pre, mode=ctypes.RTLD_GLOBAL)\n"
+            f"sys.path.insert(0, {str(h.ROOT / 'tests')!r}); sys.path.insert(0, {str(h.ROOT)!r})\n"
+            "import rm_import, helpers as h\n"
+            "rm = rm_import.load()\n"
+            "cmd, words = h.scene_s2()\n"
+            "r = rm.spec_compile_check(cmd, words, rm.MODE_FAST | rm.SPEC_LITERAL_TIER)\n"
+            "assert r['rc'] == 0, r\n"
+            "print(r['cubin_bytes'])\n")
+
+    def cubin_bytes(preload, env_path=None):
+        env = {k: v for k, v in os.environ.items() if k != "RM_NVRTC_PATH"}
+        if env_path:
+            env["RM_NVRTC_PATH"] = env_path
+        r = subprocess.run([sys.executable, "-c", code, preload], capture_output=True, text=True, env=env, timeout=600)
+        assert r.returncode == 0, r.stderr[-2000:]
+        return int(r.stdout.strip().splitlines()[-1])
+
+    with_new = cubin_bytes("", str(new))
+    with_old = cubin_bytes("", str(old))
+    assert cubin_bytes(str(old)) == with_new          # old one preloaded, no override: the newest candidate wins
+    if with_old == with_new:
+        pytest.skip("the two compilers produce the same cubin here: nothing to tell apart")
