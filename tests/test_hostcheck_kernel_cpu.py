@@ -212,11 +212,11 @@ extern "C" int hc_spec_paint(const void *uniforms144, const void *limits12, uint
 """
 
 
-def spec_paint(tmp_path, rm_lib, cmd, words, u, W, H, exact=True, R=0, **kw):
+def spec_paint(tmp_path, rm_lib, cmd, words, u, W, H, exact=True, R=0, literal=False, **kw):
     w = np.ascontiguousarray(np.asarray(words, np.uint32))
     buf = C.create_string_buffer(1 << 20)
     need = C.c_size_t()
-    rc = rm_lib.rm_spec_source(cmd, w.ctypes.data_as(u32p), w.size, 0 if exact else 1, R, buf, 1 << 20, C.byref(need))
+    rc = rm_lib.rm_spec_source(cmd, w.ctypes.data_as(u32p), w.size, (0 if exact else 1) | (0x100 if literal else 0), R, buf, 1 << 20, C.byref(need))
     assert rc == 0, rc
     src = buf.value.decode()
     r = int(re.search(r"rm::SpecMap<(?:true|false), (\d)> map\(", src).group(1))
@@ -227,7 +227,7 @@ def spec_paint(tmp_path, rm_lib, cmd, words, u, W, H, exact=True, R=0, **kw):
     table = "static const unsigned hc_spec_params_bits[] = {" + ", ".join("0x%08xu" % int(x) for x in params.view(np.uint32)) + "};\n" \
             "#define hc_spec_params ((const float *)hc_spec_params_bits)\n"
     cu.write_text('#include "hc_grid.h"\n' + src + f"\n#define HC_R {r}\n" + table + SPEC_DRIVER)
-    so = tmp_path / f"libspec_kernel_{abs(hash((cmd, bytes(w), exact, R)))}.so"  # params are baked into the driver: one .so per word stream
+    so = tmp_path / f"libspec_kernel_{abs(hash((cmd, bytes(w), exact, R, literal)))}.so"  # params are baked into the driver: one .so per word stream
     subprocess.run(CXX + ["-pthread", f"-I{HC_DIR}", "-o", str(so), str(cu)], check=True, capture_output=True)
     lib = C.CDLL(str(so))
     lib.hc_spec_paint.restype = C.c_int
@@ -309,3 +309,29 @@ def test_generated_fast_kernel_in_ray_pairs_equals_the_interpreter_bit_for_bit(h
     ref = paint(hc, cmd, words, u, W, H, exact=0, R=8 if name != "S1" else 4)
     assert np.array_equal(got["rgba"], ref["rgba"]), (name, r)
     assert (got["rgba"][..., :3] != got["rgba"][0, 0, :3]).any()
+
+
+@pytest.mark.parametrize("seed,n_leaves", [(0, 3), (1, 7), (2, 12), (3, 21)])
+def test_generated_fast_kernel_in_ray_pairs_on_random_trees(hc, rm_lib, tmp_path, seed, n_leaves):
+    """The same identity on random trees: every operator, smooth unions with several k, sub-trees on either side (spill
+    slots in the interpreter, SSA values in the generated code)."""
+    from test_gpu_parity import random_program
+    rng = np.random.default_rng(900 + seed)
+    words, cmd = random_program(rng, n_leaves)
+    W, H = 26, 15
+    u = h.orbit_uniforms(W, H, yaw=0.8 * seed, pitch=0.3, radius=5.0)
+    got, r = spec_paint(tmp_path, rm_lib, cmd, words, u, W, H, exact=False)
+    ref = paint(hc, cmd, words, u, W, H, exact=0)
+    assert np.array_equal(got["rgba"], ref["rgba"]), (seed, n_leaves, r)
+
+
+def test_generated_literal_tier_fast_kernel_equals_the_interpreter_bit_for_bit(hc, rm_lib, tmp_path):
+    """The literal tier of the deep scene (every value an immediate, out of line, rays in pairs) on the host."""
+    cmd, words = h.scene_s2()
+    W, H = 40, 22
+    u = h.orbit_uniforms(W, H, yaw=0.6, pitch=0.4)
+    got, r = spec_paint(tmp_path, rm_lib, cmd, words, u, W, H, exact=False, literal=True)
+    assert r == 2
+    assert np.array_equal(got["rgba"], paint(hc, cmd, words, u, W, H, exact=0, R=8)["rgba"])
+    got, _ = spec_paint(tmp_path, rm_lib, cmd, words, u, W, H, exact=True, literal=True)
+    assert np.array_equal(got["rgba"], h.oracle_render(u, cmd, words, W, H)["rgba"])
