@@ -137,9 +137,10 @@ const Nvrtc &nvrtc() {
     return n;
 }
 
-// Where a command parameter of the generated code comes from.  Default: the kernel's SpecParams argument (constant
-// bank; FADD / FFMA / FMNMX take a c[0x0][off] operand directly, so it costs no instruction and no register) — the code
-// then depends on the program's STRUCTURE only and one cubin serves every edit of a radius, a centre or a k.  Exception:
+// Where a command parameter of the generated code comes from.  Default: the kernel's SpecParams argument, or for deep
+// programs the module's __constant__ copy of it (constant bank either way, read through uniform registers: one LDCU per
+// 1-4 values on sm_100 — arithmetic takes UR operands, not c[bank][off] ones) — the code then depends on the program's
+// STRUCTURE only and one cubin serves every edit of a radius, a centre or a k.  Exception:
 // a parameter that is exactly +0 or -0 stays a literal (and its zero-ness is part of the structure signature), so that
 // `p - 0` and friends still fold; an editor drag leaves 0 once, not per frame.  The LITERAL tier emits every parameter
 // as an immediate by its bits and is keyed by the whole word stream: sm_100 arithmetic takes immediates for free, but a
